@@ -1,0 +1,140 @@
+// Shared host/device utilities for libvitb200: error reporting across the C ABI, launch checks, small math.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+namespace vb {
+
+// Thread-local error string returned by vitb200_last_error().  Nothing throws or exits across the ABI.
+void set_error(const char* fmt, ...);
+const char* last_error();
+
+constexpr int kOk = 0;
+constexpr int kErrInvalid = -1;   // bad argument (shape / alignment / dtype)
+constexpr int kErrCuda = -2;      // CUDA runtime / driver error
+constexpr int kErrUnsupported = -3;
+
+#define VB_CHECK_CUDA(expr)                                                                  \
+  do {                                                                                       \
+    cudaError_t _e = (expr);                                                                 \
+    if (_e != cudaSuccess) {                                                                 \
+      ::vb::set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__, cudaGetErrorString(_e)); \
+      return ::vb::kErrCuda;                                                                 \
+    }                                                                                        \
+  } while (0)
+
+#define VB_CHECK_LAUNCH() VB_CHECK_CUDA(cudaGetLastError())
+
+#define VB_REQUIRE(cond, ...)          \
+  do {                                 \
+    if (!(cond)) {                     \
+      ::vb::set_error(__VA_ARGS__);    \
+      return ::vb::kErrInvalid;        \
+    }                                  \
+  } while (0)
+
+#define VB_PROPAGATE(expr)        \
+  do {                            \
+    int _rc = (expr);             \
+    if (_rc != ::vb::kOk) return _rc; \
+  } while (0)
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+template <typename T>
+__host__ __device__ constexpr T ceil_div(T a, T b) {
+  return (a + b - 1) / b;
+}
+
+int num_sms();  // SM count of the current device (cached)
+
+// ---------------------------------------------------------------------------------------------------
+// Counter-based dropout RNG (Philox4x32-10).  One call yields 4 uniform 32-bit words for a
+// (seed, stream, index/4) triple, so forward and backward regenerate identical masks without storing them.
+// ---------------------------------------------------------------------------------------------------
+struct Philox4 {
+  uint32_t x, y, z, w;
+};
+__host__ __device__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b) {
+#ifdef __CUDA_ARCH__
+  return __umulhi(a, b);
+#else
+  return static_cast<uint32_t>((static_cast<uint64_t>(a) * b) >> 32);
+#endif
+}
+__host__ __device__ __forceinline__ Philox4 philox4x32_10(uint64_t seed, uint64_t stream, uint64_t ctr) {
+  uint32_t c0 = static_cast<uint32_t>(ctr), c1 = static_cast<uint32_t>(ctr >> 32);
+  uint32_t c2 = static_cast<uint32_t>(stream), c3 = static_cast<uint32_t>(stream >> 32);
+  uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = mulhi32(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = mulhi32(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return Philox4{c0, c1, c2, c3};
+}
+// keep-probability threshold on a 32-bit word: keep iff word < thresh (thresh = keep * 2^32, saturating).
+__host__ __device__ __forceinline__ uint32_t keep_threshold(float p_drop) {
+  const double keep = 1.0 - static_cast<double>(p_drop);
+  const double t = keep * 4294967296.0;
+  return t >= 4294967295.0 ? 0xFFFFFFFFu : static_cast<uint32_t>(t);
+}
+
+// Dropout descriptor passed by value to kernels.  p == 0 disables (eval mode / parity mode).
+struct Dropout {
+  float p;            // drop probability
+  float scale;        // 1 / (1 - p)
+  uint32_t thresh;    // keep iff rnd < thresh
+  uint64_t seed;
+  uint64_t stream;    // distinguishes call sites (layer id * 2 + {proj, fc2})
+};
+inline Dropout make_dropout(float p, uint64_t seed, uint64_t stream) {
+  Dropout d;
+  d.p = p;
+  d.scale = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  d.thresh = keep_threshold(p);
+  d.seed = seed;
+  d.stream = stream;
+  return d;
+}
+// 4 consecutive elements starting at linear index `idx4*4`: returns multiplicative factors (0 or scale).
+__device__ __forceinline__ void dropout_factors4(const Dropout& d, uint64_t idx4, float (&f)[4]) {
+  const Philox4 r = philox4x32_10(d.seed, d.stream, idx4);
+  f[0] = r.x < d.thresh ? d.scale : 0.f;
+  f[1] = r.y < d.thresh ? d.scale : 0.f;
+  f[2] = r.z < d.thresh ? d.scale : 0.f;
+  f[3] = r.w < d.thresh ? d.scale : 0.f;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// dtype helpers
+// ---------------------------------------------------------------------------------------------------
+using bf16 = __nv_bfloat16;
+__device__ __forceinline__ float to_f32(float v) { return v; }
+__device__ __forceinline__ float to_f32(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f32<bf16>(float v) { return __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+}  // namespace vb

@@ -1,0 +1,140 @@
+// fp32 CUDA-core contraction used when the model runs in fp32 (the 1e-4 parity gate; tensor cores cannot
+// meet it).  128x128x8 tiles, 8x8 register micro-tiles, arbitrary M/N/K/strides, same epilogue semantics as
+// the tcgen05 kernel.  Replaces the fp32 cuBLAS calls behind nn.Linear / Conv2d of the reference
+// (transformer.py:22-28,46,56-58; vit.py:21-28) and their autograd backward.
+#include "common.cuh"
+#include "gemm_epilogue.cuh"
+
+namespace vb {
+
+namespace {
+
+constexpr int FBM = 128, FBN = 128, FBK = 8, FTHREADS = 256;
+
+__device__ __forceinline__ void epilogue_store1_f32(const GemmEpilogue& ep, int m, int n, int N, float v) {
+  if (ep.bias != nullptr) v += __ldg(ep.bias + n);
+  if (ep.relu) v = fmaxf(v, 0.f);
+  const int64_t off = epi_out_row(ep, m) * ep.ldc + n;
+  if (ep.mask_aux != nullptr) v = reinterpret_cast<const float*>(ep.mask_aux)[off] > 0.f ? v : 0.f;
+  if (ep.drop.p > 0.f) {
+    const uint64_t lin = static_cast<uint64_t>(m) * static_cast<uint64_t>(N) + static_cast<uint64_t>(n);
+    const Philox4 r = philox4x32_10(ep.drop.seed, ep.drop.stream, lin >> 2);
+    const uint32_t w = (lin & 3) == 0 ? r.x : (lin & 3) == 1 ? r.y : (lin & 3) == 2 ? r.z : r.w;
+    v *= w < ep.drop.thresh ? ep.drop.scale : 0.f;
+  }
+  if (ep.row_add != nullptr) {
+    const int pr = ep.row_period > 0 ? (m % ep.row_period) : m;
+    v += __ldg(ep.row_add + static_cast<int64_t>(pr) * N + n);
+  }
+  if (ep.residual != nullptr) v += ep.residual[off];
+  float* c = reinterpret_cast<float*>(ep.C) + off;
+  if (ep.accumulate) atomicAdd(c, v);
+  else *c = v;
+}
+
+// A(m,k) = A[m*sam + k*sak], B(n,k) = B[n*sbn + k*sbk]
+template <bool A_KMAJOR, bool B_KMAJOR>
+__global__ void __launch_bounds__(FTHREADS)
+gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ B, int64_t ldb, int M, int N,
+                int K, int k_per_split, const GemmEpilogue ep) {
+  __shared__ float As[FBK][FBM + 4];
+  __shared__ float Bs[FBK][FBN + 4];
+  const int tid = threadIdx.x;
+  const int m0 = blockIdx.y * FBM, n0 = blockIdx.x * FBN;
+  const int k_begin = blockIdx.z * k_per_split;
+  const int k_end = min(K, k_begin + k_per_split);
+  const int tx = tid % 16, ty = tid / 16;  // micro-tile: rows ty*8.., cols tx*8..
+
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = k_begin; k0 < k_end; k0 += FBK) {
+    // ---- stage tiles (4 elements per thread per operand), coalesced along the contiguous index
+#pragma unroll
+    for (int i = 0; i < (FBM * FBK) / FTHREADS; ++i) {
+      const int e = tid + i * FTHREADS;
+      int r, kk;
+      if (A_KMAJOR) { kk = e % FBK; r = e / FBK; } else { r = e % FBM; kk = e / FBM; }
+      const int gm = m0 + r, gk = k0 + kk;
+      float v = 0.f;
+      if (gm < M && gk < k_end) v = A_KMAJOR ? A[static_cast<int64_t>(gm) * lda + gk] : A[static_cast<int64_t>(gk) * lda + gm];
+      As[kk][r] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < (FBN * FBK) / FTHREADS; ++i) {
+      const int e = tid + i * FTHREADS;
+      int r, kk;
+      if (B_KMAJOR) { kk = e % FBK; r = e / FBK; } else { r = e % FBN; kk = e / FBN; }
+      const int gn = n0 + r, gk = k0 + kk;
+      float v = 0.f;
+      if (gn < N && gk < k_end) v = B_KMAJOR ? B[static_cast<int64_t>(gn) * ldb + gk] : B[static_cast<int64_t>(gk) * ldb + gn];
+      Bs[kk][r] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < FBK; ++kk) {
+      float a[8], b[8];
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[kk][ty * 8]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[kk][ty * 8 + 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 8]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 8 + 4]);
+      a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+      b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int m = m0 + ty * 8 + i;
+    if (m >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int n = n0 + tx * 8 + j;
+      if (n < N) epilogue_store1_f32(ep, m, n, N, acc[i][j]);
+    }
+  }
+}
+
+}  // namespace
+
+int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int64_t lda, const float* B,
+             int64_t ldb, int splits, const GemmEpilogue& ep_in, cudaStream_t stream) {
+  VB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_f32: empty problem M=%d N=%d K=%d", M, N, K);
+  GemmEpilogue ep = ep_in;
+  int s = ep.accumulate ? splits : 1;
+  const int tiles = ceil_div(M, FBM) * ceil_div(N, FBN);
+  if (s <= 0) {
+    s = ceil_div(2 * num_sms(), tiles);
+    const int max_s = K / 64 > 0 ? K / 64 : 1;
+    if (s > max_s) s = max_s;
+    if (s < 1) s = 1;
+  }
+  int k_per_split = ceil_div(ceil_div(K, s), FBK) * FBK;
+  s = ceil_div(K, k_per_split);
+  dim3 grid(ceil_div(N, FBN), ceil_div(M, FBM), s);
+  VB_REQUIRE(grid.y <= 65535 && grid.z <= 65535, "gemm_f32: grid too large");
+  if (a_major == 0 && b_major == 0)
+    gemm_f32_kernel<true, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);
+  else if (a_major == 0 && b_major == 1)
+    gemm_f32_kernel<true, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);
+  else if (a_major == 1 && b_major == 1)
+    gemm_f32_kernel<false, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);
+  else if (a_major == 1 && b_major == 0)
+    gemm_f32_kernel<false, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);
+  else {
+    set_error("gemm_f32: bad operand majors a=%d b=%d", a_major, b_major);
+    return kErrInvalid;
+  }
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+}  // namespace vb

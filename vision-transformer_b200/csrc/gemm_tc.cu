@@ -1,0 +1,316 @@
+// bf16 x bf16 -> fp32 contraction on the 5th-gen tensor cores (tcgen05.mma, accumulators in TMEM),
+// operands staged by TMA (128B swizzle) through a 4-deep mbarrier ring, persistent over output tiles,
+// warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM allocator), warps 2-5 = epilogue.
+// Two TMEM accumulator stages (2 x BN columns) let the epilogue of tile i overlap the mainloop of tile i+1.
+//
+// Replaces the cuBLAS calls behind nn.Linear at reference transformer.py:22-28,46,56-58 and the patch
+// Conv2d at vit.py:21-28 (as an im2col GEMM), plus their autograd backward GEMMs.
+#include <cuda.h>
+#include <mutex>
+
+#include "common.cuh"
+#include "gemm_epilogue.cuh"
+#include "ptx.cuh"
+
+namespace vb {
+
+namespace {
+
+constexpr int BM = 128;          // UMMA M (cta_group::1)
+constexpr int BK = 64;           // 64 bf16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kStages = 4;
+constexpr int kThreads = 192;
+
+template <int BN>
+struct TileCfg {
+  static constexpr int A_BYTES = BM * BK * 2;       // 16 KB
+  static constexpr int B_BYTES = BN * BK * 2;       // 32 KB @ BN=256
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + BAR_BYTES + 1024;  // +1024 alignment slack
+  static constexpr int TMEM_COLS = 2 * BN;
+};
+
+struct TcParams {
+  int M, N, K;
+  int m_tiles, n_tiles;
+  int splits, kb_per_split, kb_total;
+};
+
+template <int AMAJ, int BMAJ, int BN, typename OutT>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+               const TcParams p, const GemmEpilogue ep) {
+  using Cfg = TileCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tmem_full = empty_bar + kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles = p.m_tiles * p.n_tiles;
+  const int total_work = tiles * p.splits;
+
+  if (threadIdx.x == 0) {
+    ptx::tma_prefetch_desc(&tma_a);
+    ptx::tma_prefetch_desc(&tma_b);
+    for (int s = 0; s < kStages; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&tmem_full[s], 1);
+      ptx::mbar_init(&tmem_empty[s], 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_ptr, Cfg::TMEM_COLS);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int split = w / tiles;
+        const int tile = w - split * tiles;
+        const int m_blk = tile / p.n_tiles;
+        const int n_blk = tile - m_blk * p.n_tiles;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1u);
+          ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+          uint8_t* sA = smem + stage * Cfg::STAGE_BYTES;
+          uint8_t* sB = sA + Cfg::A_BYTES;
+          if constexpr (AMAJ == 0) {
+            ptx::tma_load_2d(sA, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              ptx::tma_load_2d(sA + j * (BK * 128), &tma_a, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+          }
+          if constexpr (BMAJ == 0) {
+            ptx::tma_load_2d(sB, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              ptx::tma_load_2d(sB + j * (BK * 128), &tma_b, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(BM, BN, AMAJ, BMAJ);
+      // K-major: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.
+      // MN-major: 64-wide MN slabs BK*128 B apart (LBO), 8 k-rows = 1024 B (SBO), k-step = 16 rows * 128 B.
+      constexpr uint32_t a_lbo = AMAJ == 0 ? 16 : BK * 128, a_sbo = 1024, a_kstep = AMAJ == 0 ? 32 : 2048;
+      constexpr uint32_t b_lbo = BMAJ == 0 ? 16 : BK * 128, b_sbo = 1024, b_kstep = BMAJ == 0 ? 32 : 2048;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+        const int split = w / tiles;
+        const int kb0 = split * p.kb_per_split;
+        const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+        ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t a_addr = ptx::smem_u32(smem + stage * Cfg::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + Cfg::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t da = ptx::make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, a_sbo);
+            const uint64_t db = ptx::make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, b_sbo);
+            ptx::umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty_bar[stage]);   // smem slot reusable once these MMAs retire
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+        ptx::umma_commit(&tmem_full[acc]);        // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue (4 warps, 1 row / thread)
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      const int split = w / tiles;
+      const int tile = w - split * tiles;
+      const int m_blk = tile / p.n_tiles;
+      const int n_blk = tile - m_blk * p.n_tiles;
+      const int m = m_blk * BM + q * 32 + lane;
+      ptx::mbar_wait(&tmem_full[acc], acc_phase);
+      ptx::tc_fence_after();
+      const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int n0 = n_blk * BN + c * 32;
+        if (n0 >= p.N) break;                      // warp-uniform
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(c * 32), r);
+        ptx::tmem_ld_wait();
+        if (m < p.M) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int n = n0 + j * 8;
+            if (n < p.N) {
+              float v[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[j * 8 + i]);
+              epilogue_store8<OutT>(ep, m, n, p.N, v);
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+}  // namespace
+
+// ----------------------------------------------------------------------------------------------------
+// Host side: tensor maps + launch
+// ----------------------------------------------------------------------------------------------------
+namespace {
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// 2-D bf16 tensor map over a row-major matrix [rows][ld] whose logical width is `cols`;
+// box = box_cols (inner, <= 64 elements = 128 B) x box_rows, 128B swizzle, OOB reads return zero.
+int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_cols,
+                   int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (enc == nullptr) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return kErrCuda;
+  }
+  const cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  const cuuint64_t gstr[1] = {static_cast<cuuint64_t>(ld) * 2};
+  const cuuint32_t box[2] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows)};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d): rows=%lld cols=%lld ld=%lld box=%dx%d", static_cast<int>(r),
+              static_cast<long long>(rows), static_cast<long long>(cols), static_cast<long long>(ld), box_cols, box_rows);
+    return kErrCuda;
+  }
+  return kOk;
+}
+
+template <int AMAJ, int BMAJ, int BN, typename OutT>
+int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
+              cudaStream_t stream) {
+  using Cfg = TileCfg<BN>;
+  auto kern = gemm_tc_kernel<AMAJ, BMAJ, BN, OutT>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+  });
+  VB_CHECK_CUDA(attr_err);
+  const int total = p.m_tiles * p.n_tiles * p.splits;
+  const int grid = total < num_sms() ? total : num_sms();
+  kern<<<grid, kThreads, Cfg::SMEM_BYTES, stream>>>(ta, tb, p, ep);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+}  // namespace
+
+// Entry used by vitb200_gemm() for in_dtype == BF16.  out_f32 selects the C dtype.
+int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, int64_t lda, const void* B,
+                 int64_t ldb, bool out_f32, int splits, const GemmEpilogue& ep, cudaStream_t stream) {
+  VB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tc: empty problem M=%d N=%d K=%d", M, N, K);
+  VB_REQUIRE(N % 8 == 0 && ep.ldc % 8 == 0, "gemm_tc: N (%d) and ldc (%lld) must be multiples of 8", N,
+             static_cast<long long>(ep.ldc));
+  VB_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm_tc: lda/ldb must be multiples of 8 elements (16 B rows for TMA)");
+  VB_REQUIRE(aligned16(A) && aligned16(B) && aligned16(ep.C), "gemm_tc: operands must be 16-byte aligned");
+  VB_REQUIRE(!ep.accumulate || out_f32, "gemm_tc: atomic accumulation needs an fp32 output");
+  VB_REQUIRE(ep.residual == nullptr || out_f32, "gemm_tc: residual add needs an fp32 output");
+  constexpr int BN = 256;
+
+  CUtensorMap ta, tb;
+  if (a_major == 0) VB_PROPAGATE(make_tmap_bf16(&ta, A, M, K, lda, BK, BM));
+  else              VB_PROPAGATE(make_tmap_bf16(&ta, A, K, M, lda, 64, BK));
+  if (b_major == 0) VB_PROPAGATE(make_tmap_bf16(&tb, B, N, K, ldb, BK, BN));
+  else              VB_PROPAGATE(make_tmap_bf16(&tb, B, K, N, ldb, 64, BK));
+
+  TcParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.m_tiles = ceil_div(M, BM);
+  p.n_tiles = ceil_div(N, BN);
+  p.kb_total = ceil_div(K, BK);
+  int s = splits;
+  if (!ep.accumulate) s = 1;
+  if (s <= 0) {  // auto: aim for ~2 waves of work units, at least 4 k-blocks per split
+    const int tiles = p.m_tiles * p.n_tiles;
+    s = ceil_div(2 * num_sms(), tiles);
+    const int max_s = p.kb_total / 4 > 0 ? p.kb_total / 4 : 1;
+    if (s > max_s) s = max_s;
+    if (s < 1) s = 1;
+  }
+  p.kb_per_split = ceil_div(p.kb_total, s);
+  p.splits = ceil_div(p.kb_total, p.kb_per_split);
+
+  if (a_major == 0 && b_major == 0) {
+    return out_f32 ? launch_tc<0, 0, BN, float>(ta, tb, p, ep, stream) : launch_tc<0, 0, BN, bf16>(ta, tb, p, ep, stream);
+  } else if (a_major == 0 && b_major == 1) {
+    return out_f32 ? launch_tc<0, 1, BN, float>(ta, tb, p, ep, stream) : launch_tc<0, 1, BN, bf16>(ta, tb, p, ep, stream);
+  } else if (a_major == 1 && b_major == 1) {
+    return out_f32 ? launch_tc<1, 1, BN, float>(ta, tb, p, ep, stream) : launch_tc<1, 1, BN, bf16>(ta, tb, p, ep, stream);
+  }
+  set_error("gemm_tc: operand major combination a=%d b=%d not instantiated", a_major, b_major);
+  return kErrUnsupported;
+}
+
+}  // namespace vb
