@@ -72,6 +72,124 @@ typedef struct {
 
 int vitb200_gemm(const vitb200_gemm_args* args, void* stream);
 
+
+/* ------------------------------------------------------------------------------------------------------
+ * Single-op entry points (unit-tested one by one against the oracle / torch fp32).
+ * ---------------------------------------------------------------------------------------------------- */
+
+/* nn.LayerNorm(E), eps, affine (transformer.py:72-73; vit.py:72).  x fp32 [M,E] -> y [M,E] of y_dtype. */
+int vitb200_ln_fwd(const float* x, const float* gamma, const float* beta, void* y, int y_dtype, float* mean,
+                   float* rstd, int M, int E, float eps, void* stream);
+/* LayerNorm backward.  g (fp32 [M,E]) receives dx (add_to_g: g += dx).  dgamma/dbeta are ACCUMULATED.
+ * dyn (optional, dy_dtype) = cast(g_new * dropout factors) — the operand of the next backward GEMM. */
+int vitb200_ln_bwd(const void* dy, int dy_dtype, const float* x, const float* mean, const float* rstd,
+                   const float* gamma, float* g, int add_to_g, float* dgamma, float* dbeta, void* dyn,
+                   vitb200_dropout dyn_dropout, int M, int E, void* stream);
+
+/* Multi-head self-attention core (transformer.py:20-31,44-45): qkv [B*T, 3E] packed (q | k | v, head h at
+ * columns h*hs), logits * scale (the reference MULTIPLIES by sqrt(hs)), softmax, @v, heads concatenated into
+ * out [B*T, E]; lse [B,H,T] fp32 saved for backward. */
+int vitb200_attn_fwd(const void* qkv, void* out, float* lse, int dtype, int B, int T, int H, int hs, float scale,
+                     void* stream);
+/* dqkv [B*T,3E] from d_out; delta is fp32 scratch [B,H,T]. */
+int vitb200_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
+                     void* dqkv, int dtype, int B, int T, int H, int hs, float scale, void* stream);
+/* Debug/export: probs fp32 [B,H,T,T] = MultiHeadAttention.attention_probs (transformer.py:48); fp32 qkv only. */
+int vitb200_attn_probs(const float* qkv, float* probs, int B, int T, int H, int hs, float scale, void* stream);
+
+/* Patch gather of Conv2d(C,E,P,stride=P) (vit.py:20-30): x fp32 [B,C,Hi,Wi] -> A [B*N, Kpad] of out_dtype,
+ * row b*N + gy*(Wi/P) + gx, column c*P*P + ph*P + pw. */
+int vitb200_im2col(const float* x, void* A, int out_dtype, int B, int C, int Hi, int Wi, int P, int Kpad,
+                   void* stream);
+/* out[n] += sum_m in[m,n] (bias gradients). */
+int vitb200_colsum(const void* in, int in_dtype, int64_t ld, float* out, int M, int N, void* stream);
+/* nn.CrossEntropyLoss() mean + gradient (train.py:81,93).  dlogits may be NULL. */
+int vitb200_cross_entropy(const float* logits, const int64_t* labels, float* loss, float* dlogits, int B, int C,
+                          float grad_scale, void* stream);
+int vitb200_cast_f32_bf16(const float* in, void* out_bf16, int64_t n, void* stream);
+/* out = cast(g * dropout factors of (seed, stream)) — the masked gradient operand of a backward GEMM. */
+int vitb200_mask_cast(const float* g, void* out, int out_dtype, vitb200_dropout d, int64_t n, void* stream);
+/* keep[i] in {0,1}: the mask the fused dropout epilogues regenerate for (seed, stream). */
+int vitb200_dropout_mask(uint8_t* keep, int64_t n, vitb200_dropout d, void* stream);
+
+/* torch.optim.AdamW step (train.py:66,96) over a flat fp32 arena in ONE launch; shadow_bf16 (optional) receives
+ * the bf16 copy of the updated parameters; grad_scale folds the data-parallel mean. */
+typedef struct {
+  float lr, beta1, beta2, eps, weight_decay;
+  int step;          /* 1-based */
+  float grad_scale;
+} vitb200_adamw_hyper;
+int vitb200_adamw_flat(float* p, const float* g, float* m, float* v, void* shadow_bf16, int64_t n,
+                       vitb200_adamw_hyper h, void* stream);
+/* Multi-tensor form: device arrays of tensor addresses / sizes and a (block -> tensor, chunk of 65536) table. */
+int vitb200_adamw_multi(const uint64_t* p_ptrs, const uint64_t* g_ptrs, const uint64_t* m_ptrs,
+                        const uint64_t* v_ptrs, const uint64_t* shadow_ptrs, const int64_t* sizes,
+                        const int32_t* blk_tensor, const int32_t* blk_chunk, int n_blocks, vitb200_adamw_hyper h,
+                        void* stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Stage-level entry points: the model forward/backward is embed -> L x block -> head, each stage one call.
+ * `dtype` is the activation / GEMM-operand dtype (BF16: tcgen05 path; F32: fp32 parity path).  The residual
+ * stream, LayerNorm statistics, biases, LayerNorm parameters, the classifier head and ALL gradients are fp32.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct {
+  int B, T, E, H;       /* batch, tokens (= patches + 1), embedding, heads */
+  int C, P, Hi, Wi;     /* image channels, patch size, image height / width */
+  int classes;
+  int dtype;
+  float dropout_p;      /* 0 in eval mode; the reference hard-codes 0.2 when training (transformer.py:35,53) */
+  uint64_t seed;        /* dropout seed for this step */
+  float ln_eps;
+} vitb200_dims;
+
+/* PatchEmbedding (vit.py:9-43).  w_lp is the dtype copy of w_f32 ([E, C*P*P]); used when dtype == BF16 and
+ * C*P*P % 8 == 0, otherwise the fp32 kernel runs on w_f32. */
+typedef struct {
+  const float* w_f32; const void* w_lp; const float* bias;  /* Conv2d weight (E,C,P,P) and bias (E) */
+  const float* cls;   /* (B,1,E) one CLS vector per batch slot, appended LAST */
+  const float* pos;   /* (1,T,E) */
+} vitb200_embed_params;
+typedef struct { float *w, *bias, *cls, *pos; } vitb200_embed_grads;
+int64_t vitb200_embed_act_bytes(const vitb200_dims* d);
+int vitb200_embed_fwd(const vitb200_dims* d, const vitb200_embed_params* p, const float* images, float* x_out,
+                      void* acts, void* stream);
+/* g: fp32 [B,T,E] gradient of the embedding output; scratch >= vitb200_embed_act_bytes. Grads are ACCUMULATED. */
+int vitb200_embed_bwd(const vitb200_dims* d, const vitb200_embed_grads* gr, const float* g, const void* acts,
+                      void* scratch, void* stream);
+
+/* Block (transformer.py:66-79): x + MHA(LN1 x), then x + MLP(LN2 x).  Weights in `dtype`, rest fp32.
+ * w_qkv packs the 3H per-head matrices: row s*E + h*hs + j = heads[h].{query,key,value}[s].weight[j]. */
+typedef struct {
+  const float *ln1_w, *ln1_b, *ln2_w, *ln2_b;
+  const void* w_qkv;                      /* [3E, E] */
+  const void* w_proj; const float* b_proj; /* [E, E]  */
+  const void* w_fc1;  const float* b_fc1;  /* [4E, E] */
+  const void* w_fc2;  const float* b_fc2;  /* [E, 4E] */
+} vitb200_block_params;
+typedef struct {
+  float *ln1_w, *ln1_b, *ln2_w, *ln2_b, *w_qkv, *w_proj, *b_proj, *w_fc1, *b_fc1, *w_fc2, *b_fc2;
+} vitb200_block_grads;
+int64_t vitb200_block_act_bytes(const vitb200_dims* d);
+int64_t vitb200_block_scratch_bytes(const vitb200_dims* d);
+/* x_in, x_out fp32 [B*T, E] (may not alias).  acts: saved activations for backward (or scratch in eval). */
+int vitb200_block_fwd(const vitb200_dims* d, int layer, const vitb200_block_params* p, const float* x_in,
+                      float* x_out, void* acts, void* stream);
+/* g: fp32 [B*T,E], in: dL/dx_out, out: dL/dx_in.  dy_in: `dtype` [B*T,E] = cast(dL/dx_out * fc2 dropout mask of
+ * this layer).  dy_out (optional): same quantity for layer-1, produced for the next call.  Grads ACCUMULATED. */
+int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_params* p, const vitb200_block_grads* gr,
+                      const float* x_in, const void* acts, float* g, const void* dy_in, void* dy_out, void* scratch,
+                      void* stream);
+
+/* Classifier head on token 0 (vit.py:69-74,80): Linear(E,4E) -> GELU(erf) -> LayerNorm(4E) -> Linear(4E,cls); fp32. */
+typedef struct { const float *w1, *b1, *ln_w, *ln_b, *w3, *b3; } vitb200_head_params;
+typedef struct { float *w1, *b1, *ln_w, *ln_b, *w3, *b3; } vitb200_head_grads;
+int64_t vitb200_head_act_bytes(const vitb200_dims* d);
+int vitb200_head_fwd(const vitb200_dims* d, const vitb200_head_params* p, const float* x_last, float* logits,
+                     void* acts, void* stream);
+/* Produces g (fp32 [B*T,E], zero except token 0) and dy_out = cast(g * fc2-dropout mask of layer n_layers-1). */
+int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_params* p, const vitb200_head_grads* gr,
+                     const void* acts, const float* dlogits, float* g, void* dy_out, void* scratch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

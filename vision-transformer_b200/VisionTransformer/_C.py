@@ -43,6 +43,34 @@ class GemmArgs(ctypes.Structure):
     ]
 
 
+class AdamWHyper(ctypes.Structure):
+    _fields_ = [("lr", c_float), ("beta1", c_float), ("beta2", c_float), ("eps", c_float), ("weight_decay", c_float),
+                ("step", c_int), ("grad_scale", c_float)]
+
+
+class Dims(ctypes.Structure):
+    _fields_ = [("B", c_int), ("T", c_int), ("E", c_int), ("H", c_int),
+                ("C", c_int), ("P", c_int), ("Hi", c_int), ("Wi", c_int),
+                ("classes", c_int), ("dtype", c_int), ("dropout_p", c_float), ("seed", c_uint64),
+                ("ln_eps", c_float)]
+
+
+def _ptr_struct(name, fields):
+    return type(name, (ctypes.Structure,), {"_fields_": [(f, c_void_p) for f in fields]})
+
+
+EMBED_FIELDS_P = ("w_f32", "w_lp", "bias", "cls", "pos")
+EMBED_FIELDS_G = ("w", "bias", "cls", "pos")
+BLOCK_FIELDS_P = ("ln1_w", "ln1_b", "ln2_w", "ln2_b", "w_qkv", "w_proj", "b_proj", "w_fc1", "b_fc1", "w_fc2", "b_fc2")
+BLOCK_FIELDS_G = ("ln1_w", "ln1_b", "ln2_w", "ln2_b", "w_qkv", "w_proj", "b_proj", "w_fc1", "b_fc1", "w_fc2", "b_fc2")
+HEAD_FIELDS = ("w1", "b1", "ln_w", "ln_b", "w3", "b3")
+EmbedParams = _ptr_struct("EmbedParams", EMBED_FIELDS_P)
+EmbedGrads = _ptr_struct("EmbedGrads", EMBED_FIELDS_G)
+BlockParams = _ptr_struct("BlockParams", BLOCK_FIELDS_P)
+BlockGrads = _ptr_struct("BlockGrads", BLOCK_FIELDS_G)
+HeadParams = _ptr_struct("HeadParams", HEAD_FIELDS)
+HeadGrads = _ptr_struct("HeadGrads", HEAD_FIELDS)
+
 _lib = None
 
 
@@ -65,6 +93,51 @@ def _declare(L):
     L.vitb200_device_ok.restype = c_int
     L.vitb200_gemm.argtypes = [ctypes.POINTER(GemmArgs), c_void_p]
     L.vitb200_gemm.restype = c_int
+    P = ctypes.POINTER
+    sig = {
+        "vitb200_ln_fwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],
+        "vitb200_ln_bwd": [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                           c_void_p, Dropout, c_int, c_int, c_void_p],
+        "vitb200_attn_fwd": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p],
+        "vitb200_attn_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                             c_float, c_void_p],
+        "vitb200_attn_probs": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p],
+        "vitb200_im2col": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
+        "vitb200_colsum": [c_void_p, c_int, c_int64, c_void_p, c_int, c_int, c_void_p],
+        "vitb200_cross_entropy": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],
+        "vitb200_cast_f32_bf16": [c_void_p, c_void_p, c_int64, c_void_p],
+        "vitb200_dropout_mask": [c_void_p, c_int64, Dropout, c_void_p],
+        "vitb200_mask_cast": [c_void_p, c_void_p, c_int, Dropout, c_int64, c_void_p],
+        "vitb200_adamw_flat": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, AdamWHyper, c_void_p],
+        "vitb200_adamw_multi": [c_void_p] * 8 + [c_int, AdamWHyper, c_void_p],
+        "vitb200_embed_fwd": [P(Dims), P(EmbedParams), c_void_p, c_void_p, c_void_p, c_void_p],
+        "vitb200_embed_bwd": [P(Dims), P(EmbedGrads), c_void_p, c_void_p, c_void_p, c_void_p],
+        "vitb200_block_fwd": [P(Dims), c_int, P(BlockParams), c_void_p, c_void_p, c_void_p, c_void_p],
+        "vitb200_block_bwd": [P(Dims), c_int, P(BlockParams), P(BlockGrads), c_void_p, c_void_p, c_void_p, c_void_p,
+                              c_void_p, c_void_p, c_void_p],
+        "vitb200_head_fwd": [P(Dims), P(HeadParams), c_void_p, c_void_p, c_void_p, c_void_p],
+        "vitb200_head_bwd": [P(Dims), c_int, P(HeadParams), P(HeadGrads), c_void_p, c_void_p, c_void_p, c_void_p,
+                             c_void_p, c_void_p],
+    }
+    for name, args in sig.items():
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = c_int
+    for name in ("vitb200_embed_act_bytes", "vitb200_block_act_bytes", "vitb200_block_scratch_bytes",
+                 "vitb200_head_act_bytes"):
+        fn = getattr(L, name)
+        fn.argtypes = [P(Dims)]
+        fn.restype = c_int64
+
+
+EXPORTS = (
+    "vitb200_last_error", "vitb200_version", "vitb200_device_ok", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
+    "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
+    "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
+    "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_bwd",
+    "vitb200_block_act_bytes", "vitb200_block_scratch_bytes", "vitb200_block_fwd", "vitb200_block_bwd",
+    "vitb200_head_act_bytes", "vitb200_head_fwd", "vitb200_head_bwd",
+)
 
 
 def check(rc):

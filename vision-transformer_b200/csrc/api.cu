@@ -4,7 +4,7 @@
 
 #include "../../include/vitb200.h"
 #include "common.cuh"
-#include "gemm_epilogue.cuh"
+#include "kernels.h"
 
 namespace vb {
 
@@ -29,11 +29,6 @@ int num_sms() {
   }
   return cached[dev];
 }
-
-int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, int64_t lda, const void* B,
-                 int64_t ldb, bool out_f32, int splits, const GemmEpilogue& ep, cudaStream_t stream);
-int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int64_t lda, const float* B,
-             int64_t ldb, int splits, const GemmEpilogue& ep, cudaStream_t stream);
 
 }  // namespace vb
 

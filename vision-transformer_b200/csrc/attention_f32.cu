@@ -1,0 +1,221 @@
+// fp32 self-attention (forward, backward, probability export) on CUDA cores, any head size / sequence length.
+// This is the fp32-mode path (1e-4 parity gate, head_size 1 in the reference's default config) and the debug
+// path that materialises `attention_probs`; the bf16 training path uses the tensor-core kernel in
+// attention_bf16.cu.  Semantics follow reference transformer.py:20-31: logits = (q k^T) * scale with
+// scale = +sqrt(head_size) (MULTIPLIED), softmax over keys, out = wei v; heads are column slices h*hs of the
+// packed [M, 3E] qkv buffer (q | k | v), output written at column h*hs of [M, E] (the torch.cat at :45).
+#include "common.cuh"
+
+namespace vb {
+
+namespace {
+
+constexpr int AF_WARPS = 8;
+
+// One warp per query row.  smem per warp: q[hs] + p[T].
+template <bool WRITE_PROBS>
+__global__ void __launch_bounds__(AF_WARPS * 32)
+attn_f32_fwd_kernel(const float* __restrict__ qkv, float* __restrict__ out, float* __restrict__ lse,
+                    float* __restrict__ probs, int B, int T, int H, int hs, float scale) {
+  extern __shared__ float af_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int E = H * hs;
+  const int bh = blockIdx.x, b = bh / H, h = bh % H;
+  const int i = blockIdx.y * AF_WARPS + warp;
+  if (i >= T) return;
+  float* qs = af_smem + static_cast<size_t>(warp) * (hs + T);
+  float* ps = qs + hs;
+  const int64_t row3 = 3 * static_cast<int64_t>(E);
+  const float* qrow = qkv + (static_cast<int64_t>(b) * T + i) * row3 + h * hs;
+  const float* kbase = qkv + static_cast<int64_t>(b) * T * row3 + E + h * hs;
+  const float* vbase = kbase + E;
+  for (int d = lane; d < hs; d += 32) qs[d] = qrow[d];
+  __syncwarp();
+  float mx = -INFINITY;
+  for (int j = lane; j < T; j += 32) {
+    const float* kr = kbase + j * row3;
+    float s = 0.f;
+    for (int d = 0; d < hs; ++d) s = fmaf(qs[d], kr[d], s);
+    s *= scale;
+    ps[j] = s;
+    mx = fmaxf(mx, s);
+  }
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int j = lane; j < T; j += 32) {
+    const float e = expf(ps[j] - mx);
+    ps[j] = e;
+    sum += e;
+  }
+  sum = warp_sum(sum);
+  const float inv = 1.f / sum;
+  __syncwarp();
+  if (WRITE_PROBS) {
+    float* pr = probs + (static_cast<int64_t>(bh) * T + i) * T;
+    for (int j = lane; j < T; j += 32) pr[j] = ps[j] * inv;
+  } else {
+    if (lane == 0 && lse != nullptr) lse[static_cast<int64_t>(bh) * T + i] = mx + logf(sum);
+    float* orow = out + (static_cast<int64_t>(b) * T + i) * E + h * hs;
+    for (int d = lane; d < hs; d += 32) {
+      float acc = 0.f;
+      for (int j = 0; j < T; ++j) acc = fmaf(ps[j], vbase[j * row3 + d], acc);
+      orow[d] = acc * inv;
+    }
+  }
+}
+
+// delta[bh, i] = sum_d dO[i, d] * O[i, d]
+template <typename T_>
+__global__ void attn_delta_kernel(const T_* __restrict__ o, const T_* __restrict__ d_o, float* __restrict__ delta,
+                                  int B, int T, int H, int hs) {
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int total = B * H * T;
+  if (warp_global >= total) return;
+  const int i = warp_global % T, bh = warp_global / T, b = bh / H, h = bh % H;
+  const int64_t off = (static_cast<int64_t>(b) * T + i) * (H * hs) + h * hs;
+  float s = 0.f;
+  for (int d = lane; d < hs; d += 32) s = fmaf(to_f32(o[off + d]), to_f32(d_o[off + d]), s);
+  s = warp_sum(s);
+  if (lane == 0) delta[static_cast<int64_t>(bh) * T + i] = s;
+}
+
+// dQ: one warp per query row i.  ds_ij = p_ij (dP_ij - delta_i) * scale ; dq_i = sum_j ds_ij k_j
+__global__ void __launch_bounds__(AF_WARPS * 32)
+attn_f32_bwd_dq_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, const float* __restrict__ lse,
+                       const float* __restrict__ delta, float* __restrict__ dqkv, int B, int T, int H, int hs,
+                       float scale) {
+  extern __shared__ float af_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int E = H * hs;
+  const int bh = blockIdx.x, b = bh / H, h = bh % H;
+  const int i = blockIdx.y * AF_WARPS + warp;
+  if (i >= T) return;
+  float* qs = af_smem + static_cast<size_t>(warp) * (2 * hs + T);
+  float* dos = qs + hs;
+  float* ds = dos + hs;
+  const int64_t row3 = 3 * static_cast<int64_t>(E);
+  const int64_t tok = static_cast<int64_t>(b) * T + i;
+  const float* kbase = qkv + static_cast<int64_t>(b) * T * row3 + E + h * hs;
+  const float* vbase = kbase + E;
+  for (int d = lane; d < hs; d += 32) {
+    qs[d] = qkv[tok * row3 + h * hs + d];
+    dos[d] = d_o[tok * E + h * hs + d];
+  }
+  __syncwarp();
+  const float l = lse[static_cast<int64_t>(bh) * T + i], dl = delta[static_cast<int64_t>(bh) * T + i];
+  for (int j = lane; j < T; j += 32) {
+    const float* kr = kbase + j * row3;
+    const float* vr = vbase + j * row3;
+    float s = 0.f, dp = 0.f;
+    for (int d = 0; d < hs; ++d) { s = fmaf(qs[d], kr[d], s); dp = fmaf(dos[d], vr[d], dp); }
+    const float p = expf(s * scale - l);
+    ds[j] = p * (dp - dl) * scale;
+  }
+  __syncwarp();
+  for (int d = lane; d < hs; d += 32) {
+    float acc = 0.f;
+    for (int j = 0; j < T; ++j) acc = fmaf(ds[j], kbase[j * row3 + d], acc);
+    dqkv[tok * row3 + h * hs + d] = acc;
+  }
+}
+
+// dK, dV: one warp per key row j.  dv_j = sum_i p_ij dO_i ; dk_j = sum_i ds_ij q_i
+__global__ void __launch_bounds__(AF_WARPS * 32)
+attn_f32_bwd_dkv_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, const float* __restrict__ lse,
+                        const float* __restrict__ delta, float* __restrict__ dqkv, int B, int T, int H, int hs,
+                        float scale) {
+  extern __shared__ float af_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int E = H * hs;
+  const int bh = blockIdx.x, b = bh / H, h = bh % H;
+  const int j = blockIdx.y * AF_WARPS + warp;
+  if (j >= T) return;
+  float* ks = af_smem + static_cast<size_t>(warp) * (2 * hs + 2 * T);
+  float* vs = ks + hs;
+  float* ps = vs + hs;
+  float* ds = ps + T;
+  const int64_t row3 = 3 * static_cast<int64_t>(E);
+  const int64_t tok = static_cast<int64_t>(b) * T + j;
+  const float* qbase = qkv + static_cast<int64_t>(b) * T * row3 + h * hs;
+  const float* dobase = d_o + static_cast<int64_t>(b) * T * E + h * hs;
+  for (int d = lane; d < hs; d += 32) {
+    ks[d] = qkv[tok * row3 + E + h * hs + d];
+    vs[d] = qkv[tok * row3 + 2 * E + h * hs + d];
+  }
+  __syncwarp();
+  for (int i = lane; i < T; i += 32) {
+    const float* qr = qbase + i * row3;
+    const float* dor = dobase + static_cast<int64_t>(i) * E;
+    float s = 0.f, dp = 0.f;
+    for (int d = 0; d < hs; ++d) { s = fmaf(qr[d], ks[d], s); dp = fmaf(dor[d], vs[d], dp); }
+    const float p = expf(s * scale - lse[static_cast<int64_t>(bh) * T + i]);
+    ps[i] = p;
+    ds[i] = p * (dp - delta[static_cast<int64_t>(bh) * T + i]) * scale;
+  }
+  __syncwarp();
+  for (int d = lane; d < hs; d += 32) {
+    float dk = 0.f, dv = 0.f;
+    for (int i = 0; i < T; ++i) {
+      dk = fmaf(ds[i], qbase[i * row3 + d], dk);
+      dv = fmaf(ps[i], dobase[static_cast<int64_t>(i) * E + d], dv);
+    }
+    dqkv[tok * row3 + E + h * hs + d] = dk;
+    dqkv[tok * row3 + 2 * E + h * hs + d] = dv;
+  }
+}
+
+template <typename K>
+int set_smem(K kern, size_t smem) {
+  VB_REQUIRE(smem <= 220 * 1024, "attention_f32: sequence too long for the fp32 path (%zu B smem)", smem);
+  if (smem > 48 * 1024) VB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  return kOk;
+}
+
+}  // namespace
+
+int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B, int T, int H, int hs,
+               cudaStream_t stream) {
+  const int total_warps = B * H * T;
+  const int threads = 256;
+  const int grid = ceil_div(total_warps * 32, threads);
+  if (is_bf16) attn_delta_kernel<bf16><<<grid, threads, 0, stream>>>(static_cast<const bf16*>(o), static_cast<const bf16*>(d_o), delta, B, T, H, hs);
+  else attn_delta_kernel<float><<<grid, threads, 0, stream>>>(static_cast<const float*>(o), static_cast<const float*>(d_o), delta, B, T, H, hs);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int attn_f32_forward(const float* qkv, float* out, float* lse, int B, int T, int H, int hs, float scale,
+                     cudaStream_t stream) {
+  const size_t smem = static_cast<size_t>(AF_WARPS) * (hs + T) * sizeof(float);
+  VB_PROPAGATE(set_smem(attn_f32_fwd_kernel<false>, smem));
+  dim3 grid(B * H, ceil_div(T, AF_WARPS));
+  attn_f32_fwd_kernel<false><<<grid, AF_WARPS * 32, smem, stream>>>(qkv, out, lse, nullptr, B, T, H, hs, scale);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int attn_f32_probs(const float* qkv, float* probs, int B, int T, int H, int hs, float scale, cudaStream_t stream) {
+  const size_t smem = static_cast<size_t>(AF_WARPS) * (hs + T) * sizeof(float);
+  VB_PROPAGATE(set_smem(attn_f32_fwd_kernel<true>, smem));
+  dim3 grid(B * H, ceil_div(T, AF_WARPS));
+  attn_f32_fwd_kernel<true><<<grid, AF_WARPS * 32, smem, stream>>>(qkv, nullptr, nullptr, probs, B, T, H, hs, scale);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int attn_f32_backward(const float* qkv, const float* out, const float* d_o, const float* lse, float* delta,
+                      float* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t stream) {
+  VB_PROPAGATE(attn_delta(out, d_o, false, delta, B, T, H, hs, stream));
+  dim3 grid(B * H, ceil_div(T, AF_WARPS));
+  const size_t smem_q = static_cast<size_t>(AF_WARPS) * (2 * hs + T) * sizeof(float);
+  VB_PROPAGATE(set_smem(attn_f32_bwd_dq_kernel, smem_q));
+  attn_f32_bwd_dq_kernel<<<grid, AF_WARPS * 32, smem_q, stream>>>(qkv, d_o, lse, delta, dqkv, B, T, H, hs, scale);
+  VB_CHECK_LAUNCH();
+  const size_t smem_kv = static_cast<size_t>(AF_WARPS) * (2 * hs + 2 * T) * sizeof(float);
+  VB_PROPAGATE(set_smem(attn_f32_bwd_dkv_kernel, smem_kv));
+  attn_f32_bwd_dkv_kernel<<<grid, AF_WARPS * 32, smem_kv, stream>>>(qkv, d_o, lse, delta, dqkv, B, T, H, hs, scale);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+}  // namespace vb

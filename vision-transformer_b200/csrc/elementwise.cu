@@ -1,0 +1,397 @@
+// Bandwidth kernels around the contractions: patch im2col, CLS rows, embedding-gradient reductions, bias-gradient
+// column sums, classifier-head pointwise ops, cross-entropy, casts and the dropout-mask export used by tests.
+#include "common.cuh"
+
+namespace vb {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------- im2col
+// x fp32 [B,C,Hi,Wi] -> A [B*N, Kpad], row b*N + gy*gw + gx, column c*P*P + ph*P + pw (zero padded to Kpad).
+// Replaces the gather implicit in Conv2d(C,E,P,stride=P) + Flatten + permute (reference vit.py:20-30,40).
+template <typename OutT, bool VEC4>
+__global__ void im2col_kernel(const float* __restrict__ x, OutT* __restrict__ A, int B, int C, int Hi, int Wi, int P,
+                              int gh, int gw, int K, int Kpad) {
+  const int kq = VEC4 ? Kpad / 4 : Kpad;
+  const int64_t total = static_cast<int64_t>(B) * gh * gw * kq;
+  for (int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int kk = static_cast<int>(idx % kq);
+    const int64_t row = idx / kq;
+    const int gx = static_cast<int>(row % gw);
+    const int gy = static_cast<int>((row / gw) % gh);
+    const int b = static_cast<int>(row / (static_cast<int64_t>(gw) * gh));
+    if (VEC4) {
+      const int k = kk * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (k < K) {
+        const int c = k / (P * P), rem = k - c * P * P, ph = rem / P, pw = rem - ph * P;
+        v = __ldg(reinterpret_cast<const float4*>(
+            x + ((static_cast<int64_t>(b) * C + c) * Hi + gy * P + ph) * Wi + gx * P + pw));
+      }
+      if constexpr (sizeof(OutT) == 2) {
+        uint2 o;
+        o.x = pack_bf16x2(v.x, v.y);
+        o.y = pack_bf16x2(v.z, v.w);
+        *reinterpret_cast<uint2*>(A + row * Kpad + k) = o;
+      } else {
+        *reinterpret_cast<float4*>(A + row * Kpad + k) = v;
+      }
+    } else {
+      float v = 0.f;
+      if (kk < K) {
+        const int c = kk / (P * P), rem = kk - c * P * P, ph = rem / P, pw = rem - ph * P;
+        v = __ldg(x + ((static_cast<int64_t>(b) * C + c) * Hi + gy * P + ph) * Wi + gx * P + pw);
+      }
+      A[row * Kpad + kk] = from_f32<OutT>(v);
+    }
+  }
+}
+
+// out[b, N, :] = cls[b, :] + pos[N, :]   (CLS appended LAST: reference vit.py:41-42)
+__global__ void cls_rows_kernel(const float* __restrict__ cls, const float* __restrict__ pos, float* __restrict__ out,
+                                int B, int T, int E) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * E) return;
+  const int b = idx / E, e = idx - b * E;
+  out[(static_cast<int64_t>(b) * T + (T - 1)) * E + e] = cls[idx] + pos[static_cast<int64_t>(T - 1) * E + e];
+}
+
+// Embedding backward reductions over the batch: g fp32 [B,T,E] ->
+//   dpos[t,e] += sum_b g[b,t,e];  dcls[b,e] += g[b,T-1,e];  dY[b*N+t, e] = cast(g[b,t,e]) for t < N.
+template <typename OutT>
+__global__ void embed_bwd_kernel(const float* __restrict__ g, float* __restrict__ dpos, float* __restrict__ dcls,
+                                 OutT* __restrict__ dY, int B, int T, int E) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= T * E) return;
+  const int t = idx / E, e = idx - t * E;
+  const int N = T - 1;
+  float s = 0.f;
+  for (int b = 0; b < B; ++b) {
+    const float v = g[(static_cast<int64_t>(b) * T + t) * E + e];
+    s += v;
+    if (t < N) dY[(static_cast<int64_t>(b) * N + t) * E + e] = from_f32<OutT>(v);
+    else dcls[static_cast<int64_t>(b) * E + e] += v;
+  }
+  dpos[idx] += s;
+}
+
+// out[n] += sum_m in[m, n]   (bias gradients).  blockDim = (32, 8); each x-thread owns one column.
+template <typename InT>
+__global__ void colsum_kernel(const InT* __restrict__ in, int64_t ld, float* __restrict__ out, int M, int N) {
+  __shared__ float red[8][33];
+  const int n = blockIdx.x * 32 + threadIdx.x;
+  float s = 0.f;
+  if (n < N)
+    for (int m = blockIdx.y * 8 + threadIdx.y; m < M; m += gridDim.y * 8) s += to_f32(in[static_cast<int64_t>(m) * ld + n]);
+  red[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && n < N) {
+    float tsum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) tsum += red[j][threadIdx.x];
+    atomicAdd(out + n, tsum);
+  }
+}
+
+// bf16 variant with 16-byte loads: each x-thread owns 8 consecutive columns (N % 8 == 0, ld % 8 == 0).
+__global__ void colsum_bf16x8_kernel(const bf16* __restrict__ in, int64_t ld, float* __restrict__ out, int M, int N) {
+  __shared__ float red[8][32][9];
+  const int n0 = (blockIdx.x * 32 + threadIdx.x) * 8;
+  float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (n0 < N) {
+    for (int m = blockIdx.y * 8 + threadIdx.y; m < M; m += gridDim.y * 8) {
+      const uint4 raw = __ldcs(reinterpret_cast<const uint4*>(in + static_cast<int64_t>(m) * ld + n0));
+      const bf16* h = reinterpret_cast<const bf16*>(&raw);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s[j] += __bfloat162float(h[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x][j] = s[j];
+  __syncthreads();
+  if (threadIdx.y == 0 && n0 < N) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float tsum = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) tsum += red[r][threadIdx.x][j];
+      atomicAdd(out + n0 + j, tsum);
+    }
+  }
+}
+
+// x0[b, :] = x[b, 0, :]  (the classifier reads token 0, reference vit.py:80)
+__global__ void gather_row0_kernel(const float* __restrict__ x, float* __restrict__ x0, int B, int T, int E) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * E) return;
+  const int b = idx / E, e = idx - b * E;
+  x0[idx] = x[static_cast<int64_t>(b) * T * E + e];
+}
+
+// g[b,0,:] = dx0[b,:], g[b,t>0,:] = 0 ; dyn = cast(g * dropout factors)   (top of the encoder backward)
+template <typename OutT>
+__global__ void head_scatter_kernel(const float* __restrict__ dx0, float* __restrict__ g, OutT* __restrict__ dyn,
+                                    const Dropout drop, int B, int T, int E) {
+  const int64_t total4 = static_cast<int64_t>(B) * T * E / 4;
+  for (int64_t i4 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i4 < total4;
+       i4 += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t lin = i4 * 4;
+    const int e = static_cast<int>(lin % E);
+    const int64_t row = lin / E;
+    const int t = static_cast<int>(row % T);
+    const int b = static_cast<int>(row / T);
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t == 0) v = *reinterpret_cast<const float4*>(dx0 + static_cast<int64_t>(b) * E + e);
+    *reinterpret_cast<float4*>(g + lin) = v;
+    if (dyn != nullptr) {
+      float o[4] = {v.x, v.y, v.z, v.w};
+      if (drop.p > 0.f && t == 0) {
+        float f[4];
+        dropout_factors4(drop, static_cast<uint64_t>(i4), f);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) o[j] *= f[j];
+      }
+      if constexpr (sizeof(OutT) == 2) {
+        uint2 pk;
+        pk.x = pack_bf16x2(o[0], o[1]);
+        pk.y = pack_bf16x2(o[2], o[3]);
+        *reinterpret_cast<uint2*>(dyn + lin) = pk;
+      } else {
+        *reinterpret_cast<float4*>(dyn + lin) = make_float4(o[0], o[1], o[2], o[3]);
+      }
+    }
+  }
+}
+template <typename OutT>
+__global__ void head_scatter_scalar_kernel(const float* __restrict__ dx0, float* __restrict__ g, OutT* __restrict__ dyn,
+                                           const Dropout drop, int B, int T, int E) {
+  const int64_t total = static_cast<int64_t>(B) * T * E;
+  for (int64_t lin = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; lin < total;
+       lin += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int e = static_cast<int>(lin % E);
+    const int64_t row = lin / E;
+    const int t = static_cast<int>(row % T);
+    const int b = static_cast<int>(row / T);
+    float v = t == 0 ? dx0[static_cast<int64_t>(b) * E + e] : 0.f;
+    g[lin] = v;
+    if (dyn != nullptr) {
+      if (drop.p > 0.f) {
+        const Philox4 r = philox4x32_10(drop.seed, drop.stream, static_cast<uint64_t>(lin) >> 2);
+        const uint32_t w = (lin & 3) == 0 ? r.x : (lin & 3) == 1 ? r.y : (lin & 3) == 2 ? r.z : r.w;
+        v *= w < drop.thresh ? drop.scale : 0.f;
+      }
+      dyn[lin] = from_f32<OutT>(v);
+    }
+  }
+}
+
+// exact-erf GELU (nn.GELU() default, reference vit.py:71) and its derivative
+__global__ void gelu_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n) {
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const float v = x[i];
+    y[i] = 0.5f * v * (1.f + erff(v * 0.70710678118654752f));
+  }
+}
+__global__ void gelu_bwd_kernel(const float* __restrict__ x, float* __restrict__ dy_inout, int64_t n) {
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const float v = x[i];
+    const float cdf = 0.5f * (1.f + erff(v * 0.70710678118654752f));
+    const float pdf = 0.3989422804014327f * expf(-0.5f * v * v);
+    dy_inout[i] *= cdf + v * pdf;
+  }
+}
+
+// Mean cross-entropy over B rows + its gradient (reference train.py:81,93).  One CTA; one warp per row.
+__global__ void ce_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ loss,
+                          float* __restrict__ dlogits, int B, int C, float grad_scale) {
+  __shared__ float warp_loss[32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  float acc = 0.f;
+  for (int b = warp; b < B; b += nwarps) {
+    const float* row = logits + static_cast<int64_t>(b) * C;
+    float mx = -INFINITY;
+    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, row[c]);
+    mx = warp_max(mx);
+    float s = 0.f;
+    for (int c = lane; c < C; c += 32) s += expf(row[c] - mx);
+    s = warp_sum(s);
+    const int y = static_cast<int>(labels[b]);
+    const float lse = mx + logf(s);
+    if (lane == 0) acc += lse - row[y];
+    if (dlogits != nullptr)
+      for (int c = lane; c < C; c += 32)
+        dlogits[static_cast<int64_t>(b) * C + c] = (expf(row[c] - lse) - (c == y ? 1.f : 0.f)) * grad_scale;
+  }
+  if (lane == 0) warp_loss[warp] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < nwarps; ++w) t += warp_loss[w];
+    *loss = t / static_cast<float>(B);
+  }
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, int64_t n) {
+  const int64_t n4 = n / 4;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const float4 v = *reinterpret_cast<const float4*>(in + i * 4);
+    uint2 o;
+    o.x = pack_bf16x2(v.x, v.y);
+    o.y = pack_bf16x2(v.z, v.w);
+    *reinterpret_cast<uint2*>(out + i * 4) = o;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (int64_t i = n4 * 4; i < n; ++i) out[i] = __float2bfloat16_rn(in[i]);
+}
+
+// keep[i] = 1 if element i of the (seed, stream) dropout stream is kept.  Test/debug export of the mask that the
+// fused epilogues regenerate on the fly.
+__global__ void dropout_mask_kernel(uint8_t* __restrict__ keep, int64_t n, const Dropout drop) {
+  for (int64_t i4 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i4 * 4 < n;
+       i4 += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const Philox4 r = philox4x32_10(drop.seed, drop.stream, static_cast<uint64_t>(i4));
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+    for (int j = 0; j < 4 && i4 * 4 + j < n; ++j) keep[i4 * 4 + j] = w[j] < drop.thresh ? 1 : 0;
+  }
+}
+
+// out = cast(g * dropout factors): the masked low-precision gradient a backward GEMM consumes, for call sites where
+// no LayerNorm-backward kernel is upstream to fuse it into (stand-alone Block / FeedForward / MultiHeadAttention).
+template <typename OutT>
+__global__ void mask_cast_kernel(const float* __restrict__ g, OutT* __restrict__ out, const Dropout drop, int64_t n) {
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    float v = g[i];
+    if (drop.p > 0.f) {
+      const Philox4 r = philox4x32_10(drop.seed, drop.stream, static_cast<uint64_t>(i) >> 2);
+      const uint32_t w = (i & 3) == 0 ? r.x : (i & 3) == 1 ? r.y : (i & 3) == 2 ? r.z : r.w;
+      v *= w < drop.thresh ? drop.scale : 0.f;
+    }
+    out[i] = from_f32<OutT>(v);
+  }
+}
+
+inline int grid_for(int64_t work_items, int threads) {
+  const int64_t blocks = ceil_div<int64_t>(work_items, threads);
+  const int64_t cap = static_cast<int64_t>(num_sms()) * 16;
+  return static_cast<int>(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+}  // namespace
+
+int im2col(const float* x, void* A, bool out_bf16, int B, int C, int Hi, int Wi, int P, int Kpad, cudaStream_t s) {
+  const int gh = Hi / P, gw = Wi / P, K = C * P * P;
+  VB_REQUIRE(gh > 0 && gw > 0 && Kpad >= K, "im2col: bad geometry");
+  const bool vec = (P % 4 == 0) && (Wi % 4 == 0) && (Kpad % 4 == 0) && aligned16(x) && aligned16(A);
+  const int64_t items = static_cast<int64_t>(B) * gh * gw * (vec ? Kpad / 4 : Kpad);
+  const int grid = grid_for(items, 256);
+  if (out_bf16) {
+    if (vec) im2col_kernel<bf16, true><<<grid, 256, 0, s>>>(x, static_cast<bf16*>(A), B, C, Hi, Wi, P, gh, gw, K, Kpad);
+    else im2col_kernel<bf16, false><<<grid, 256, 0, s>>>(x, static_cast<bf16*>(A), B, C, Hi, Wi, P, gh, gw, K, Kpad);
+  } else {
+    if (vec) im2col_kernel<float, true><<<grid, 256, 0, s>>>(x, static_cast<float*>(A), B, C, Hi, Wi, P, gh, gw, K, Kpad);
+    else im2col_kernel<float, false><<<grid, 256, 0, s>>>(x, static_cast<float*>(A), B, C, Hi, Wi, P, gh, gw, K, Kpad);
+  }
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int cls_rows(const float* cls, const float* pos, float* out, int B, int T, int E, cudaStream_t s) {
+  cls_rows_kernel<<<ceil_div(B * E, 256), 256, 0, s>>>(cls, pos, out, B, T, E);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int embed_bwd_reduce(const float* g, float* dpos, float* dcls, void* dY, bool dy_bf16, int B, int T, int E,
+                     cudaStream_t s) {
+  const int grid = ceil_div(T * E, 128);
+  if (dy_bf16) embed_bwd_kernel<bf16><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<bf16*>(dY), B, T, E);
+  else embed_bwd_kernel<float><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<float*>(dY), B, T, E);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int colsum(const void* in, bool in_bf16, int64_t ld, float* out, int M, int N, cudaStream_t s) {
+  dim3 block(32, 8);
+  if (in_bf16 && N % 8 == 0 && ld % 8 == 0 && aligned16(in)) {
+    const int gx = ceil_div(N, 256);
+    int gy = ceil_div(num_sms() * 4, gx);
+    if (gy > ceil_div(M, 8)) gy = ceil_div(M, 8);
+    colsum_bf16x8_kernel<<<dim3(gx, gy), block, 0, s>>>(static_cast<const bf16*>(in), ld, out, M, N);
+  } else {
+    const int gx = ceil_div(N, 32);
+    int gy = ceil_div(num_sms() * 4, gx);
+    if (gy > ceil_div(M, 8)) gy = ceil_div(M, 8);
+    if (gy < 1) gy = 1;
+    if (in_bf16) colsum_kernel<bf16><<<dim3(gx, gy), block, 0, s>>>(static_cast<const bf16*>(in), ld, out, M, N);
+    else colsum_kernel<float><<<dim3(gx, gy), block, 0, s>>>(static_cast<const float*>(in), ld, out, M, N);
+  }
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int gather_row0(const float* x, float* x0, int B, int T, int E, cudaStream_t s) {
+  gather_row0_kernel<<<ceil_div(B * E, 256), 256, 0, s>>>(x, x0, B, T, E);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int head_scatter(const float* dx0, float* g, void* dyn, bool dyn_bf16, const Dropout& drop, int B, int T, int E,
+                 cudaStream_t s) {
+  const int64_t total = static_cast<int64_t>(B) * T * E;
+  if (E % 4 == 0) {
+    const int grid = grid_for(total / 4, 256);
+    if (dyn_bf16) head_scatter_kernel<bf16><<<grid, 256, 0, s>>>(dx0, g, static_cast<bf16*>(dyn), drop, B, T, E);
+    else head_scatter_kernel<float><<<grid, 256, 0, s>>>(dx0, g, static_cast<float*>(dyn), drop, B, T, E);
+  } else {
+    const int grid = grid_for(total, 256);
+    if (dyn_bf16) head_scatter_scalar_kernel<bf16><<<grid, 256, 0, s>>>(dx0, g, static_cast<bf16*>(dyn), drop, B, T, E);
+    else head_scatter_scalar_kernel<float><<<grid, 256, 0, s>>>(dx0, g, static_cast<float*>(dyn), drop, B, T, E);
+  }
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int gelu_forward(const float* x, float* y, int64_t n, cudaStream_t s) {
+  gelu_fwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, y, n);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+int gelu_backward(const float* x, float* dy_inout, int64_t n, cudaStream_t s) {
+  gelu_bwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, dy_inout, n);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int cross_entropy(const float* logits, const int64_t* labels, float* loss, float* dlogits, int B, int C,
+                  float grad_scale, cudaStream_t s) {
+  ce_kernel<<<1, 1024, 0, s>>>(logits, labels, loss, dlogits, B, C, grad_scale);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int cast_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t s) {
+  VB_REQUIRE(aligned16(in) && (reinterpret_cast<uintptr_t>(out) & 7u) == 0, "cast: unaligned buffers");
+  cast_f32_bf16_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, s>>>(in, out, n);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int mask_cast(const float* g, void* out, bool out_bf16, const Dropout& drop, int64_t n, cudaStream_t s) {
+  if (out_bf16) mask_cast_kernel<bf16><<<grid_for(n, 256), 256, 0, s>>>(g, static_cast<bf16*>(out), drop, n);
+  else mask_cast_kernel<float><<<grid_for(n, 256), 256, 0, s>>>(g, static_cast<float*>(out), drop, n);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int dropout_mask(uint8_t* keep, int64_t n, const Dropout& drop, cudaStream_t s) {
+  dropout_mask_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, s>>>(keep, n, drop);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+}  // namespace vb

@@ -1,0 +1,65 @@
+// Internal (C++) entry points of the individual kernels; the C ABI in include/vitb200.h wraps these.
+#pragma once
+#include "common.cuh"
+#include "gemm_epilogue.cuh"
+
+namespace vb {
+
+struct AdamWHyper {
+  float lr, beta1, beta2, eps, weight_decay;
+  float bias_corr1;      // 1 - beta1^step
+  float inv_sqrt_bc2;    // 1 / sqrt(1 - beta2^step)
+  float grad_scale;      // multiply gradients (1/world_size for the data-parallel mean)
+};
+
+// contractions
+int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, int64_t lda, const void* B,
+                 int64_t ldb, bool out_f32, int splits, const GemmEpilogue& ep, cudaStream_t stream);
+int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int64_t lda, const float* B,
+             int64_t ldb, int splits, const GemmEpilogue& ep, cudaStream_t stream);
+
+// layer norm
+int ln_forward(const float* x, const float* gamma, const float* beta, void* y, bool y_bf16, float* mean,
+               float* rstd, int M, int E, float eps, cudaStream_t stream);
+int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean, const float* rstd,
+                const float* gamma, float* g, int add_to_g, float* dgamma, float* dbeta, void* dyn,
+                const Dropout& drop, int M, int E, cudaStream_t stream);
+
+// attention
+int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B, int T, int H, int hs,
+               cudaStream_t stream);
+int attn_f32_forward(const float* qkv, float* out, float* lse, int B, int T, int H, int hs, float scale,
+                     cudaStream_t stream);
+int attn_f32_probs(const float* qkv, float* probs, int B, int T, int H, int hs, float scale, cudaStream_t stream);
+int attn_f32_backward(const float* qkv, const float* out, const float* d_o, const float* lse, float* delta,
+                      float* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t stream);
+int attn_bf16_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
+                      cudaStream_t stream);
+int attn_bf16_backward(const bf16* qkv, const bf16* out, const bf16* d_o, const float* lse, float* delta, bf16* dqkv,
+                       int B, int T, int H, int hs, float scale, cudaStream_t stream);
+
+// bandwidth kernels
+int im2col(const float* x, void* A, bool out_bf16, int B, int C, int Hi, int Wi, int P, int Kpad, cudaStream_t s);
+int cls_rows(const float* cls, const float* pos, float* out, int B, int T, int E, cudaStream_t s);
+int embed_bwd_reduce(const float* g, float* dpos, float* dcls, void* dY, bool dy_bf16, int B, int T, int E,
+                     cudaStream_t s);
+int colsum(const void* in, bool in_bf16, int64_t ld, float* out, int M, int N, cudaStream_t s);
+int gather_row0(const float* x, float* x0, int B, int T, int E, cudaStream_t s);
+int head_scatter(const float* dx0, float* g, void* dyn, bool dyn_bf16, const Dropout& drop, int B, int T, int E,
+                 cudaStream_t s);
+int gelu_forward(const float* x, float* y, int64_t n, cudaStream_t s);
+int gelu_backward(const float* x, float* dy_inout, int64_t n, cudaStream_t s);
+int cross_entropy(const float* logits, const int64_t* labels, float* loss, float* dlogits, int B, int C,
+                  float grad_scale, cudaStream_t s);
+int cast_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t s);
+int mask_cast(const float* g, void* out, bool out_bf16, const Dropout& drop, int64_t n, cudaStream_t s);
+int dropout_mask(uint8_t* keep, int64_t n, const Dropout& drop, cudaStream_t s);
+
+// optimiser
+int adamw_flat(float* p, const float* g, float* m, float* v, bf16* shadow, int64_t n, const AdamWHyper& h,
+               cudaStream_t s);
+int adamw_multi(const uint64_t* p_ptrs, const uint64_t* g_ptrs, const uint64_t* m_ptrs, const uint64_t* v_ptrs,
+                const uint64_t* s_ptrs, const int64_t* sizes, const int32_t* blk_tensor, const int32_t* blk_chunk,
+                int n_blocks, const AdamWHyper& h, cudaStream_t s);
+
+}  // namespace vb
