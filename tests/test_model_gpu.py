@@ -1,0 +1,234 @@
+"""GPU: the drop-in modules (through the C ABI) against the oracle restatement and the committed reference fixtures.
+
+Tolerances (BASELINE.json north_star): fp32 rel-err <= 1e-4 on logits and every gradient; bf16 logits rel <= 2e-2 and
+gradient cosine >= 0.999; patch indexing / position-embedding layout bit-exact.  Dropout is off (eval(), grad enabled)
+for parity, as a fused kernel cannot replay ATen's Philox stream; dropout statistics are tested apart.
+"""
+import math
+
+import pytest
+import torch
+
+from conftest import cosine, load_golden, rel_err
+from oracle import ref_vit
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _build(c, precision=torch.float32):
+    from VisionTransformer import config, vit
+    cfg = config.ViTConfig(c["input_channels"], c["num_classes"], c["num_patches"], c["embedding_size"],
+                           c["patch_size"], c["num_heads"], c["num_blocks"], DEV, c["batch_size"], precision=precision)
+    return vit.VisionTransformer(cfg).to(DEV)
+
+
+def _grads_by_ref_key(model):
+    """Gradients unpacked to the reference's state_dict keys (qkv_weight -> heads.h.{key,query,value}.weight)."""
+    out = {}
+    for name, p in model.named_parameters():
+        if name.endswith("multi_head.qkv_weight"):
+            mh = model.get_submodule(name.rsplit(".", 1)[0])
+            Eh, hs = mh.num_heads * mh.head_size, mh.head_size
+            for s, sec in enumerate(("query", "key", "value")):
+                for h in range(mh.num_heads):
+                    out[name.replace("qkv_weight", f"heads.{h}.{sec}.weight")] = p.grad[s * Eh + h * hs: s * Eh + (h + 1) * hs]
+        else:
+            out[name] = p.grad
+    return out
+
+
+@pytest.mark.parametrize("name", ["tiny", "odd", "c1"])
+def test_fp32_model_matches_reference_fixture(lib, name):
+    g = load_golden(name)
+    m = _build(g["config"]).eval()
+    m.load_state_dict(g["state_dict"])
+    x = (g["images_u8"].float() / 255.0).to(DEV)
+    logits = m(x)
+    assert logits.shape == g["logits"].shape and logits.dtype == torch.float32
+    assert rel_err(logits, g["logits"]) < 1e-4
+    loss = torch.nn.CrossEntropyLoss()(logits, g["labels"].to(DEV))
+    assert abs(loss.item() - g["loss"].item()) < 1e-5
+    loss.backward()
+    mine = _grads_by_ref_key(m)
+    assert set(mine) == set(g["grads"])
+    for k, ref in g["grads"].items():
+        assert rel_err(mine[k], ref) < 1e-4, k
+
+
+def _synthetic_case(E, H, L, B, P, img, classes, C=3, seed=0):
+    N = (img // P) ** 2
+    cfg = ref_vit.Cfg(C, classes, N, E, P, H, L, B)
+    sd = ref_vit.random_state_dict(cfg, seed=seed)
+    gen = torch.Generator().manual_seed(seed + 1)
+    x = torch.rand(B, C, img, img, generator=gen)
+    y = torch.randint(0, classes, (B,), generator=gen)
+    c = dict(input_channels=C, num_classes=classes, num_patches=N, embedding_size=E, patch_size=P, num_heads=H,
+             num_blocks=L, batch_size=B)
+    return cfg, c, sd, x, y
+
+
+def _oracle_on_gpu(sd, x, y, cfg, double=False):
+    dt = torch.float64 if double else torch.float32
+    sd = {k: v.to(DEV, dt) for k, v in sd.items()}
+    return ref_vit.loss_and_grads(sd, x.to(DEV, dt), y.to(DEV), cfg)
+
+
+def test_fp32_vit_s16_step_matches_oracle(lib):
+    """BASELINE configs[1]: ViT-S/16 fp32 single-GPU training step (batch reduced to 8 for test time)."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    cfg, c, sd, x, y = _synthetic_case(384, 6, 12, 8, 16, 224, 2)
+    m = _build(c).eval()
+    m.load_state_dict(sd)
+    logits = m(x.to(DEV))
+    loss = torch.nn.functional.cross_entropy(logits, y.to(DEV))
+    loss.backward()
+    ref_logits, ref_loss, ref_grads = _oracle_on_gpu(sd, x, y, cfg, double=True)
+    assert rel_err(logits, ref_logits) < 1e-4
+    assert abs(loss.item() - ref_loss.item()) < 1e-5
+    mine = _grads_by_ref_key(m)
+    worst = max((rel_err(mine[k], ref_grads[k]), k) for k in ref_grads)
+    assert worst[0] < 1e-4, worst
+
+
+@pytest.mark.parametrize("E,H,L,B,P,img", [(768, 12, 2, 4, 16, 224), (384, 6, 3, 3, 16, 224), (320, 4, 1, 2, 14, 112)])
+def test_bf16_model_within_tolerance(lib, E, H, L, B, P, img):
+    cfg, c, sd, x, y = _synthetic_case(E, H, L, B, P, img, 2, seed=3)
+    m = _build(c, precision=torch.bfloat16).eval()
+    m.load_state_dict(sd)
+    logits = m(x.to(DEV))
+    loss = torch.nn.functional.cross_entropy(logits.float(), y.to(DEV))
+    loss.backward()
+    ref_logits, _, ref_grads = _oracle_on_gpu(sd, x, y, cfg)
+    assert rel_err(logits, ref_logits) < 2e-2
+    mine = _grads_by_ref_key(m)
+    bad = [(k, cosine(mine[k], ref_grads[k])) for k in ref_grads if cosine(mine[k], ref_grads[k]) < 0.999]
+    assert not bad, bad[:5]
+
+
+def test_autocast_selects_bf16_kernels(lib):
+    cfg, c, sd, x, y = _synthetic_case(128, 2, 1, 2, 16, 64, 3, seed=4)
+    m = _build(c).eval()
+    m.load_state_dict(sd)
+    ref = m(x.to(DEV))
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        lo = m(x.to(DEV))
+    assert not torch.equal(ref, lo)
+    assert rel_err(lo, ref) < 2e-2
+
+
+def test_layout_bit_exact_patch_and_position(lib):
+    """One-hot probes: pixel (c,y,x) reaches exactly token (y//P)*(W/P)+x//P; pos row t moves only token t;
+    CLS is the LAST token; the classifier reads token 0."""
+    from VisionTransformer import vit
+    torch.manual_seed(0)
+    B, C, P, img, E = 2, 3, 4, 16, 8
+    N = (img // P) ** 2
+    emb = vit.PatchEmbedding(C, E, P, B, N, torch.float32, DEV).to(DEV)
+    with torch.no_grad():
+        emb.sequence[0].bias.zero_()
+        emb.pos_embd.zero_()
+        emb.cls_tkn_embd.copy_(torch.arange(B * E, dtype=torch.float32).reshape(B, 1, E) + 100)
+        out0 = emb(torch.zeros(B, C, img, img, device=DEV))
+        assert torch.count_nonzero(out0[:, :N]) == 0
+        assert torch.equal(out0[:, N], emb.cls_tkn_embd[:, 0])          # CLS last, per batch slot
+        for (b, c, y, xx) in [(0, 0, 0, 0), (1, 2, 15, 15), (1, 1, 5, 10)]:
+            x = torch.zeros(B, C, img, img, device=DEV)
+            x[b, c, y, xx] = 1.0
+            out = emb(x)
+            tok = (y // P) * (img // P) + xx // P
+            want = emb.sequence[0].weight[:, c, y % P, xx % P]
+            assert torch.equal(out[b, tok], want)                        # exact: a single product 1.0 * w
+            out[b, tok] = 0
+            assert torch.count_nonzero(out[:, :N]) == 0
+        for t in (0, 7, N):
+            emb.pos_embd.zero_()
+            emb.pos_embd[0, t] = 1.0
+            d = emb(torch.zeros(B, C, img, img, device=DEV)) - out0
+            assert torch.equal(d[:, t], torch.ones(B, E, device=DEV))
+            d[:, t] = 0
+            assert torch.count_nonzero(d) == 0
+
+
+def test_submodules_match_oracle_fp32(lib):
+    from VisionTransformer import transformer
+    torch.manual_seed(1)
+    B, T, E, H = 2, 37, 64, 4
+    hs = E // H
+    x = torch.randn(B, T, E, device=DEV, requires_grad=True)
+    blk = transformer.Block(E, H, T).to(DEV).eval()
+    sd = {k: v.detach() for k, v in blk.state_dict().items()}
+    y = blk(x)
+    y.square().sum().backward()
+    x2 = x.detach().clone().requires_grad_(True)
+    leaf = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    y_ref, wei_ref = ref_vit.block(leaf, "", x2, H)
+    y_ref.square().sum().backward()
+    assert rel_err(y, y_ref) < 1e-4
+    assert rel_err(x.grad, x2.grad) < 1e-4
+    assert rel_err(blk.ffwd.mlp[0].weight.grad, leaf["ffwd.mlp.0.weight"].grad) < 1e-4
+    assert rel_err(blk.multi_head.qkv_weight.grad[E:E + hs], leaf["multi_head.heads.0.key.weight"].grad) < 1e-4
+    # MultiHeadAttention alone + opt-in attention_probs export (reference transformer.py:48)
+    mh = blk.multi_head
+    mh.export_attention_probs = True
+    mh(x.detach())
+    assert mh.attention_probs.shape == (B, H, T, T)
+    _, wei = ref_vit.multi_head(sd, "multi_head.", x.detach(), H)
+    assert rel_err(mh.attention_probs, wei) < 1e-4
+    # Head returns (out, wei) like the reference
+    hd = transformer.Head(hs, E, T).to(DEV)
+    o, w = hd(x.detach())
+    o_ref, w_ref = ref_vit.head({k: v.detach() for k, v in hd.state_dict().items()}, "", x.detach())
+    assert rel_err(o, o_ref) < 1e-4 and rel_err(w, w_ref) < 1e-4
+
+
+def test_batch_size_contract_and_no_grad(lib):
+    cfg, c, sd, x, y = _synthetic_case(64, 2, 2, 3, 8, 32, 2, seed=5)
+    m = _build(c).eval()
+    m.load_state_dict(sd)
+    with pytest.raises(RuntimeError, match="Sizes of tensors must match"):
+        m(x[:2].to(DEV))
+    a = m(x.to(DEV))
+    with torch.no_grad():
+        b = m(x.to(DEV))
+    assert torch.equal(a.detach(), b) and not b.requires_grad
+
+
+def test_training_mode_dropout_statistics_and_determinism(lib):
+    """train(): dropout p=0.2 live (hard-coded, reference transformer.py:35,53); backward regenerates the same
+    masks (gradient check by finite differences is impossible with fresh masks, so check grad consistency)."""
+    cfg, c, sd, x, y = _synthetic_case(64, 2, 2, 4, 8, 32, 2, seed=6)
+    m = _build(c).train()
+    m.load_state_dict(sd)
+    xs = x.to(DEV)
+    a, b = m(xs).detach(), m(xs).detach()
+    assert not torch.equal(a, b)                       # fresh masks per call
+    m.eval()
+    e = m(xs).detach()
+    assert rel_err(a, e) > 1e-4
+    # mean over many masked forwards approaches the eval output only loosely (non-linear); check it is finite & close
+    m.train()
+    acc = torch.stack([m(xs).detach() for _ in range(64)]).mean(0)
+    assert torch.isfinite(acc).all()
+    # backward under dropout: d(loss)/d(bias of fc2) must equal colsum of masked upstream gradient => nonzero & finite
+    m.zero_grad()
+    torch.nn.functional.cross_entropy(m(xs), y.to(DEV)).backward()
+    for n, p in m.named_parameters():
+        assert p.grad is not None and torch.isfinite(p.grad).all(), n
+
+
+def test_adamw_training_reduces_loss_fp32_and_bf16(lib):
+    for prec in (torch.float32, torch.bfloat16):
+        cfg, c, sd, x, y = _synthetic_case(64, 4, 2, 8, 8, 32, 2, seed=7)
+        m = _build(c, precision=prec).eval()
+        m.load_state_dict(sd)
+        opt = torch.optim.AdamW(m.parameters(), lr=1e-3, weight_decay=1e-4)
+        losses = []
+        for _ in range(12):
+            loss = torch.nn.functional.cross_entropy(m(x.to(DEV)).float(), y.to(DEV))
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+        assert losses[-1] < 0.5 * losses[0], (prec, losses)

@@ -38,8 +38,16 @@ class _Precision:
     """Mixin: `precision` (torch.float32 | torch.bfloat16) and the bf16 weight-shadow cache."""
     precision = torch.float32
 
+    def _kernel_dtype(self):
+        """bf16 (tcgen05 path) when configured so or when called under torch.autocast(cuda, bfloat16)."""
+        if self.precision == torch.bfloat16:
+            return torch.bfloat16
+        if torch.is_autocast_enabled("cuda") and torch.get_autocast_dtype("cuda") == torch.bfloat16:
+            return torch.bfloat16
+        return torch.float32
+
     def _w(self, p):
-        if self.precision == torch.float32:
+        if self._kernel_dtype() == torch.float32:
             return p.detach()
         if not hasattr(self, "_shadow"):
             object.__setattr__(self, "_shadow", eng.ShadowCache())
@@ -61,7 +69,7 @@ class _HeadFn(torch.autograd.Function):
     def forward(ctx, x, wq, wk, wv, mod):
         B, T, E = x.shape
         hs = wq.shape[0]
-        dt = mod.precision
+        dt = mod._kernel_dtype()
         w = torch.cat([wq, wk, wv], dim=0).contiguous()      # packed [3hs, E]
         xl, wl = _lp(x.reshape(B * T, E), dt), _lp(w, dt)
         qkv = torch.empty(B * T, 3 * hs, dtype=dt, device=x.device)
@@ -107,7 +115,7 @@ class Head(_Precision, nn.Module):
 
     def forward(self, x):
         x = _check_input(x, self.key.in_features)
-        if self.precision == torch.bfloat16 and self.key.out_features % 16 != 0:
+        if self._kernel_dtype() == torch.bfloat16 and self.key.out_features % 16 != 0:
             raise RuntimeError("bf16 Head needs head_size % 16 == 0; use precision float32")
         return _HeadFn.apply(x, self.query.weight, self.key.weight, self.value.weight, self)
 
@@ -134,7 +142,7 @@ class _MHAFn(torch.autograd.Function):
         H = mod.num_heads
         Eh = wqkv.shape[0] // 3  # H * hs
         hs = Eh // H
-        dt = mod.precision
+        dt = mod._kernel_dtype()
         M = B * T
         xl = _lp(x.reshape(M, E), dt)
         wq, wp = mod._w(wqkv), mod._w(wproj)
@@ -209,7 +217,8 @@ class MultiHeadAttention(_Precision, nn.Module):
         packed = destination.pop(prefix + "qkv_weight")
         Eh, hs = self.num_heads * self.head_size, self.head_size
         for h in range(self.num_heads):
-            for s, name in enumerate(_SECTIONS):
+            for name in ("key", "query", "value"):  # the reference's registration order (transformer.py:12-17)
+                s = _SECTIONS.index(name)
                 destination[f"{prefix}heads.{h}.{name}.weight"] = packed[s * Eh + h * hs: s * Eh + (h + 1) * hs]
 
     def _load_from_state_dict(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys,
@@ -244,7 +253,7 @@ class _FFNFn(torch.autograd.Function):
     def forward(ctx, x, w1, b1, w2, b2, mod, p_drop, seed):
         B, T, E = x.shape
         M, F = B * T, w1.shape[0]
-        dt = mod.precision
+        dt = mod._kernel_dtype()
         xl = _lp(x.reshape(M, E), dt)
         w1l, w2l = mod._w(w1), mod._w(w2)
         h = torch.empty(M, F, dtype=dt, device=x.device)
@@ -320,7 +329,7 @@ class _BlockFn(torch.autograd.Function):
     def forward(ctx, x, blk, layer, p_drop, seed, *params):
         B, T, E = x.shape
         H = blk.multi_head.num_heads
-        d = _dims_for(x, E, H, blk.precision, p_drop, seed)
+        d = _dims_for(x, E, H, blk._kernel_dtype(), p_drop, seed)
         L = _C.lib()
         acts = torch.empty(L.vitb200_block_act_bytes(ctypes.byref(d)), dtype=torch.uint8, device=x.device)
         y = torch.empty(B * T, E, dtype=torch.float32, device=x.device)
@@ -328,7 +337,7 @@ class _BlockFn(torch.autograd.Function):
         plan = eng.Plan.__new__(eng.Plan)
         eng.Plan.block_fwd(plan, d, layer, pd, x, y, acts)
         ctx.save_for_backward(x, acts, *[pd[n] for n in _C.BLOCK_FIELDS_P])
-        ctx.meta = (d, layer, blk.precision)
+        ctx.meta = (d, layer, blk._kernel_dtype())
         return y.reshape(B, T, E)
 
     @staticmethod
