@@ -1,0 +1,306 @@
+"""Benchmark of the ViT training hot path (BASELINE.json: "ViT-B/16 train images/s at 1/2/4/8 B200").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]            # our arm (N>1: launched by torchrun, one rank/GPU)
+    python bench.py --impl reference [--gpus N --steps K --warmup W]   # the reference's CPU path on the host cores
+
+A step = forward + mean cross-entropy + backward + gradient all-reduce + AdamW on one batch of 256 synthetic
+224x224x3 images per GPU (ViT-B/16, bf16 tensor-core operands, fp32 master weights / residual stream / gradients,
+dropout p=0.2 live, 2 classes = the brain-tumor classifier's shape).  Rank 0 prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (os.path.join(ROOT, "vision-transformer_b200"), ROOT):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+MODELS = {
+    # name: (E, H, L, P, img)
+    "vit_s16": (384, 6, 12, 16, 224),
+    "vit_b16": (768, 12, 12, 16, 224),
+    "vit_l16": (1024, 16, 24, 16, 224),
+    "vit_h14": (1280, 16, 32, 14, 336),
+}
+METRIC = "ViT-B/16 train images/s"
+UNIT = "images/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="vit_b16", choices=sorted(MODELS))
+    ap.add_argument("--batch", type=int, default=256, help="images per GPU")
+    ap.add_argument("--classes", type=int, default=2)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--bucket-mb", type=float, default=48)
+    return ap.parse_args()
+
+
+def workload(args):
+    E, H, L, P, img = MODELS[args.model]
+    return dict(input_channels=3, num_classes=args.classes, image_size=img, patch_size=P, embedding_size=E,
+                num_heads=H, num_blocks=L)
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"tflops_sustained": p.get("bf16_tflops_sustained"), "tflops_burst": p.get("bf16_tflops"),
+                "hbm_gbs": p.get("hbm_gbs"), "source": "measured (MEASURED_PEAKS.json)"}
+    return {"tflops_sustained": 1400.0, "tflops_burst": 1590.0, "hbm_gbs": 6650.0,
+            "source": "fallback (B200_PROFILING.md)"}
+
+
+# ---------------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.f.read().splitlines():
+            parts = [c.strip() for c in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1])); pw.append(float(parts[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, parts[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), power_w_max=max(pw), reasons=sorted(reasons),
+                       samples=len(sm))
+        return out
+
+
+# ---------------------------------------------------------------------------------------------------- CPU arms
+def cpu_sample(args, batch, steps, warmup):
+    """Oracle port of the reference's CPU path (oracle/cpu_step.py) on `batch` images per step."""
+    import torch
+    from oracle import cpu_step
+    tr = cpu_step.CpuTrainer(batch_size=batch, **workload(args))
+    sec = cpu_step.time_steps(tr, steps, warmup)
+    host = cpu_step.host_description()
+    return batch / sec, sec, host, torch.get_num_threads()
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's own CPU implementation of the step (its PyTorch path restated in
+    oracle/, since /root/reference is a Python tree that does not travel to the GPU box), all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    # size the per-step sample so that (steps + warmup) steps end within ~3 minutes
+    ips, _, _, _ = cpu_sample(args, 2, 1, 1)
+    budget = 170.0 / max(args.steps + args.warmup, 1)
+    batch = int(max(1, min(16, ips * budget)))
+    ips, sec, host, threads = cpu_sample(args, batch, args.steps, args.warmup)
+    E, H, L, P, img = MODELS[args.model]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": ips, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.model} train step (fwd+CE+bwd+AdamW), {img}x{img}x3 synthetic, dropout 0.2, "
+                               f"{args.classes} classes; CPU sample of {batch} images per step",
+                   "global_batch": batch},
+        "cpu_baseline": {"value": ips, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{args.steps} steps x {batch} images after {args.warmup} warm-up, torch "
+                                   f"{torch.__version__} CPU, {host['cpu_model']}, os.cpu_count={host['os_cpu_count']}"},
+        "e2e": {"value": ips, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------- our arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from VisionTransformer import _C
+    import train_dp
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    pg = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+        pg = dist.group.WORLD
+
+    dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    wl = workload(args)
+    tr = train_dp.DPTrainer(batch_size=args.batch, dtype=dtype, device=dev, process_group=pg, world_size=world,
+                            bucket_mb=args.bucket_mb, seed=0, **wl)
+    tr.init_parameters(seed=0)  # random-init weights of the architecture (no checkpoints offline)
+    tr.broadcast_parameters()
+
+    gen = torch.Generator().manual_seed(1234 + rank)
+    n_host = 2
+    xh = [torch.rand(args.batch, 3, tr.img, tr.img, generator=gen).pin_memory() for _ in range(n_host)]
+    yh = [torch.randint(0, args.classes, (args.batch,), generator=gen).pin_memory() for _ in range(n_host)]
+    xd = [x.to(dev) for x in xh]
+    yd = [y.to(dev) for y in yh]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for i in range(warmup):
+            fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = _C.launch_count()
+        e0.record()
+        for i in range(steps):
+            fn(warmup + i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), _C.launch_count() - l0
+
+    # ---- device-resident inputs: `value`
+    sampler = ClockSampler(local) if rank == 0 else None
+    total_ms, launches = timed(lambda i: tr.step(xd[i % n_host], yd[i % n_host]), args.steps, args.warmup)
+    clocks = sampler.stop() if sampler else None
+    loss_after = float(tr.loss.item())
+    ms_step = total_ms / args.steps
+    gb = args.batch * world
+    value = gb / (ms_step * 1e-3)
+
+    # ---- host-resident inputs through the public step API: `e2e`
+    e2e = None
+    if not args.no_e2e:
+        idx = []
+        e2e_ms, _ = timed(lambda i: idx.append(tr.step_host(xh[i % n_host], yh[i % n_host])), args.steps,
+                          min(args.warmup, 3))
+        losses = [tr.read_loss(li) for li in idx[-min(len(idx), 8):]]
+        e2e = {"value": gb / (e2e_ms / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": tr.h2d_bytes,
+               "d2h_bytes_per_step": tr.d2h_bytes, "ms_per_step": e2e_ms / args.steps, "last_loss": losses[-1],
+               "api": "train_dp.DPTrainer.step_host(pinned images fp32, labels): H2D on a copy stream "
+                      "(double-buffered) + loss D2H every step"}
+
+    # ---- live per-kernel-class timing (CUDA events on the launching stream) over 2 more steps: `roofline`
+    pk = peaks()
+    barrier()
+    _C.prof_begin()
+    for i in range(2):
+        tr.step(xd[i % n_host], yd[i % n_host])
+    prof = _C.prof_end()
+    kern = {}
+    tot_ms = sum(v["ms"] for v in prof.values()) or 1.0
+    for name, v in prof.items():
+        if v["launches"] == 0:
+            continue
+        rate = v["work"] / (v["ms"] * 1e-3) if v["ms"] > 0 else 0.0
+        is_flops = name.startswith(("gemm", "attn"))
+        kern[name] = {"launches_per_step": v["launches"] // 2, "ms_per_step": v["ms"] / 2,
+                      "share": v["ms"] / tot_ms,
+                      ("tflops" if is_flops else "gbs"): rate / (1e12 if is_flops else 1e9)}
+    g = prof["gemm_tcgen05"] if args.dtype == "bf16" else prof["gemm_f32"]
+    ach = g["work"] / (g["ms"] * 1e-3) / 1e12 if g["ms"] > 0 else 0.0
+    peak_tf = pk["tflops_sustained"] if args.dtype == "bf16" else None
+    roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05/TMEM/TMA bf16 contraction, all call sites)",
+                "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": (ach / peak_tf) if peak_tf else None,
+                "peak_source": pk["source"] + ", sustained cuBLAS bf16 (kernel timed inside a long step)",
+                "traffic": None, "launches_per_step": g["launches"] // 2,
+                "flops_per_launch_avg": g["work"] / max(g["launches"], 1),
+                "share_of_step": g["ms"] / tot_ms}
+    step_tflops = tr.flops_per_image() * args.batch / (ms_step * 1e-3) / 1e12  # per GPU
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        torch.cuda.synchronize()
+        b = 4
+        ips, sec, host, threads = cpu_sample(args, b, 2, 1)
+        cpu = {"value": ips, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"2 steps x {b} images after 1 warm-up ({sec:.2f} s/step), oracle/cpu_step.py (restated "
+                         f"reference PyTorch path, fwd+CE+bwd+AdamW, dropout on), {host['cpu_model']}, "
+                         f"os.cpu_count={host['os_cpu_count']}"}
+
+    E, H, L, P, img = MODELS[args.model]
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": f"{args.model} train step (fwd + CE + bwd + grad all-reduce + AdamW), {img}x{img}x3 "
+                               f"synthetic images, {args.classes} classes, dropout 0.2 live, batch {args.batch}/GPU",
+                   "global_batch": gb, "tokens_per_image": tr.T, "parallelism": f"dp{world}",
+                   "l2_policy": "inputs (154 MB/step at B=256) and activations (~13 GB) exceed the 126 MB L2; "
+                                "no explicit flush",
+                   "grad_buckets_mb": [round((b_ - a_) * 4 / 2 ** 20, 1) for a_, b_, _ in tr.buckets]},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
+        "roofline": roofline, "cpu_baseline": cpu,
+        "mfu": {"algorithmic_tflops_per_gpu": step_tflops, "of_measured_sustained": step_tflops / pk["tflops_sustained"],
+                "of_measured_burst": step_tflops / pk["tflops_burst"], "of_datasheet_2250": step_tflops / 2250.0},
+        "kernels": kern, "loss_after": loss_after,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

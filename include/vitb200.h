@@ -30,6 +30,19 @@ int vitb200_version(void);
 /* 1 if the current device is sm_100 (B200); the library refuses to run anywhere else. */
 int vitb200_device_ok(void);
 
+/* Launch accounting and live profiling (bench.py's roofline / gpu_launches; no reference counterpart).
+ * vitb200_launch_count: kernels launched by this library so far (process-wide).
+ * vitb200_prof_begin .. vitb200_prof_end: every kernel launch in between is bracketed by a cudaEvent pair on its
+ * launching stream; prof_end synchronises the device and fills out[VITB200_PROF_CLASSES] with, per kernel class,
+ * the summed device time, the summed algorithmic work (FLOPs for gemm/attn classes, bytes for the others) and the
+ * launch count. */
+#define VITB200_PROF_CLASSES 8
+typedef struct { double ms; double work; int64_t launches; } vitb200_prof_entry;
+int64_t vitb200_launch_count(void);
+const char* vitb200_prof_class_name(int cls);
+int vitb200_prof_begin(void);
+int vitb200_prof_end(vitb200_prof_entry* out);
+
 /* Dropout descriptor: p == 0 disables.  Masks are regenerated from (seed, stream, element index) with
  * Philox4x32-10, so backward never stores them.  Replaces nn.Dropout(0.2) at transformer.py:40,47,59. */
 typedef struct {
@@ -103,7 +116,7 @@ int vitb200_im2col(const float* x, void* A, int out_dtype, int B, int C, int Hi,
                    void* stream);
 /* out[n] += sum_m in[m,n] (bias gradients). */
 int vitb200_colsum(const void* in, int in_dtype, int64_t ld, float* out, int M, int N, void* stream);
-/* nn.CrossEntropyLoss() mean + gradient (train.py:81,93).  dlogits may be NULL. */
+/* nn.CrossEntropyLoss() mean + gradient (train.py:81,93): dlogits = grad_scale * d(mean loss)/dlogits, may be NULL. */
 int vitb200_cross_entropy(const float* logits, const int64_t* labels, float* loss, float* dlogits, int B, int C,
                           float grad_scale, void* stream);
 int vitb200_cast_f32_bf16(const float* in, void* out_bf16, int64_t n, void* stream);

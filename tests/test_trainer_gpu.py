@@ -1,0 +1,90 @@
+"""GPU: the flat-arena trainer (train_dp.DPTrainer) against the oracle: gradients, AdamW update, loss descent, and the
+host-input (e2e) step."""
+import pytest
+import torch
+
+from conftest import cosine, rel_err
+from oracle import ref_vit
+
+pytestmark = pytest.mark.gpu
+
+
+def _make(dtype, E=64, H=2, L=2, B=4, P=8, img=32, classes=3, dropout_p=0.0):
+    import train_dp
+    tr = train_dp.DPTrainer(input_channels=3, num_classes=classes, image_size=img, patch_size=P, embedding_size=E,
+                            num_heads=H, num_blocks=L, batch_size=B, dtype=dtype, dropout_p=dropout_p, lr=1e-3)
+    cfg = ref_vit.Cfg(3, classes, (img // P) ** 2, E, P, H, L, B)
+    sd = ref_vit.random_state_dict(cfg, seed=21)
+    tr.load_state_dict(sd)
+    gen = torch.Generator().manual_seed(22)
+    x = torch.rand(B, 3, img, img, generator=gen)
+    y = torch.randint(0, classes, (B,), generator=gen)
+    return tr, cfg, sd, x, y
+
+
+def test_trainer_state_dict_roundtrip(lib):
+    tr, cfg, sd, x, y = _make(torch.float32)
+    out = tr.state_dict()
+    assert list(out.keys()) != [] and set(out) == set(sd)
+    for k in sd:
+        assert torch.equal(out[k].cpu(), sd[k]), k
+
+
+def test_trainer_fp32_grads_and_adamw_match_oracle(lib):
+    tr, cfg, sd, x, y = _make(torch.float32)
+    d = tr._dims(False)
+    tr.forward(x.cuda(), d)
+    tr.backward(y.cuda(), d)
+    ref_logits, ref_loss, ref_grads = ref_vit.loss_and_grads(sd, x, y, cfg)
+    assert rel_err(tr.logits, ref_logits) < 1e-4
+    assert abs(tr.loss.item() - ref_loss.item()) < 1e-5
+    mine = tr.grads_by_ref_key()
+    for k, g in ref_grads.items():
+        assert rel_err(mine[k], g) < 1e-4, k
+    # one AdamW step over the whole arena == oracle AdamW per tensor
+    mine = {k: v.clone().cpu() for k, v in mine.items()}
+    tr.optimizer_step()
+    new = tr.state_dict()
+    for k in sd:
+        p = sd[k].clone()
+        # first Adam step is lr * g / (|g| + eps): feed the oracle OUR gradient so near-zero entries do not flip
+        ref_vit.adamw_step(p, mine[k], torch.zeros_like(p), torch.zeros_like(p), 1, lr=1e-3)
+        assert torch.allclose(new[k].cpu(), p, rtol=1e-4, atol=2e-6), k
+    assert torch.count_nonzero(tr.g) == 0  # gradients cleared for the next step
+
+
+def test_trainer_bf16_grads_cosine(lib):
+    tr, cfg, sd, x, y = _make(torch.bfloat16, E=128, H=2)
+    sd = {k: (v * 0.25 if k.endswith(("key.weight", "query.weight")) else v) for k, v in sd.items()}  # see _soften
+    tr.load_state_dict(sd)
+    d = tr._dims(False)
+    tr.forward(x.cuda(), d)
+    tr.backward(y.cuda(), d)
+    ref_logits, _, ref_grads = ref_vit.loss_and_grads(sd, x, y, cfg)
+    assert rel_err(tr.logits, ref_logits) < 2e-2
+    mine = tr.grads_by_ref_key()
+    bad = [(k, cosine(mine[k], g)) for k, g in ref_grads.items() if cosine(mine[k], g) < 0.999]
+    assert not bad, bad[:5]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_trainer_training_reduces_loss_with_dropout(lib, dtype):
+    tr, cfg, sd, x, y = _make(dtype, E=128, H=2, B=8, dropout_p=0.2)
+    xs, ys = x.cuda(), y.cuda()
+    losses = [tr.step(xs, ys).item() for _ in range(30)]
+    assert losses[-1] < 0.6 * losses[0], losses
+    if dtype == torch.bfloat16:
+        assert torch.equal(tr.shadow, tr.p.bfloat16())  # AdamW keeps the bf16 shadow weights in sync
+
+
+def test_trainer_step_host_matches_step(lib):
+    tr_a, cfg, sd, x, y = _make(torch.float32)
+    tr_b, *_ = _make(torch.float32)
+    xh, yh = x.pin_memory(), y.pin_memory()
+    for _ in range(3):
+        tr_a.step(x.cuda(), y.cuda())
+        li = tr_b.step_host(xh, yh)
+    assert abs(tr_b.read_loss(li) - tr_a.loss.item()) < 1e-6
+    assert torch.allclose(tr_a.p, tr_b.p, rtol=1e-5, atol=1e-7)
+    with pytest.raises(RuntimeError, match="Sizes of tensors must match"):
+        tr_a.step(x[:2].cuda(), y[:2].cuda())

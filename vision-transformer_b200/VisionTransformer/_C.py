@@ -55,6 +55,13 @@ class Dims(ctypes.Structure):
                 ("ln_eps", c_float)]
 
 
+class ProfEntry(ctypes.Structure):
+    _fields_ = [("ms", ctypes.c_double), ("work", ctypes.c_double), ("launches", c_int64)]
+
+
+PROF_CLASSES = 8
+
+
 def _ptr_struct(name, fields):
     return type(name, (ctypes.Structure,), {"_fields_": [(f, c_void_p) for f in fields]})
 
@@ -93,6 +100,12 @@ def _declare(L):
     L.vitb200_device_ok.restype = c_int
     L.vitb200_gemm.argtypes = [ctypes.POINTER(GemmArgs), c_void_p]
     L.vitb200_gemm.restype = c_int
+    L.vitb200_launch_count.restype = c_int64
+    L.vitb200_prof_class_name.argtypes = [c_int]
+    L.vitb200_prof_class_name.restype = ctypes.c_char_p
+    L.vitb200_prof_begin.restype = c_int
+    L.vitb200_prof_end.argtypes = [ctypes.POINTER(ProfEntry)]
+    L.vitb200_prof_end.restype = c_int
     P = ctypes.POINTER
     sig = {
         "vitb200_ln_fwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],
@@ -131,13 +144,31 @@ def _declare(L):
 
 
 EXPORTS = (
-    "vitb200_last_error", "vitb200_version", "vitb200_device_ok", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
+    "vitb200_last_error", "vitb200_version", "vitb200_device_ok", "vitb200_launch_count", "vitb200_prof_class_name",
+    "vitb200_prof_begin", "vitb200_prof_end", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
     "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
     "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
     "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_bwd",
     "vitb200_block_act_bytes", "vitb200_block_scratch_bytes", "vitb200_block_fwd", "vitb200_block_bwd",
     "vitb200_head_act_bytes", "vitb200_head_fwd", "vitb200_head_bwd",
 )
+
+
+def launch_count():
+    return int(lib().vitb200_launch_count())
+
+
+def prof_begin():
+    check(lib().vitb200_prof_begin())
+
+
+def prof_end():
+    """-> {class name: {"ms", "work", "launches"}} for the kernels launched since prof_begin()."""
+    arr = (ProfEntry * PROF_CLASSES)()
+    check(lib().vitb200_prof_end(arr))
+    return {lib().vitb200_prof_class_name(i).decode(): {"ms": arr[i].ms, "work": arr[i].work,
+                                                         "launches": int(arr[i].launches)}
+            for i in range(PROF_CLASSES)}
 
 
 def check(rc):

@@ -136,7 +136,7 @@ class _ViTFn(torch.autograd.Function):
         plan.L = nL
         L = _C.lib()
         dev = x.device
-        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        need_grad = any(ctx.needs_input_grad)  # False under torch.no_grad(): no activation stash (train.py:29-44)
         nb = lambda n: torch.empty(max(int(n), 256), dtype=torch.uint8, device=dev)  # noqa: E731
 
         pe = _embed_param_dict(emb, *params[:4])

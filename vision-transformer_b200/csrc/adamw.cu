@@ -81,6 +81,7 @@ int adamw_flat(float* p, const float* g, float* m, float* v, bf16* shadow, int64
   VB_REQUIRE(n > 0, "adamw: empty arena");
   const int64_t blocks = ceil_div<int64_t>(n, 256 * 4 * 4);
   const int64_t cap = static_cast<int64_t>(num_sms()) * 8;
+  ProfScope prof(kProfAdamW, static_cast<double>(n) * (28 + (shadow ? 2 : 0)), 1, s);
   adamw_flat_kernel<<<static_cast<int>(blocks < cap ? blocks : cap), 256, 0, s>>>(p, g, m, v, shadow, n, h);
   VB_CHECK_LAUNCH();
   return kOk;
@@ -90,6 +91,7 @@ int adamw_multi(const uint64_t* p_ptrs, const uint64_t* g_ptrs, const uint64_t* 
                 const uint64_t* s_ptrs, const int64_t* sizes, const int32_t* blk_tensor, const int32_t* blk_chunk,
                 int n_blocks, const AdamWHyper& h, cudaStream_t s) {
   VB_REQUIRE(n_blocks > 0, "adamw_multi: empty table");
+  ProfScope prof(kProfAdamW, 0.0, 1, s);
   adamw_multi_kernel<<<n_blocks, 256, 0, s>>>(p_ptrs, g_ptrs, m_ptrs, v_ptrs, s_ptrs, sizes, blk_tensor, blk_chunk, h);
   VB_CHECK_LAUNCH();
   return kOk;

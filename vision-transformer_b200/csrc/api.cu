@@ -1,6 +1,9 @@
 // C-ABI plumbing: error string, device check, GEMM dispatch (see include/vitb200.h).
+#include <atomic>
 #include <cstdarg>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 #include "../../include/vitb200.h"
 #include "common.cuh"
@@ -30,9 +33,79 @@ int num_sms() {
   return cached[dev];
 }
 
+// ---- launch accounting / live profiling --------------------------------------------------------------
+namespace {
+constexpr int kProfMaxScopes = 16384;
+std::atomic<long long> g_launches{0};
+std::atomic<bool> g_prof_on{false};
+std::mutex g_prof_mu;
+struct ProfRec { cudaEvent_t e0, e1; int cls; double work; int launches; };
+std::vector<ProfRec> g_prof_recs;      // scopes recorded since prof_begin
+std::vector<cudaEvent_t> g_prof_pool;  // reusable events
+cudaEvent_t prof_take_event() {
+  if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+}  // namespace
+
+ProfScope::ProfScope(int cls, double work, int launches, cudaStream_t s) : slot(-1), stream(s) {
+  g_launches.fetch_add(launches, std::memory_order_relaxed);
+  if (!g_prof_on.load(std::memory_order_relaxed)) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (static_cast<int>(g_prof_recs.size()) >= kProfMaxScopes) return;
+  ProfRec r;
+  r.e0 = prof_take_event(); r.e1 = prof_take_event();
+  r.cls = cls; r.work = work; r.launches = launches;
+  if (r.e0 == nullptr || r.e1 == nullptr) return;
+  cudaEventRecord(r.e0, s);
+  slot = static_cast<int>(g_prof_recs.size());
+  g_prof_recs.push_back(r);
+}
+ProfScope::~ProfScope() {
+  if (slot < 0) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (slot < static_cast<int>(g_prof_recs.size())) cudaEventRecord(g_prof_recs[slot].e1, stream);
+}
+
 }  // namespace vb
 
 extern "C" {
+
+int64_t vitb200_launch_count(void) { return vb::g_launches.load(); }
+
+const char* vitb200_prof_class_name(int cls) {
+  static const char* names[vb::kProfCount] = {"gemm_tcgen05", "gemm_f32", "attn_fwd", "attn_bwd", "ln_fwd", "ln_bwd",
+                                              "elementwise", "adamw"};
+  return cls >= 0 && cls < vb::kProfCount ? names[cls] : "?";
+}
+
+int vitb200_prof_begin(void) {
+  std::lock_guard<std::mutex> lk(vb::g_prof_mu);
+  for (auto& r : vb::g_prof_recs) { vb::g_prof_pool.push_back(r.e0); vb::g_prof_pool.push_back(r.e1); }
+  vb::g_prof_recs.clear();
+  vb::g_prof_on.store(true);
+  return 0;
+}
+
+int vitb200_prof_end(vitb200_prof_entry* out) {
+  using namespace vb;
+  g_prof_on.store(false);
+  VB_CHECK_CUDA(cudaDeviceSynchronize());
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (int c = 0; c < kProfCount; ++c) { out[c].ms = 0; out[c].work = 0; out[c].launches = 0; }
+  for (auto& r : g_prof_recs) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
+      out[r.cls].ms += ms; out[r.cls].work += r.work; out[r.cls].launches += r.launches;
+    }
+    g_prof_pool.push_back(r.e0); g_prof_pool.push_back(r.e1);
+  }
+  g_prof_recs.clear();
+  (void)cudaGetLastError();
+  return kOk;
+}
 
 const char* vitb200_last_error(void) { return vb::last_error(); }
 int vitb200_version(void) { return 100; }

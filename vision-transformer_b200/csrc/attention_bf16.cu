@@ -416,6 +416,7 @@ int fwd_launch(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, floa
   const size_t smem = 5 * Tile<HS>::BYTES;
   VB_PROPAGATE(set_attn_smem(attn_bf16_fwd_kernel<HS>, smem));
   dim3 grid(ceil_div(T, AT_BLK), B * H);
+  ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * T * HS, 1, stream);
   attn_bf16_fwd_kernel<HS><<<grid, AT_THREADS, smem, stream>>>(qkv, out, lse, T, H, scale);
   VB_CHECK_LAUNCH();
   return kOk;
@@ -425,6 +426,7 @@ template <int HS>
 int bwd_launch(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B, int T, int H,
                float scale, cudaStream_t stream) {
   dim3 grid(ceil_div(T, AT_BLK), B * H);
+  ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * T * HS, 2, stream);
   const size_t smem_kv = 4 * Tile<HS>::BYTES + 4 * AT_BLK * sizeof(float);
   VB_PROPAGATE(set_attn_smem(attn_bf16_bwd_dkv_kernel<HS>, smem_kv));
   attn_bf16_bwd_dkv_kernel<HS><<<grid, AT_THREADS, smem_kv, stream>>>(qkv, d_o, lse, delta, dqkv, T, H, scale);
@@ -444,13 +446,14 @@ int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B
 int attn_bf16_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
                       cudaStream_t stream) {
   switch (hs) {
+    case 16: return fwd_launch<16>(qkv, out, lse, B, T, H, scale, stream);
     case 32: return fwd_launch<32>(qkv, out, lse, B, T, H, scale, stream);
     case 64: return fwd_launch<64>(qkv, out, lse, B, T, H, scale, stream);
     case 80: return fwd_launch<80>(qkv, out, lse, B, T, H, scale, stream);
     case 96: return fwd_launch<96>(qkv, out, lse, B, T, H, scale, stream);
     case 128: return fwd_launch<128>(qkv, out, lse, B, T, H, scale, stream);
     default:
-      set_error("attention (bf16): head_size %d not instantiated (supported: 32, 64, 80, 96, 128)", hs);
+      set_error("attention (bf16): head_size %d not instantiated (supported: 16, 32, 64, 80, 96, 128)", hs);
       return kErrUnsupported;
   }
 }
@@ -459,13 +462,14 @@ int attn_bf16_backward(const bf16* qkv, const bf16* out, const bf16* d_o, const 
                        int B, int T, int H, int hs, float scale, cudaStream_t stream) {
   VB_PROPAGATE(attn_delta(out, d_o, true, delta, B, T, H, hs, stream));
   switch (hs) {
+    case 16: return bwd_launch<16>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
     case 32: return bwd_launch<32>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
     case 64: return bwd_launch<64>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
     case 80: return bwd_launch<80>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
     case 96: return bwd_launch<96>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
     case 128: return bwd_launch<128>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
     default:
-      set_error("attention (bf16): head_size %d not instantiated (supported: 32, 64, 80, 96, 128)", hs);
+      set_error("attention (bf16): head_size %d not instantiated (supported: 16, 32, 64, 80, 96, 128)", hs);
       return kErrUnsupported;
   }
 }

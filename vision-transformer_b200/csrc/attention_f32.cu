@@ -175,6 +175,7 @@ int set_smem(K kern, size_t smem) {
 
 int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B, int T, int H, int hs,
                cudaStream_t stream) {
+  ProfScope prof(kProfAttnBwd, 0.0, 1, stream);
   const int total_warps = B * H * T;
   const int threads = 256;
   const int grid = ceil_div(total_warps * 32, threads);
@@ -189,6 +190,7 @@ int attn_f32_forward(const float* qkv, float* out, float* lse, int B, int T, int
   const size_t smem = static_cast<size_t>(AF_WARPS) * (hs + T) * sizeof(float);
   VB_PROPAGATE(set_smem(attn_f32_fwd_kernel<false>, smem));
   dim3 grid(B * H, ceil_div(T, AF_WARPS));
+  ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * T * hs, 1, stream);
   attn_f32_fwd_kernel<false><<<grid, AF_WARPS * 32, smem, stream>>>(qkv, out, lse, nullptr, B, T, H, hs, scale);
   VB_CHECK_LAUNCH();
   return kOk;
@@ -198,6 +200,7 @@ int attn_f32_probs(const float* qkv, float* probs, int B, int T, int H, int hs, 
   const size_t smem = static_cast<size_t>(AF_WARPS) * (hs + T) * sizeof(float);
   VB_PROPAGATE(set_smem(attn_f32_fwd_kernel<true>, smem));
   dim3 grid(B * H, ceil_div(T, AF_WARPS));
+  ProfScope prof(kProfAttnFwd, 2.0 * B * H * T * T * hs, 1, stream);
   attn_f32_fwd_kernel<true><<<grid, AF_WARPS * 32, smem, stream>>>(qkv, nullptr, nullptr, probs, B, T, H, hs, scale);
   VB_CHECK_LAUNCH();
   return kOk;
@@ -207,6 +210,7 @@ int attn_f32_backward(const float* qkv, const float* out, const float* d_o, cons
                       float* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t stream) {
   VB_PROPAGATE(attn_delta(out, d_o, false, delta, B, T, H, hs, stream));
   dim3 grid(B * H, ceil_div(T, AF_WARPS));
+  ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * T * hs, 2, stream);
   const size_t smem_q = static_cast<size_t>(AF_WARPS) * (2 * hs + T) * sizeof(float);
   VB_PROPAGATE(set_smem(attn_f32_bwd_dq_kernel, smem_q));
   attn_f32_bwd_dq_kernel<<<grid, AF_WARPS * 32, smem_q, stream>>>(qkv, d_o, lse, delta, dqkv, B, T, H, hs, scale);

@@ -51,6 +51,23 @@ __host__ __device__ constexpr T ceil_div(T a, T b) {
 int num_sms();  // SM count of the current device (cached)
 
 // ---------------------------------------------------------------------------------------------------
+// Launch accounting + optional live profiling (vitb200_prof_begin / vitb200_prof_end): every host-side kernel
+// wrapper opens a ProfScope naming its kernel class, its algorithmic work (FLOPs for contractions / attention,
+// bytes for bandwidth kernels) and how many kernels it launches.  Disabled: one relaxed atomic add.  Enabled:
+// a cudaEvent pair recorded on the launching stream around the launches.
+// ---------------------------------------------------------------------------------------------------
+enum ProfClass {
+  kProfGemmTc = 0, kProfGemmF32, kProfAttnFwd, kProfAttnBwd, kProfLnFwd, kProfLnBwd, kProfEltwise, kProfAdamW,
+  kProfCount
+};
+struct ProfScope {
+  int slot;
+  cudaStream_t stream;
+  ProfScope(int cls, double work, int launches, cudaStream_t s);
+  ~ProfScope();
+};
+
+// ---------------------------------------------------------------------------------------------------
 // Counter-based dropout RNG (Philox4x32-10).  One call yields 4 uniform 32-bit words for a
 // (seed, stream, index/4) triple, so forward and backward regenerate identical masks without storing them.
 // ---------------------------------------------------------------------------------------------------

@@ -210,6 +210,7 @@ __global__ void ce_kernel(const float* __restrict__ logits, const int64_t* __res
   __shared__ float warp_loss[32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   float acc = 0.f;
+  const float gs = grad_scale / static_cast<float>(B);  // d(mean loss)/dlogits, times the caller's scale
   for (int b = warp; b < B; b += nwarps) {
     const float* row = logits + static_cast<int64_t>(b) * C;
     float mx = -INFINITY;
@@ -223,7 +224,7 @@ __global__ void ce_kernel(const float* __restrict__ logits, const int64_t* __res
     if (lane == 0) acc += lse - row[y];
     if (dlogits != nullptr)
       for (int c = lane; c < C; c += 32)
-        dlogits[static_cast<int64_t>(b) * C + c] = (expf(row[c] - lse) - (c == y ? 1.f : 0.f)) * grad_scale;
+        dlogits[static_cast<int64_t>(b) * C + c] = (expf(row[c] - lse) - (c == y ? 1.f : 0.f)) * gs;
   }
   if (lane == 0) warp_loss[warp] = acc;
   __syncthreads();
@@ -284,6 +285,7 @@ inline int grid_for(int64_t work_items, int threads) {
 }  // namespace
 
 int im2col(const float* x, void* A, bool out_bf16, int B, int C, int Hi, int Wi, int P, int Kpad, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   const int gh = Hi / P, gw = Wi / P, K = C * P * P;
   VB_REQUIRE(gh > 0 && gw > 0 && Kpad >= K, "im2col: bad geometry");
   const bool vec = (P % 4 == 0) && (Wi % 4 == 0) && (Kpad % 4 == 0) && aligned16(x) && aligned16(A);
@@ -301,6 +303,7 @@ int im2col(const float* x, void* A, bool out_bf16, int B, int C, int Hi, int Wi,
 }
 
 int cls_rows(const float* cls, const float* pos, float* out, int B, int T, int E, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   cls_rows_kernel<<<ceil_div(B * E, 256), 256, 0, s>>>(cls, pos, out, B, T, E);
   VB_CHECK_LAUNCH();
   return kOk;
@@ -308,6 +311,7 @@ int cls_rows(const float* cls, const float* pos, float* out, int B, int T, int E
 
 int embed_bwd_reduce(const float* g, float* dpos, float* dcls, void* dY, bool dy_bf16, int B, int T, int E,
                      cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   const int grid = ceil_div(T * E, 128);
   if (dy_bf16) embed_bwd_kernel<bf16><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<bf16*>(dY), B, T, E);
   else embed_bwd_kernel<float><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<float*>(dY), B, T, E);
@@ -316,6 +320,7 @@ int embed_bwd_reduce(const float* g, float* dpos, float* dcls, void* dY, bool dy
 }
 
 int colsum(const void* in, bool in_bf16, int64_t ld, float* out, int M, int N, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   dim3 block(32, 8);
   if (in_bf16 && N % 8 == 0 && ld % 8 == 0 && aligned16(in)) {
     const int gx = ceil_div(N, 256);
@@ -335,6 +340,7 @@ int colsum(const void* in, bool in_bf16, int64_t ld, float* out, int M, int N, c
 }
 
 int gather_row0(const float* x, float* x0, int B, int T, int E, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   gather_row0_kernel<<<ceil_div(B * E, 256), 256, 0, s>>>(x, x0, B, T, E);
   VB_CHECK_LAUNCH();
   return kOk;
@@ -342,6 +348,7 @@ int gather_row0(const float* x, float* x0, int B, int T, int E, cudaStream_t s) 
 
 int head_scatter(const float* dx0, float* g, void* dyn, bool dyn_bf16, const Dropout& drop, int B, int T, int E,
                  cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   const int64_t total = static_cast<int64_t>(B) * T * E;
   if (E % 4 == 0) {
     const int grid = grid_for(total / 4, 256);
@@ -357,11 +364,13 @@ int head_scatter(const float* dx0, float* g, void* dyn, bool dyn_bf16, const Dro
 }
 
 int gelu_forward(const float* x, float* y, int64_t n, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   gelu_fwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, y, n);
   VB_CHECK_LAUNCH();
   return kOk;
 }
 int gelu_backward(const float* x, float* dy_inout, int64_t n, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   gelu_bwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(x, dy_inout, n);
   VB_CHECK_LAUNCH();
   return kOk;
@@ -369,12 +378,14 @@ int gelu_backward(const float* x, float* dy_inout, int64_t n, cudaStream_t s) {
 
 int cross_entropy(const float* logits, const int64_t* labels, float* loss, float* dlogits, int B, int C,
                   float grad_scale, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   ce_kernel<<<1, 1024, 0, s>>>(logits, labels, loss, dlogits, B, C, grad_scale);
   VB_CHECK_LAUNCH();
   return kOk;
 }
 
 int cast_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   VB_REQUIRE(aligned16(in) && (reinterpret_cast<uintptr_t>(out) & 7u) == 0, "cast: unaligned buffers");
   cast_f32_bf16_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, s>>>(in, out, n);
   VB_CHECK_LAUNCH();
@@ -382,6 +393,7 @@ int cast_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t s) {
 }
 
 int mask_cast(const float* g, void* out, bool out_bf16, const Dropout& drop, int64_t n, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   if (out_bf16) mask_cast_kernel<bf16><<<grid_for(n, 256), 256, 0, s>>>(g, static_cast<bf16*>(out), drop, n);
   else mask_cast_kernel<float><<<grid_for(n, 256), 256, 0, s>>>(g, static_cast<float*>(out), drop, n);
   VB_CHECK_LAUNCH();
@@ -389,6 +401,7 @@ int mask_cast(const float* g, void* out, bool out_bf16, const Dropout& drop, int
 }
 
 int dropout_mask(uint8_t* keep, int64_t n, const Dropout& drop, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
   dropout_mask_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, s>>>(keep, n, drop);
   VB_CHECK_LAUNCH();
   return kOk;

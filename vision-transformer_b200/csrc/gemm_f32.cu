@@ -120,6 +120,7 @@ int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int6
   int k_per_split = ceil_div(ceil_div(K, s), FBK) * FBK;
   s = ceil_div(K, k_per_split);
   dim3 grid(ceil_div(N, FBN), ceil_div(M, FBM), s);
+  ProfScope prof(kProfGemmF32, 2.0 * M * N * K, 1, stream);
   VB_REQUIRE(grid.y <= 65535 && grid.z <= 65535, "gemm_f32: grid too large");
   if (a_major == 0 && b_major == 0)
     gemm_f32_kernel<true, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);

@@ -258,6 +258,7 @@ int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, c
     attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
   });
   VB_CHECK_CUDA(attr_err);
+  ProfScope prof(kProfGemmTc, 2.0 * p.M * p.N * p.K, 1, stream);
   const int total = p.m_tiles * p.n_tiles * p.splits;
   const int grid = total < num_sms() ? total : num_sms();
   kern<<<grid, kThreads, Cfg::SMEM_BYTES, stream>>>(ta, tb, p, ep);

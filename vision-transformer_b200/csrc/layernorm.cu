@@ -237,6 +237,7 @@ int ln_forward(const float* x, const float* gamma, const float* beta, void* y, b
   const size_t smem = static_cast<size_t>(nw) * E * sizeof(float);
   VB_REQUIRE(smem <= 200 * 1024, "ln_forward: row too long (E=%d)", E);
   const int grid = ln_grid(M, nw, 4);
+  ProfScope prof(kProfLnFwd, static_cast<double>(M) * E * (4 + (y_bf16 ? 2 : 4)) + 8.0 * M, 1, stream);
   if (y_bf16) {
     if (smem > 48 * 1024) VB_CHECK_CUDA(cudaFuncSetAttribute(ln_fwd_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
     ln_fwd_kernel<bf16><<<grid, nw * 32, smem, stream>>>(x, gamma, beta, static_cast<bf16*>(y), mean, rstd, M, E, eps);
@@ -257,6 +258,9 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
   VB_REQUIRE(smem <= 200 * 1024, "ln_backward: row too long (E=%d)", E);
   // fewer, fatter CTAs than forward: each CTA ends with 2*E global atomics
   const int grid = ln_grid(M, nw, 2);
+  const double es = dy_bf16 ? 2 : 4;  // bytes: x read, dy read, g write (+read when add_to_g), dyn write, stats
+  ProfScope prof(kProfLnBwd, static_cast<double>(M) * E * (4 + es + 4 + (add_to_g ? 4 : 0) + (dyn ? es : 0)) + 8.0 * M,
+                 1, stream);
   const int vpl = ((E & 3) == 0 && E <= 512) ? 4 : ((E & 3) == 0 && E <= 1024) ? 8 : ((E & 3) == 0 && E <= 1536) ? 12 : 0;
 #define VB_LN_BWD(T, V)                                                                                          \
   do {                                                                                                           \

@@ -1,0 +1,347 @@
+"""Data-parallel training step over the stage-level C ABI — the B200 replacement for the step lines of the
+reference's src/train.py (:66 AdamW(lr, weight_decay=1e-4), :81/:93 CrossEntropyLoss, :94-96 zero_grad/backward/step).
+
+One process per GPU.  All parameters live in ONE flat fp32 arena (forward order: embedding, block 0..L-1, head;
+every tensor 256-byte aligned), gradients / Adam moments / bf16 shadow weights in arenas of the same layout, and
+every activation buffer is allocated once: a steady-state step performs no allocation and no host sync.
+
+Multi-GPU: the path shards by images (pure data parallel).  Gradients are summed with NCCL all-reduce on contiguous
+arena slices ("buckets", reverse layer order) issued on a side stream as soon as the backward stage that completes
+a bucket has been enqueued, so the exchange overlaps the rest of backward; the fused AdamW kernel folds the 1/world
+mean into its gradient read.  `cls_tkn_embd` is a per-batch-slot parameter (reference vit.py:31-33) and is averaged
+across ranks like any other parameter, exactly as DistributedDataParallel would treat it.
+"""
+import ctypes
+import os
+import sys
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+if _HERE not in sys.path:
+    sys.path.insert(0, _HERE)
+
+from VisionTransformer import _C  # noqa: E402
+from VisionTransformer import _engine as eng  # noqa: E402
+
+ALIGN = 64  # elements: 256 B in fp32, 128 B in bf16 — keeps every tensor TMA-legal (16 B) in both arenas
+_SECTIONS = ("query", "key", "value")
+
+
+# ---------------------------------------------------------------------------------------------------- layout
+def param_layout(*, C, P, E, H, L, T, B, classes):
+    """[(stage, field, reference-key or None, shape)] in arena order.  stage: 'embed' | int layer | 'head'."""
+    F = 4 * E
+    out = [("embed", "w", "emdeddings.sequence.0.weight", (E, C, P, P)),
+           ("embed", "bias", "emdeddings.sequence.0.bias", (E,)),
+           ("embed", "cls", "emdeddings.cls_tkn_embd", (B, 1, E)),
+           ("embed", "pos", "emdeddings.pos_embd", (1, T, E))]
+    for i in range(L):
+        b = f"transformer_encoder.blocks.{i}."
+        out += [(i, "ln1_w", b + "ln1.weight", (E,)), (i, "ln1_b", b + "ln1.bias", (E,)),
+                (i, "ln2_w", b + "ln2.weight", (E,)), (i, "ln2_b", b + "ln2.bias", (E,)),
+                (i, "w_qkv", None, (3 * E, E)),  # packed from heads.h.{query,key,value}.weight
+                (i, "w_proj", b + "multi_head.proj.weight", (E, E)), (i, "b_proj", b + "multi_head.proj.bias", (E,)),
+                (i, "w_fc1", b + "ffwd.mlp.0.weight", (F, E)), (i, "b_fc1", b + "ffwd.mlp.0.bias", (F,)),
+                (i, "w_fc2", b + "ffwd.mlp.2.weight", (E, F)), (i, "b_fc2", b + "ffwd.mlp.2.bias", (E,))]
+    out += [("head", "w1", "mlp.0.weight", (F, E)), ("head", "b1", "mlp.0.bias", (F,)),
+            ("head", "ln_w", "mlp.2.weight", (F,)), ("head", "ln_b", "mlp.2.bias", (F,)),
+            ("head", "w3", "mlp.3.weight", (classes, F)), ("head", "b3", "mlp.3.bias", (classes,))]
+    return out
+
+
+def arena_offsets(layout):
+    offs, tot = [], 0
+    for _, _, _, shape in layout:
+        n = 1
+        for s in shape:
+            n *= s
+        offs.append((tot, n))
+        tot += (n + ALIGN - 1) // ALIGN * ALIGN
+    return offs, tot
+
+
+def make_buckets(layout, offs, total, bucket_elems):
+    """Contiguous arena slices in the order their gradients complete (head first, embedding last).
+    -> [(start, end, stage_that_completes_it)]"""
+    stages = []  # (stage, start, end) in forward order
+    for (stage, _, _, _), (o, n) in zip(layout, offs):
+        end = (o + n + ALIGN - 1) // ALIGN * ALIGN
+        if stages and stages[-1][0] == stage:
+            stages[-1] = (stage, stages[-1][1], end)
+        else:
+            stages.append((stage, o, end))
+    buckets, cur_end = [], total
+    for stage, start, _ in reversed(stages):
+        if cur_end - start >= bucket_elems or start == 0:   # the embedding stage (offset 0) always closes the last one
+            buckets.append((start, cur_end, stage))
+            cur_end = start
+    return buckets
+
+
+# ---------------------------------------------------------------------------------------------------- trainer
+class DPTrainer:
+    def __init__(self, *, input_channels=3, num_classes=2, image_size=224, patch_size=16, embedding_size=768,
+                 num_heads=12, num_blocks=12, batch_size=256, dtype=torch.bfloat16, device=None, lr=1e-4,
+                 weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8, dropout_p=eng.DROPOUT_P, process_group=None,
+                 world_size=1, bucket_mb=48, seed=0):
+        dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+        eng.require_cuda(torch.empty(0, device=dev), "trainer device")
+        if _C.lib().vitb200_device_ok() != 1:
+            raise RuntimeError("libvitb200 runs on sm_100 (B200) only")
+        self.dev, self.dtype, self.code = dev, dtype, _C.dtype_code(dtype)
+        gh = image_size // patch_size
+        self.B, self.C, self.P, self.E, self.H, self.L = batch_size, input_channels, patch_size, embedding_size, \
+            num_heads, num_blocks
+        self.T, self.classes, self.img = gh * gh + 1, num_classes, image_size
+        self.M = self.B * self.T
+        self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
+        self.dropout_p, self.seed, self.step_no = float(dropout_p), int(seed), 0
+        self.pg, self.world = process_group, int(world_size)
+
+        self.layout = param_layout(C=self.C, P=self.P, E=self.E, H=self.H, L=self.L, T=self.T, B=self.B,
+                                   classes=self.classes)
+        self.offs, self.total = arena_offsets(self.layout)
+        z = lambda dt: torch.zeros(self.total, dtype=dt, device=dev)  # noqa: E731
+        self.p, self.g, self.m, self.v = z(torch.float32), z(torch.float32), z(torch.float32), z(torch.float32)
+        self.shadow = z(torch.bfloat16) if dtype == torch.bfloat16 else None
+        self.buckets = make_buckets(self.layout, self.offs, self.total, int(bucket_mb * (1 << 20) / 4))
+
+        # pointer tables per stage
+        self._views = {}
+        for (stage, field, _, shape), (o, n) in zip(self.layout, self.offs):
+            self._views[(stage, field)] = (o, n, shape)
+        lp = {"w_qkv", "w_proj", "w_fc1", "w_fc2"}
+
+        def ptrs(stage, fields, grads=False, lowp=()):
+            d = {}
+            for f in fields:
+                o, n, _ = self._views[(stage, f)]
+                src = self.g if grads else (self.shadow if (f in lowp and self.shadow is not None) else self.p)
+                d[f] = src[o:o + n]
+            return d
+
+        self.embed_p = ptrs("embed", ("bias", "cls", "pos"))
+        o, n, _ = self._views[("embed", "w")]
+        self.embed_p["w_f32"] = self.p[o:o + n]
+        self.embed_p["w_lp"] = self.shadow[o:o + n] if self.shadow is not None else None
+        self.embed_g = ptrs("embed", _C.EMBED_FIELDS_G, grads=True)
+        self.block_p = [ptrs(i, _C.BLOCK_FIELDS_P, lowp=lp) for i in range(self.L)]
+        self.block_g = [ptrs(i, _C.BLOCK_FIELDS_G, grads=True) for i in range(self.L)]
+        self.head_p = ptrs("head", _C.HEAD_FIELDS)
+        self.head_g = ptrs("head", _C.HEAD_FIELDS, grads=True)
+
+        # activations / scratch, allocated once
+        self.plan = eng.Plan(B=self.B, T=self.T, E=self.E, H=self.H, C=self.C, P=self.P, Hi=self.img, Wi=self.img,
+                             classes=self.classes, L=self.L, dtype=dtype)
+        pl = self.plan
+        self.emb_acts = pl.new_bytes(pl.embed_act_bytes, dev)
+        self.xs = [pl.new_stream_tensor(dev) for _ in range(self.L + 1)]
+        self.blk_acts = [pl.new_bytes(pl.block_act_bytes, dev) for _ in range(self.L)]
+        self.head_acts = pl.new_bytes(pl.head_act_bytes, dev)
+        self.scratch = pl.new_bytes(max(pl.block_scratch_bytes, pl.head_act_bytes), dev)
+        self.gstream = pl.new_stream_tensor(dev)
+        self.dy = [pl.new_lp(dev), pl.new_lp(dev)]
+        self.logits = torch.empty(self.B, self.classes, dtype=torch.float32, device=dev)
+        self.dlogits = torch.empty_like(self.logits)
+        self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
+
+        # host <-> device staging for step_host()
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.comm_stream = torch.cuda.Stream(device=dev) if self.world > 1 else None
+        self._in = [(torch.empty(self.B, self.C, self.img, self.img, dtype=torch.float32, device=dev),
+                     torch.empty(self.B, dtype=torch.int64, device=dev)) for _ in range(2)]
+        self._in_ready = [torch.cuda.Event() for _ in range(2)]
+        self._in_free = [torch.cuda.Event() for _ in range(2)]
+        self._bucket_ev = [torch.cuda.Event() for _ in self.buckets]
+        self._slot = 0
+        self.loss_host = torch.zeros(64, dtype=torch.float32).pin_memory()
+        self._loss_ev = [torch.cuda.Event() for _ in range(64)]
+        self.h2d_bytes = self._in[0][0].numel() * 4 + self.B * 8
+        self.d2h_bytes = 4
+
+    # ------------------------------------------------------------------------------------------ parameters
+    def view(self, stage, field, arena=None):
+        o, n, shape = self._views[(stage, field)]
+        return (self.p if arena is None else arena)[o:o + n].view(shape)
+
+    def load_state_dict(self, sd):
+        """Fill the arena from a state_dict with the REFERENCE's keys (per-head q/k/v packed on the fly)."""
+        E, H = self.E, self.H
+        hs = E // H
+        with torch.no_grad():
+            for stage, field, key, shape in self.layout:
+                dst = self.view(stage, field)
+                if key is not None:
+                    src = sd[key]
+                    if tuple(src.shape) != tuple(shape):
+                        raise RuntimeError(f"size mismatch for {key}: {tuple(src.shape)} vs {tuple(shape)}")
+                    dst.copy_(src.to(self.dev, torch.float32))
+                else:
+                    for s, sec in enumerate(_SECTIONS):
+                        for h in range(H):
+                            k = f"transformer_encoder.blocks.{stage}.multi_head.heads.{h}.{sec}.weight"
+                            dst[s * E + h * hs: s * E + (h + 1) * hs].copy_(sd[k].to(self.dev, torch.float32))
+        self.sync_shadow()
+
+    def init_parameters(self, seed=0):
+        """Random init with the reference's distributions (vit.py:31-36 randn for cls/pos; nn.Linear / nn.Conv2d
+        default Kaiming-uniform(a=sqrt(5)) = U(+-1/sqrt(fan_in)) for weights and biases; LayerNorm 1 / 0)."""
+        gen = torch.Generator(device=self.dev).manual_seed(int(seed))
+        fan_in = {"w": self.C * self.P * self.P, "bias": self.C * self.P * self.P, "w_qkv": self.E, "w_proj": self.E,
+                  "b_proj": self.E, "w_fc1": self.E, "b_fc1": self.E, "w_fc2": 4 * self.E, "b_fc2": 4 * self.E,
+                  "w1": self.E, "b1": self.E, "w3": 4 * self.E, "b3": 4 * self.E}
+        with torch.no_grad():
+            for stage, field, _, shape in self.layout:
+                dst = self.view(stage, field)
+                if field in ("cls", "pos"):
+                    dst.copy_(torch.randn(shape, generator=gen, device=self.dev))
+                elif field in ("ln1_w", "ln2_w", "ln_w"):
+                    dst.fill_(1.0)
+                elif field in ("ln1_b", "ln2_b", "ln_b"):
+                    dst.zero_()
+                else:
+                    bound = fan_in[field] ** -0.5
+                    dst.copy_((torch.rand(shape, generator=gen, device=self.dev) * 2 - 1) * bound)
+        self.sync_shadow()
+
+    def state_dict(self):
+        E, H = self.E, self.H
+        hs = E // H
+        out = {}
+        for stage, field, key, _ in self.layout:
+            t = self.view(stage, field).detach().clone()
+            if key is not None:
+                out[key] = t
+            else:
+                for h in range(H):
+                    for sec in ("key", "query", "value"):
+                        s = _SECTIONS.index(sec)
+                        out[f"transformer_encoder.blocks.{stage}.multi_head.heads.{h}.{sec}.weight"] = \
+                            t[s * E + h * hs: s * E + (h + 1) * hs].clone()
+        return out
+
+    def grads_by_ref_key(self):
+        E, H = self.E, self.H
+        hs = E // H
+        out = {}
+        for stage, field, key, _ in self.layout:
+            t = self.view(stage, field, self.g)
+            if key is not None:
+                out[key] = t
+            else:
+                for h in range(H):
+                    for s, sec in enumerate(_SECTIONS):
+                        out[f"transformer_encoder.blocks.{stage}.multi_head.heads.{h}.{sec}.weight"] = \
+                            t[s * E + h * hs: s * E + (h + 1) * hs]
+        return out
+
+    def sync_shadow(self):
+        if self.shadow is not None:
+            eng.cast_bf16(self.p, self.shadow)
+
+    def broadcast_parameters(self, src=0):
+        if self.world > 1:
+            torch.distributed.broadcast(self.p, src=src, group=self.pg)
+            self.sync_shadow()
+
+    # ------------------------------------------------------------------------------------------ one step
+    def _dims(self, train):
+        seed = (self.seed * 0x9E3779B97F4A7C15 + self.step_no * 0xD1B54A32D192ED03) & 0xFFFFFFFFFFFFFFFF
+        return self.plan.dims(self.dropout_p if train else 0.0, seed)
+
+    def forward(self, images, d):
+        pl = self.plan
+        pl.embed_fwd(d, self.embed_p, images, self.xs[0], self.emb_acts)
+        for i in range(self.L):
+            pl.block_fwd(d, i, self.block_p[i], self.xs[i], self.xs[i + 1], self.blk_acts[i])
+        pl.head_fwd(d, self.head_p, self.xs[self.L], self.logits, self.head_acts)
+        return self.logits
+
+    def _bucket_ready(self, stage, handles):
+        """Launch the all-reduce of every bucket completed by `stage`'s backward (already enqueued)."""
+        if self.world <= 1:
+            return
+        cur = torch.cuda.current_stream(self.dev)
+        for k, (a, b, st) in enumerate(self.buckets):
+            if st == stage:
+                self._bucket_ev[k].record(cur)
+                with torch.cuda.stream(self.comm_stream):
+                    self.comm_stream.wait_event(self._bucket_ev[k])
+                    handles.append(torch.distributed.all_reduce(self.g[a:b], group=self.pg, async_op=True))
+
+    def backward(self, labels, d):
+        pl, L = self.plan, _C.lib()
+        _C.check(L.vitb200_cross_entropy(self.logits.data_ptr(), labels.data_ptr(), self.loss.data_ptr(),
+                                         self.dlogits.data_ptr(), self.B, self.classes, 1.0, _C.stream_ptr()))
+        handles = []
+        dy_a, dy_b = self.dy
+        pl.head_bwd(d, self.head_p, self.head_g, self.head_acts, self.dlogits, self.gstream, dy_a, self.scratch)
+        self._bucket_ready("head", handles)
+        for i in range(self.L - 1, -1, -1):
+            pl.block_bwd(d, i, self.block_p[i], self.block_g[i], self.xs[i], self.blk_acts[i], self.gstream, dy_a,
+                         dy_b, self.scratch)
+            dy_a, dy_b = dy_b, dy_a
+            self._bucket_ready(i, handles)
+        pl.embed_bwd(d, self.embed_g, self.gstream, self.emb_acts)
+        self._bucket_ready("embed", handles)
+        for h in handles:
+            h.wait()  # the compute stream waits for the reduced buckets; the host does not block
+
+    def optimizer_step(self):
+        self.step_no += 1
+        h = _C.AdamWHyper(self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.step_no, 1.0 / self.world)
+        _C.check(_C.lib().vitb200_adamw_flat(self.p.data_ptr(), self.g.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
+                                             None if self.shadow is None else self.shadow.data_ptr(), self.total, h,
+                                             _C.stream_ptr()))
+        self.g.zero_()
+
+    def step(self, images, labels, train=True):
+        """fwd + CE + bwd + grad all-reduce + AdamW on device-resident inputs; returns the (device) loss tensor."""
+        if images.shape != self._in[0][0].shape:
+            raise RuntimeError(f"Sizes of tensors must match: expected image batch {tuple(self._in[0][0].shape)}, got "
+                               f"{tuple(images.shape)} (cls_tkn_embd is per batch slot, reference vit.py:31-33,41)")
+        d = self._dims(train)
+        self.forward(images, d)
+        self.backward(labels, d)
+        self.optimizer_step()
+        return self.loss
+
+    def step_host(self, images_host, labels_host):
+        """Same step from PINNED host tensors: H2D of this step's inputs on a copy stream (double-buffered, so it
+        overlaps the previous step's compute) and an async D2H of the loss.  -> index into self.loss_host."""
+        k = self._slot
+        self._slot ^= 1
+        x, y = self._in[k]
+        cur = torch.cuda.current_stream(self.dev)
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self._in_free[k])
+            x.copy_(images_host, non_blocking=True)
+            y.copy_(labels_host, non_blocking=True)
+            self._in_ready[k].record(self.copy_stream)
+        cur.wait_event(self._in_ready[k])
+        d = self._dims(True)
+        self.forward(x, d)
+        self._in_free[k].record(cur)  # images are only read by the patch gather at the top of forward
+        self.backward(y, d)
+        self.optimizer_step()
+        li = (self.step_no - 1) % self.loss_host.numel()
+        self.loss_host[li:li + 1].copy_(self.loss, non_blocking=True)
+        self._loss_ev[li].record(cur)
+        return li
+
+    def read_loss(self, li):
+        self._loss_ev[li].synchronize()
+        return float(self.loss_host[li])
+
+    # ------------------------------------------------------------------------------------------ accounting
+    def flops_per_image(self):
+        """Algorithmic training FLOPs per image = 3 x forward."""
+        E, T, L, N = self.E, self.T, self.L, self.T - 1
+        fwd = L * T * (24 * E * E + 4 * T * E) + N * 2 * self.C * self.P * self.P * E + 8 * E * E + 8 * E * self.classes
+        return 3.0 * fwd
+
+    def activation_bytes(self):
+        pl = self.plan
+        return (pl.embed_act_bytes + self.L * pl.block_act_bytes + (self.L + 2) * self.M * self.E * 4 +
+                pl.head_act_bytes + max(pl.block_scratch_bytes, pl.head_act_bytes))
