@@ -44,7 +44,7 @@ int vitb200_prof_begin(void);
 int vitb200_prof_end(vitb200_prof_entry* out);
 
 /* Dropout descriptor: p == 0 disables.  Masks are regenerated from (seed, stream, element index) with
- * Philox4x32-10, so backward never stores them.  Replaces nn.Dropout(0.2) at transformer.py:40,47,59. */
+ * Philox4x32-7 (16 random bits per element, one call per 8 elements), so backward never stores them.  Replaces nn.Dropout(0.2) at transformer.py:40,47,59. */
 typedef struct {
   float p;
   uint64_t seed;
@@ -56,7 +56,7 @@ typedef struct {
  *   b_major == MAJOR_K : B stored row-major [N][ldb];   MAJOR_MN: B stored [K][ldb]
  * Epilogue, applied in this order to v = acc:
  *   +bias[n]  ->  relu  ->  (mask_aux[m,n] > 0 ? v : 0)  ->  dropout  ->  +row_add[(m % row_period), n]
- *   -> +residual[orow, n]  ->  store / atomic-add into C[orow, n]
+ *   -> +residual[orow, n]  ->  store / atomic-add into C[orow, n]  (-> column sums into col_sum)
  *   with orow = (m / row_period) * row_group_stride + m % row_period when row_period > 0, else m.
  * in_dtype BF16 runs the tcgen05/TMEM/TMA tensor-core kernel (fp32 accumulation); in_dtype F32 runs the
  * fp32 CUDA-core kernel used for the fp32 parity gate.  `splits` > 1 partitions K and accumulates with
@@ -81,6 +81,7 @@ typedef struct {
   const float* residual; /* [..][ldc] fp32 or NULL (requires out_dtype F32) */
   int splits;            /* split-K factor (atomic accumulate), 0 = auto only when accumulate != 0 */
   int accumulate;        /* 1: C += result via fp32 atomics (C must be fp32) */
+  float* col_sum;        /* [N] fp32 or NULL: col_sum[n] += sum_m (value stored at C[m,n]) — fused bias gradient */
 } vitb200_gemm_args;
 
 int vitb200_gemm(const vitb200_gemm_args* args, void* stream);

@@ -37,7 +37,7 @@ def test_struct_layouts_match_header_sizes():
     assert ctypes.sizeof(_C.Dims) == 64
     assert ctypes.sizeof(_C.AdamWHyper) == 28
     assert ctypes.sizeof(_C.BlockParams) == 11 * 8
-    assert ctypes.sizeof(_C.GemmArgs) == 160
+    assert ctypes.sizeof(_C.GemmArgs) == 168
 
 
 def test_error_channel_without_gpu():

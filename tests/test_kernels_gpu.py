@@ -61,13 +61,14 @@ def test_gemm_epilogue_bias_relu_residual_rowmap(lib, dt):
     ref2 = (A.float() @ B.float().t() + bias).reshape(6, 16, N) + pos
     assert rel_err(out2.reshape(6, 17, N)[:, :16], ref2) < 1e-5
     assert torch.count_nonzero(out2.reshape(6, 17, N)[:, 16]) == 0
-    # low-precision output + aux mask (dReLU)
-    if dt == torch.bfloat16:
-        aux = torch.randn(M, N, device=DEV).to(dt)
-        out3 = torch.empty(M, N, device=DEV, dtype=dt)
-        C.gemm(A, B, out3, M=M, N=N, K=K, mask_aux=aux)
-        ref3 = (A.float() @ B.float().t()) * (aux.float() > 0)
-        assert rel_err(out3, ref3) < 5e-3
+    # output in the operand dtype + aux mask (dReLU) + fused column sums (bias gradient)
+    aux = torch.randn(M, N, device=DEV).to(dt)
+    out3 = torch.empty(M, N, device=DEV, dtype=dt)
+    cs = torch.ones(N, device=DEV)
+    C.gemm(A, B, out3, M=M, N=N, K=K, mask_aux=aux, col_sum=cs)
+    ref3 = (A.float() @ B.float().t()) * (aux.float() > 0)
+    assert rel_err(out3, ref3) < (5e-3 if dt == torch.bfloat16 else 1e-5)
+    assert rel_err(cs - 1, ref3.sum(0)) < 1e-5
 
 
 def test_gemm_dropout_epilogue_matches_exported_mask(lib):

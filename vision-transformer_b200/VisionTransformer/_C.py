@@ -40,6 +40,7 @@ class GemmArgs(ctypes.Structure):
         ("residual", c_void_p),
         ("splits", c_int),
         ("accumulate", c_int),
+        ("col_sum", c_void_p),
     ]
 
 
@@ -199,7 +200,7 @@ def ptr(t):
 
 def gemm(A, B, C, *, a_major=MAJOR_K, b_major=MAJOR_K, M, N, K, bias=None, relu=False, mask_aux=None,
          dropout=(0.0, 0, 0), row_add=None, row_period=0, row_group_stride=0, residual=None, splits=0,
-         accumulate=False, lda=None, ldb=None, ldc=None):
+         accumulate=False, col_sum=None, lda=None, ldb=None, ldc=None):
     """C[m,n] = epilogue(sum_k A(m,k) B(n,k)); see vitb200_gemm_args in include/vitb200.h."""
     a = GemmArgs()
     a.M, a.N, a.K = M, N, K
@@ -216,5 +217,6 @@ def gemm(A, B, C, *, a_major=MAJOR_K, b_major=MAJOR_K, M, N, K, bias=None, relu=
     a.row_period, a.row_group_stride = row_period, row_group_stride
     a.residual = ptr(residual)
     a.splits, a.accumulate = splits, int(accumulate)
+    a.col_sum = ptr(col_sum)
     check(lib().vitb200_gemm(ctypes.byref(a), stream_ptr()))
     return C

@@ -132,6 +132,7 @@ int vitb200_gemm(const vitb200_gemm_args* a, void* stream) {
   ep.row_period = a->row_period;
   ep.row_group_stride = a->row_group_stride;
   ep.accumulate = a->accumulate;
+  ep.col_sum = a->col_sum;
   ep.drop = make_dropout(a->dropout.p, a->dropout.seed, a->dropout.stream);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (a->in_dtype == VITB200_BF16) {

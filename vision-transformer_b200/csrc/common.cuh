@@ -81,12 +81,16 @@ __host__ __device__ __forceinline__ uint32_t mulhi32(uint32_t a, uint32_t b) {
   return static_cast<uint32_t>((static_cast<uint64_t>(a) * b) >> 32);
 #endif
 }
-__host__ __device__ __forceinline__ Philox4 philox4x32_10(uint64_t seed, uint64_t stream, uint64_t ctr) {
+// Philox4x32 with a template round count.  Dropout uses 7 rounds (the fewest that pass BigCrush, Salmon et al.
+// SC'11) and 16 random bits per element, so ONE call decides 8 consecutive elements: that keeps the mask cheap enough
+// to regenerate inside a GEMM epilogue instead of storing it.
+template <int ROUNDS>
+__host__ __device__ __forceinline__ Philox4 philox4x32(uint64_t seed, uint64_t stream, uint64_t ctr) {
   uint32_t c0 = static_cast<uint32_t>(ctr), c1 = static_cast<uint32_t>(ctr >> 32);
   uint32_t c2 = static_cast<uint32_t>(stream), c3 = static_cast<uint32_t>(stream >> 32);
   uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
 #pragma unroll
-  for (int r = 0; r < 10; ++r) {
+  for (int r = 0; r < ROUNDS; ++r) {
     const uint32_t hi0 = mulhi32(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
     const uint32_t hi1 = mulhi32(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
     const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
@@ -95,18 +99,19 @@ __host__ __device__ __forceinline__ Philox4 philox4x32_10(uint64_t seed, uint64_
   }
   return Philox4{c0, c1, c2, c3};
 }
-// keep-probability threshold on a 32-bit word: keep iff word < thresh (thresh = keep * 2^32, saturating).
+// keep-probability threshold on a 16-bit lane: keep iff lane < thresh (thresh = round(keep * 2^16), saturating).
+// p = 0.2 -> 52429 / 65536 = 0.800003 (the 4e-6 excess over 0.8 is far below the sampling noise of any mask).
 __host__ __device__ __forceinline__ uint32_t keep_threshold(float p_drop) {
   const double keep = 1.0 - static_cast<double>(p_drop);
-  const double t = keep * 4294967296.0;
-  return t >= 4294967295.0 ? 0xFFFFFFFFu : static_cast<uint32_t>(t);
+  const double t = keep * 65536.0 + 0.5;
+  return t >= 65536.0 ? 65536u : static_cast<uint32_t>(t);
 }
 
 // Dropout descriptor passed by value to kernels.  p == 0 disables (eval mode / parity mode).
 struct Dropout {
   float p;            // drop probability
   float scale;        // 1 / (1 - p)
-  uint32_t thresh;    // keep iff rnd < thresh
+  uint32_t thresh;    // keep iff 16-bit lane < thresh
   uint64_t seed;
   uint64_t stream;    // distinguishes call sites (layer id * 2 + {proj, fc2})
 };
@@ -119,13 +124,33 @@ inline Dropout make_dropout(float p, uint64_t seed, uint64_t stream) {
   d.stream = stream;
   return d;
 }
-// 4 consecutive elements starting at linear index `idx4*4`: returns multiplicative factors (0 or scale).
-__device__ __forceinline__ void dropout_factors4(const Dropout& d, uint64_t idx4, float (&f)[4]) {
-  const Philox4 r = philox4x32_10(d.seed, d.stream, idx4);
-  f[0] = r.x < d.thresh ? d.scale : 0.f;
-  f[1] = r.y < d.thresh ? d.scale : 0.f;
-  f[2] = r.z < d.thresh ? d.scale : 0.f;
-  f[3] = r.w < d.thresh ? d.scale : 0.f;
+// Element `lin` of a (seed, stream) mask lives in lane lin & 7 of Philox counter lin >> 3; lanes are the 16-bit halves
+// of the four output words in order (x.lo, x.hi, y.lo, y.hi, z.lo, z.hi, w.lo, w.hi).
+__host__ __device__ __forceinline__ uint32_t dropout_keep8(const Dropout& d, uint64_t idx8) {
+  const Philox4 r = philox4x32<7>(d.seed, d.stream, idx8);
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+  uint32_t bits = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    bits |= ((w[i] & 0xFFFFu) < d.thresh ? 1u : 0u) << (2 * i);
+    bits |= ((w[i] >> 16) < d.thresh ? 1u : 0u) << (2 * i + 1);
+  }
+  return bits;
+}
+// multiplicative factors (0 or scale) of 8 consecutive elements starting at linear index idx8 * 8
+__device__ __forceinline__ void dropout_factors8(const Dropout& d, uint64_t idx8, float (&f)[8]) {
+  const uint32_t bits = dropout_keep8(d, idx8);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) f[i] = (bits >> i) & 1u ? d.scale : 0.f;
+}
+// 4 consecutive elements starting at linear index lin4 (lin4 % 4 == 0)
+__device__ __forceinline__ void dropout_factors4(const Dropout& d, uint64_t lin4, float (&f)[4]) {
+  const uint32_t bits = dropout_keep8(d, lin4 >> 3) >> (lin4 & 4);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) f[i] = (bits >> i) & 1u ? d.scale : 0.f;
+}
+__device__ __forceinline__ float dropout_factor1(const Dropout& d, uint64_t lin) {
+  return (dropout_keep8(d, lin >> 3) >> (lin & 7)) & 1u ? d.scale : 0.f;
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -148,7 +148,7 @@ __global__ void head_scatter_kernel(const float* __restrict__ dx0, float* __rest
       float o[4] = {v.x, v.y, v.z, v.w};
       if (drop.p > 0.f && t == 0) {
         float f[4];
-        dropout_factors4(drop, static_cast<uint64_t>(i4), f);
+        dropout_factors4(drop, static_cast<uint64_t>(lin), f);
 #pragma unroll
         for (int j = 0; j < 4; ++j) o[j] *= f[j];
       }
@@ -177,9 +177,7 @@ __global__ void head_scatter_scalar_kernel(const float* __restrict__ dx0, float*
     g[lin] = v;
     if (dyn != nullptr) {
       if (drop.p > 0.f) {
-        const Philox4 r = philox4x32_10(drop.seed, drop.stream, static_cast<uint64_t>(lin) >> 2);
-        const uint32_t w = (lin & 3) == 0 ? r.x : (lin & 3) == 1 ? r.y : (lin & 3) == 2 ? r.z : r.w;
-        v *= w < drop.thresh ? drop.scale : 0.f;
+        v *= dropout_factor1(drop, static_cast<uint64_t>(lin));
       }
       dyn[lin] = from_f32<OutT>(v);
     }
@@ -252,11 +250,10 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, bf16* __restr
 // keep[i] = 1 if element i of the (seed, stream) dropout stream is kept.  Test/debug export of the mask that the
 // fused epilogues regenerate on the fly.
 __global__ void dropout_mask_kernel(uint8_t* __restrict__ keep, int64_t n, const Dropout drop) {
-  for (int64_t i4 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i4 * 4 < n;
-       i4 += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const Philox4 r = philox4x32_10(drop.seed, drop.stream, static_cast<uint64_t>(i4));
-    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
-    for (int j = 0; j < 4 && i4 * 4 + j < n; ++j) keep[i4 * 4 + j] = w[j] < drop.thresh ? 1 : 0;
+  for (int64_t i8 = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i8 * 8 < n;
+       i8 += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const uint32_t bits = dropout_keep8(drop, static_cast<uint64_t>(i8));
+    for (int j = 0; j < 8 && i8 * 8 + j < n; ++j) keep[i8 * 8 + j] = (bits >> j) & 1u;
   }
 }
 
@@ -268,9 +265,7 @@ __global__ void mask_cast_kernel(const float* __restrict__ g, OutT* __restrict__
        i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     float v = g[i];
     if (drop.p > 0.f) {
-      const Philox4 r = philox4x32_10(drop.seed, drop.stream, static_cast<uint64_t>(i) >> 2);
-      const uint32_t w = (i & 3) == 0 ? r.x : (i & 3) == 1 ? r.y : (i & 3) == 2 ? r.z : r.w;
-      v *= w < drop.thresh ? drop.scale : 0.f;
+      v *= dropout_factor1(drop, static_cast<uint64_t>(i));
     }
     out[i] = from_f32<OutT>(v);
   }
@@ -402,7 +397,7 @@ int mask_cast(const float* g, void* out, bool out_bf16, const Dropout& drop, int
 
 int dropout_mask(uint8_t* keep, int64_t n, const Dropout& drop, cudaStream_t s) {
   ProfScope prof(kProfEltwise, 0.0, 1, s);
-  dropout_mask_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, s>>>(keep, n, drop);
+  dropout_mask_kernel<<<grid_for(n / 8 + 1, 256), 256, 0, s>>>(keep, n, drop);
   VB_CHECK_LAUNCH();
   return kOk;
 }

@@ -52,7 +52,7 @@ struct Lin {
 GemmEpilogue make_ep(void* C, int64_t ldc) {
   GemmEpilogue ep;
   ep.bias = nullptr; ep.mask_aux = nullptr; ep.row_add = nullptr; ep.residual = nullptr;
-  ep.C = C; ep.ldc = ldc; ep.relu = 0; ep.row_period = 0; ep.row_group_stride = 0; ep.accumulate = 0;
+  ep.C = C; ep.ldc = ldc; ep.relu = 0; ep.row_period = 0; ep.row_group_stride = 0; ep.accumulate = 0; ep.col_sum = nullptr;
   ep.drop = make_dropout(0.f, 0, 0);
   return ep;
 }
@@ -340,13 +340,12 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
   VB_PROPAGATE(colsum(dy_in, bf, E, gr->b_fc2, M, E, s));
   // dh[M,4E] = (dy W2) * (h > 0)
   l = Lin(); l.M = M; l.N = F; l.K = E; l.b_major = 1; l.A = dy_in; l.lda = E; l.B = p->w_fc2; l.ldb = F;
-  l.ep = make_ep(sc.s1, F); l.ep.mask_aux = a.h; l.out_f32 = !bf;
+  l.ep = make_ep(sc.s1, F); l.ep.mask_aux = a.h; l.ep.col_sum = gr->b_fc1; l.out_f32 = !bf;  // db1 += colsum(dh), fused
   VB_PROPAGATE(run_lin(bf, l, s));
-  // dW1[4E,E] += dh^T ln2 ; db1 += colsum(dh)
+  // dW1[4E,E] += dh^T ln2
   l = Lin(); l.M = F; l.N = E; l.K = M; l.a_major = 1; l.b_major = 1; l.A = sc.s1; l.lda = F; l.B = a.ln2; l.ldb = E;
   l.ep = make_ep(gr->w_fc1, E); l.ep.accumulate = 1; l.out_f32 = true;
   VB_PROPAGATE(run_lin(bf, l, s));
-  VB_PROPAGATE(colsum(sc.s1, bf, F, gr->b_fc1, M, F, s));
   // d(ln2 out)[M,E] = dh W1
   l = Lin(); l.M = M; l.N = E; l.K = F; l.b_major = 1; l.A = sc.s1; l.lda = F; l.B = p->w_fc1; l.ldb = E;
   l.ep = make_ep(sc.s2, E); l.out_f32 = !bf;

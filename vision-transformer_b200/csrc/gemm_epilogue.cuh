@@ -16,8 +16,23 @@ struct GemmEpilogue {
   int row_period;          // 0 = identity
   int row_group_stride;
   int accumulate;          // atomic add into fp32 C
+  float* col_sum;          // [N] or null: col_sum[n] += sum over rows of the stored value (bias gradients)
   Dropout drop;
 };
+
+// Compile-time epilogue specialisation: a kernel instantiated with EPI != kEpiGeneric evaluates each option as a
+// constant (the hot call sites of the training step); kEpiGeneric keeps every option a run-time test so that any
+// combination reachable through the C ABI still works.
+enum : uint32_t {
+  kEpiBias = 1u, kEpiRelu = 2u, kEpiMask = 4u, kEpiDrop = 8u, kEpiRowMap = 16u, kEpiResidual = 32u, kEpiAccum = 64u,
+  kEpiColSum = 128u, kEpiGeneric = 0x80000000u
+};
+inline uint32_t epi_flags(const GemmEpilogue& ep) {
+  return (ep.bias ? kEpiBias : 0u) | (ep.relu ? kEpiRelu : 0u) | (ep.mask_aux ? kEpiMask : 0u) |
+         (ep.drop.p > 0.f ? kEpiDrop : 0u) | ((ep.row_add || ep.row_period > 0) ? kEpiRowMap : 0u) |
+         (ep.residual ? kEpiResidual : 0u) | (ep.accumulate ? kEpiAccum : 0u) | (ep.col_sum ? kEpiColSum : 0u);
+}
+#define VB_EPI(flag, cond) ((EPI == ::vb::kEpiGeneric) ? (cond) : ((EPI & (flag)) != 0u))
 
 __device__ __forceinline__ int64_t epi_out_row(const GemmEpilogue& ep, int m) {
   if (ep.row_period > 0) return static_cast<int64_t>(m / ep.row_period) * ep.row_group_stride + (m % ep.row_period);
@@ -29,46 +44,60 @@ __device__ __forceinline__ void red_add_f32x4(float* addr, float a, float b, flo
                : "memory");
 }
 
-// Apply the epilogue to 8 consecutive columns [n, n+8) of logical row m and write them.
-// Requirements: n % 8 == 0, N % 8 == 0, ldc % 8 == 0, all base pointers 16-byte aligned.
-template <typename OutT>
-__device__ __forceinline__ void epilogue_store8(const GemmEpilogue& ep, int m, int n, int N, float (&v)[8]) {
-  if (ep.bias != nullptr) {
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(ep.bias + n));
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(ep.bias + n + 4));
-    v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-    v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+// Read-side operands of the epilogue for 8 consecutive columns of one output row, fetched EARLY (before the
+// accumulator is available) so that their latency overlaps the TMEM drain instead of serialising behind it.
+struct EpiPre {
+  float4 r0, r1;   // residual
+  uint4 a0, a1;    // mask_aux: 8 x bf16 in a0, or 8 x fp32 in a0|a1
+};
+template <typename OutT, uint32_t EPI>
+__device__ __forceinline__ void epilogue_fetch8(const GemmEpilogue& ep, int64_t off, EpiPre& pre) {
+  if (VB_EPI(kEpiResidual, ep.residual != nullptr)) {
+    pre.r0 = __ldg(reinterpret_cast<const float4*>(ep.residual + off));
+    pre.r1 = __ldg(reinterpret_cast<const float4*>(ep.residual + off + 4));
   }
-  if (ep.relu) {
+  if (VB_EPI(kEpiMask, ep.mask_aux != nullptr)) {
+    const OutT* aux = reinterpret_cast<const OutT*>(ep.mask_aux) + off;
+    pre.a0 = __ldg(reinterpret_cast<const uint4*>(aux));
+    if constexpr (sizeof(OutT) == 4) pre.a1 = __ldg(reinterpret_cast<const uint4*>(aux) + 1);
+  }
+}
+
+// Apply the epilogue to 8 consecutive columns [n, n+8) of logical row m (output offset `off`) and write them.
+// bias8: the 8 bias values of these columns (zeros when ep.bias is null).  v is left holding the stored values.
+// Requirements: n % 8 == 0, N % 8 == 0, ldc % 8 == 0, all base pointers 16-byte aligned.
+template <typename OutT, uint32_t EPI>
+__device__ __forceinline__ void epilogue_finish8(const GemmEpilogue& ep, int m, int n, int N, int64_t off,
+                                                 float (&v)[8], const EpiPre& pre, const float (&bias8)[8]) {
+  if (VB_EPI(kEpiBias, true)) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] += bias8[i];
+  }
+  if (VB_EPI(kEpiRelu, ep.relu)) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
   }
-  const int64_t orow = epi_out_row(ep, m);
-  const int64_t off = orow * ep.ldc + n;
-  if (ep.mask_aux != nullptr) {
-    const OutT* aux = reinterpret_cast<const OutT*>(ep.mask_aux) + off;
+  if (VB_EPI(kEpiMask, ep.mask_aux != nullptr)) {
     if constexpr (sizeof(OutT) == 2) {
-      const uint4 raw = *reinterpret_cast<const uint4*>(aux);
-      const bf16* h = reinterpret_cast<const bf16*>(&raw);
+      const bf16* h = reinterpret_cast<const bf16*>(&pre.a0);
 #pragma unroll
       for (int i = 0; i < 8; ++i) v[i] = __bfloat162float(h[i]) > 0.f ? v[i] : 0.f;
     } else {
-      const float4 a0 = *reinterpret_cast<const float4*>(aux);
-      const float4 a1 = *reinterpret_cast<const float4*>(aux + 4);
-      const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float a[8] = {__uint_as_float(pre.a0.x), __uint_as_float(pre.a0.y), __uint_as_float(pre.a0.z),
+                          __uint_as_float(pre.a0.w), __uint_as_float(pre.a1.x), __uint_as_float(pre.a1.y),
+                          __uint_as_float(pre.a1.z), __uint_as_float(pre.a1.w)};
 #pragma unroll
       for (int i = 0; i < 8; ++i) v[i] = a[i] > 0.f ? v[i] : 0.f;
     }
   }
-  if (ep.drop.p > 0.f) {
+  if (VB_EPI(kEpiDrop, ep.drop.p > 0.f)) {
     const uint64_t lin = static_cast<uint64_t>(m) * static_cast<uint64_t>(N) + static_cast<uint64_t>(n);
-    float f0[4], f1[4];
-    dropout_factors4(ep.drop, lin >> 2, f0);
-    dropout_factors4(ep.drop, (lin >> 2) + 1, f1);
+    float f[8];
+    dropout_factors8(ep.drop, lin >> 3, f);   // lin % 8 == 0 (n % 8 == 0 and N % 8 == 0)
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { v[i] *= f0[i]; v[4 + i] *= f1[i]; }
+    for (int i = 0; i < 8; ++i) v[i] *= f[i];
   }
-  if (ep.row_add != nullptr) {
+  if (VB_EPI(kEpiRowMap, ep.row_add != nullptr) && ep.row_add != nullptr) {
     const int pr = ep.row_period > 0 ? (m % ep.row_period) : m;
     const float* ra = ep.row_add + static_cast<int64_t>(pr) * N + n;
     const float4 a0 = __ldg(reinterpret_cast<const float4*>(ra));
@@ -76,11 +105,9 @@ __device__ __forceinline__ void epilogue_store8(const GemmEpilogue& ep, int m, i
     v[0] += a0.x; v[1] += a0.y; v[2] += a0.z; v[3] += a0.w;
     v[4] += a1.x; v[5] += a1.y; v[6] += a1.z; v[7] += a1.w;
   }
-  if (ep.residual != nullptr) {
-    const float4 r0 = *reinterpret_cast<const float4*>(ep.residual + off);
-    const float4 r1 = *reinterpret_cast<const float4*>(ep.residual + off + 4);
-    v[0] += r0.x; v[1] += r0.y; v[2] += r0.z; v[3] += r0.w;
-    v[4] += r1.x; v[5] += r1.y; v[6] += r1.z; v[7] += r1.w;
+  if (VB_EPI(kEpiResidual, ep.residual != nullptr)) {
+    v[0] += pre.r0.x; v[1] += pre.r0.y; v[2] += pre.r0.z; v[3] += pre.r0.w;
+    v[4] += pre.r1.x; v[5] += pre.r1.y; v[6] += pre.r1.z; v[7] += pre.r1.w;
   }
   if constexpr (sizeof(OutT) == 2) {
     uint4 o;
@@ -89,7 +116,7 @@ __device__ __forceinline__ void epilogue_store8(const GemmEpilogue& ep, int m, i
     *reinterpret_cast<uint4*>(reinterpret_cast<bf16*>(ep.C) + off) = o;
   } else {
     float* c = reinterpret_cast<float*>(ep.C) + off;
-    if (ep.accumulate) {
+    if (VB_EPI(kEpiAccum, ep.accumulate)) {
       red_add_f32x4(c, v[0], v[1], v[2], v[3]);
       red_add_f32x4(c + 4, v[4], v[5], v[6], v[7]);
     } else {

@@ -11,16 +11,14 @@ namespace {
 
 constexpr int FBM = 128, FBN = 128, FBK = 8, FTHREADS = 256;
 
-__device__ __forceinline__ void epilogue_store1_f32(const GemmEpilogue& ep, int m, int n, int N, float v) {
+__device__ __forceinline__ float epilogue_store1_f32(const GemmEpilogue& ep, int m, int n, int N, float v) {
   if (ep.bias != nullptr) v += __ldg(ep.bias + n);
   if (ep.relu) v = fmaxf(v, 0.f);
   const int64_t off = epi_out_row(ep, m) * ep.ldc + n;
   if (ep.mask_aux != nullptr) v = reinterpret_cast<const float*>(ep.mask_aux)[off] > 0.f ? v : 0.f;
   if (ep.drop.p > 0.f) {
     const uint64_t lin = static_cast<uint64_t>(m) * static_cast<uint64_t>(N) + static_cast<uint64_t>(n);
-    const Philox4 r = philox4x32_10(ep.drop.seed, ep.drop.stream, lin >> 2);
-    const uint32_t w = (lin & 3) == 0 ? r.x : (lin & 3) == 1 ? r.y : (lin & 3) == 2 ? r.z : r.w;
-    v *= w < ep.drop.thresh ? ep.drop.scale : 0.f;
+    v *= dropout_factor1(ep.drop, lin);
   }
   if (ep.row_add != nullptr) {
     const int pr = ep.row_period > 0 ? (m % ep.row_period) : m;
@@ -30,6 +28,7 @@ __device__ __forceinline__ void epilogue_store1_f32(const GemmEpilogue& ep, int 
   float* c = reinterpret_cast<float*>(ep.C) + off;
   if (ep.accumulate) atomicAdd(c, v);
   else *c = v;
+  return v;
 }
 
 // A(m,k) = A[m*sam + k*sak], B(n,k) = B[n*sbn + k*sbk]
@@ -91,6 +90,9 @@ gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
     __syncthreads();
   }
 
+  float cs[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) cs[j] = 0.f;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int m = m0 + ty * 8 + i;
@@ -98,7 +100,14 @@ gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int n = n0 + tx * 8 + j;
-      if (n < N) epilogue_store1_f32(ep, m, n, N, acc[i][j]);
+      if (n < N) cs[j] += epilogue_store1_f32(ep, m, n, N, acc[i][j]);
+    }
+  }
+  if (ep.col_sum != nullptr) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int n = n0 + tx * 8 + j;
+      if (n < N) atomicAdd(ep.col_sum + n, cs[j]);
     }
   }
 }

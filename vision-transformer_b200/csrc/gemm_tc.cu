@@ -6,6 +6,7 @@
 // Replaces the cuBLAS calls behind nn.Linear at reference transformer.py:22-28,46,56-58 and the patch
 // Conv2d at vit.py:21-28 (as an im2col GEMM), plus their autograd backward GEMMs.
 #include <cuda.h>
+#include <cstdlib>
 #include <mutex>
 
 #include "common.cuh"
@@ -20,7 +21,8 @@ constexpr int BM = 128;          // UMMA M (cta_group::1)
 constexpr int BK = 64;           // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
 constexpr int kStages = 4;
-constexpr int kThreads = 192;
+constexpr int kEpiWarps = 8;         // 2 per TMEM lane quarter: each pair splits the accumulator columns
+constexpr int kThreads = 64 + kEpiWarps * 32;
 
 template <int BN>
 struct TileCfg {
@@ -28,7 +30,8 @@ struct TileCfg {
   static constexpr int B_BYTES = BN * BK * 2;       // 32 KB @ BN=256
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_BYTES = 256;
-  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + BAR_BYTES + 1024;  // +1024 alignment slack
+  static constexpr int STG_BYTES = kEpiWarps * 32 * 128;   // per epilogue warp: 32 rows x 32 fp32 transpose buffer
+  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + BAR_BYTES + STG_BYTES + 1024;  // +1024 alignment slack
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
@@ -38,7 +41,7 @@ struct TcParams {
   int splits, kb_per_split, kb_total;
 };
 
-template <int AMAJ, int BMAJ, int BN, typename OutT>
+template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                const TcParams p, const GemmEpilogue ep) {
@@ -65,7 +68,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tmem_full[s], 1);
-      ptx::mbar_init(&tmem_empty[s], 4);
+      ptx::mbar_init(&tmem_empty[s], kEpiWarps);
     }
     ptx::fence_barrier_init();
   }
@@ -151,8 +154,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (4 warps, 1 row / thread)
-    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    // ------------------------------------------------------------------ epilogue (8 warps)
+    // Warp (q, half) drains TMEM lanes [32q, 32q+32) x accumulator columns [half*BN/2, (half+1)*BN/2) in chunks of
+    // 32 columns: tcgen05.ld gives each thread ONE row, a swizzled warp-private shared-memory transpose turns that
+    // into "4 lanes cover 32 consecutive columns of a row", so residual / mask loads and the C stores are coalesced.
+    const int ew = warp - 2;
+    const int q = warp & 3;              // TMEM lane quarter this warp may read
+    const int half = ew >> 2;
+    const uint32_t stg_s = ptx::smem_u32(smem + kStages * Cfg::STAGE_BYTES + Cfg::BAR_BYTES) + static_cast<uint32_t>(ew * 4096);
+    const int rsub = lane >> 2;          // row within a pass of 8 rows
+    const int cg = lane & 3;             // 8-column group within the chunk
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
@@ -160,30 +171,113 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       const int tile = w - split * tiles;
       const int m_blk = tile / p.n_tiles;
       const int n_blk = tile - m_blk * p.n_tiles;
-      const int m = m_blk * BM + q * 32 + lane;
+      const int m0 = m_blk * BM + q * 32;
+      // While the mainloop of this tile is still running: pull the epilogue's read-side operands (residual rows,
+      // dReLU mask rows) of my 32 x (BN/2) sub-tile into L2, one row segment per lane.
+      if (VB_EPI(kEpiResidual | kEpiMask, ep.residual != nullptr || ep.mask_aux != nullptr)) {
+        const int m = m0 + lane;
+        const int nb = n_blk * BN + half * (BN / 2);
+        if (m < p.M && nb < p.N) {
+          const int ncols = min(BN / 2, p.N - nb);
+          const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
+          const int64_t off = orow * ep.ldc + nb;
+          if (VB_EPI(kEpiResidual, ep.residual != nullptr))
+            ptx::prefetch_l2_bulk(ep.residual + off, static_cast<uint32_t>(ncols) * 4u);
+          if (VB_EPI(kEpiMask, ep.mask_aux != nullptr))
+            ptx::prefetch_l2_bulk(reinterpret_cast<const OutT*>(ep.mask_aux) + off,
+                                  static_cast<uint32_t>(ncols) * static_cast<uint32_t>(sizeof(OutT)));
+        }
+      }
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      const int nb = n_blk * BN + half * (BN / 2);     // first column of my half
+      constexpr int NCH = BN / 2 / 32;
+      uint32_t r[32];
+      if (nb < p.N) ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * (BN / 2)), r);
+      // Read-side operands (residual / dReLU mask) are fetched ONE CHUNK AHEAD into registers: their L2 latency is
+      // covered by the previous chunk's transpose + stores instead of stalling every chunk.
+      EpiPre pre_nx[4];
+      auto fetch_chunk = [&](int cc, EpiPre (&dst)[4]) {
+        const int nn = nb + cc * 32 + cg * 8;
+        if (nn >= p.N) return;
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) {
+          const int m = m0 + pass * 8 + rsub;
+          const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
+          if (m < p.M) epilogue_fetch8<OutT, EPI>(ep, orow * ep.ldc + nn, dst[pass]);
+        }
+      };
+      fetch_chunk(0, pre_nx);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        const int n0 = n_blk * BN + c * 32;
-        if (n0 >= p.N) break;                      // warp-uniform
-        uint32_t r[32];
-        ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(c * 32), r);
+      for (int c = 0; c < NCH; ++c) {
+        const int n0 = nb + c * 32;
+        if (n0 >= p.N) break;                          // warp-uniform
+        const int n = n0 + cg * 8;
+        const bool ncol_ok = n < p.N;
+        EpiPre pre[4];
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) pre[pass] = pre_nx[pass];
+        if (c + 1 < NCH) fetch_chunk(c + 1, pre_nx);
+        int64_t off[4];
+        float bias8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) bias8[i] = 0.f;
+        if (VB_EPI(kEpiBias, ep.bias != nullptr) && ncol_ok) {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(ep.bias + n));
+          const float4 b1 = __ldg(reinterpret_cast<const float4*>(ep.bias + n + 4));
+          bias8[0] = b0.x; bias8[1] = b0.y; bias8[2] = b0.z; bias8[3] = b0.w;
+          bias8[4] = b1.x; bias8[5] = b1.y; bias8[6] = b1.z; bias8[7] = b1.w;
+        }
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) {
+          const int m = m0 + pass * 8 + rsub;
+          const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
+          off[pass] = orow * ep.ldc + n;
+        }
+        // (2) accumulator chunk: TMEM -> registers (one row per thread) -> swizzled shared-memory transpose
         ptx::tmem_ld_wait();
-        if (m < p.M) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const int n = n0 + j * 8;
-            if (n < p.N) {
-              float v[8];
+        for (int j = 0; j < 8; ++j)                    // my row, 16-byte chunk j -> physical chunk j ^ (row & 7)
+          ptx::sts128(stg_s + static_cast<uint32_t>(lane * 128 + ((j ^ (lane & 7)) << 4)), r[4 * j], r[4 * j + 1],
+                      r[4 * j + 2], r[4 * j + 3]);
+        __syncwarp();
+        // (3) next chunk's TMEM load flies while this chunk is finished
+        if (c + 1 < NCH && n0 + 32 < p.N)
+          ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * (BN / 2) + (c + 1) * 32), r);
+        float cs[8];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[j * 8 + i]);
-              epilogue_store8<OutT>(ep, m, n, p.N, v);
+        for (int i = 0; i < 8; ++i) cs[i] = 0.f;
+#pragma unroll
+        for (int pass = 0; pass < 4; ++pass) {
+          const int R = pass * 8 + rsub;
+          const int m = m0 + R;
+          const float4 lo = ptx::lds128(stg_s + static_cast<uint32_t>(R * 128 + (((2 * cg) ^ (R & 7)) << 4)));
+          const float4 hi = ptx::lds128(stg_s + static_cast<uint32_t>(R * 128 + (((2 * cg + 1) ^ (R & 7)) << 4)));
+          if (m < p.M && ncol_ok) {
+            float v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
+            epilogue_finish8<OutT, EPI>(ep, m, n, p.N, off[pass], v, pre[pass], bias8);
+            if (VB_EPI(kEpiColSum, ep.col_sum != nullptr)) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) cs[i] += v[i];
             }
           }
         }
+        if (VB_EPI(kEpiColSum, ep.col_sum != nullptr)) {   // warp-uniform
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            cs[i] += __shfl_xor_sync(0xffffffffu, cs[i], 4);
+            cs[i] += __shfl_xor_sync(0xffffffffu, cs[i], 8);
+            cs[i] += __shfl_xor_sync(0xffffffffu, cs[i], 16);
+          }
+          if (rsub == 0 && ncol_ok) {
+            red_add_f32x4(ep.col_sum + n, cs[0], cs[1], cs[2], cs[3]);
+            red_add_f32x4(ep.col_sum + n + 4, cs[4], cs[5], cs[6], cs[7]);
+          }
+        }
+        __syncwarp();
       }
+      ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
@@ -247,11 +341,11 @@ int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t col
   return kOk;
 }
 
-template <int AMAJ, int BMAJ, int BN, typename OutT>
+template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI>
 int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
               cudaStream_t stream) {
   using Cfg = TileCfg<BN>;
-  auto kern = gemm_tc_kernel<AMAJ, BMAJ, BN, OutT>;
+  auto kern = gemm_tc_kernel<AMAJ, BMAJ, BN, OutT, EPI>;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
@@ -303,13 +397,34 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   p.kb_per_split = ceil_div(p.kb_total, s);
   p.splits = ceil_div(p.kb_total, p.kb_per_split);
 
+  // Hot call sites of the training step get a compile-time-specialised epilogue; anything else runs the generic one.
+  const uint32_t f = epi_flags(ep);
+#define VB_TC(AM, BM_, T, FL) \
+  if (f == (FL)) return launch_tc<AM, BM_, BN, T, (FL)>(ta, tb, p, ep, stream)
   if (a_major == 0 && b_major == 0) {
-    return out_f32 ? launch_tc<0, 0, BN, float>(ta, tb, p, ep, stream) : launch_tc<0, 0, BN, bf16>(ta, tb, p, ep, stream);
+    if (out_f32) {
+      VB_TC(0, 0, float, 0u);
+      VB_TC(0, 0, float, kEpiBias | kEpiResidual);
+      VB_TC(0, 0, float, kEpiBias | kEpiDrop | kEpiResidual);
+      VB_TC(0, 0, float, kEpiBias | kEpiRowMap);
+      return launch_tc<0, 0, BN, float, kEpiGeneric>(ta, tb, p, ep, stream);
+    }
+    VB_TC(0, 0, bf16, 0u);
+    VB_TC(0, 0, bf16, kEpiBias | kEpiRelu);
+    return launch_tc<0, 0, BN, bf16, kEpiGeneric>(ta, tb, p, ep, stream);
   } else if (a_major == 0 && b_major == 1) {
-    return out_f32 ? launch_tc<0, 1, BN, float>(ta, tb, p, ep, stream) : launch_tc<0, 1, BN, bf16>(ta, tb, p, ep, stream);
+    if (out_f32) return launch_tc<0, 1, BN, float, kEpiGeneric>(ta, tb, p, ep, stream);
+    VB_TC(0, 1, bf16, 0u);
+    VB_TC(0, 1, bf16, kEpiMask | kEpiColSum);
+    return launch_tc<0, 1, BN, bf16, kEpiGeneric>(ta, tb, p, ep, stream);
   } else if (a_major == 1 && b_major == 1) {
-    return out_f32 ? launch_tc<1, 1, BN, float>(ta, tb, p, ep, stream) : launch_tc<1, 1, BN, bf16>(ta, tb, p, ep, stream);
+    if (out_f32) {
+      VB_TC(1, 1, float, kEpiAccum);
+      return launch_tc<1, 1, BN, float, kEpiGeneric>(ta, tb, p, ep, stream);
+    }
+    return launch_tc<1, 1, BN, bf16, kEpiGeneric>(ta, tb, p, ep, stream);
   }
+#undef VB_TC
   set_error("gemm_tc: operand major combination a=%d b=%d not instantiated", a_major, b_major);
   return kErrUnsupported;
 }

@@ -161,7 +161,7 @@ ln_bwd_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, const flo
         if (dyn != nullptr) {
           if (drop.p > 0.f) {
             float f[4];
-            dropout_factors4(drop, (static_cast<uint64_t>(base) >> 2) + i, f);
+            dropout_factors4(drop, static_cast<uint64_t>(base) + 4 * i, f);
 #pragma unroll
             for (int j = 0; j < 4; ++j) o[j] *= f[j];
           }
@@ -186,9 +186,7 @@ ln_bwd_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, const flo
         if (dyn != nullptr) {
           if (drop.p > 0.f) {
             const uint64_t lin = static_cast<uint64_t>(base) + i;
-            const Philox4 r = philox4x32_10(drop.seed, drop.stream, lin >> 2);
-            const uint32_t w = (lin & 3) == 0 ? r.x : (lin & 3) == 1 ? r.y : (lin & 3) == 2 ? r.z : r.w;
-            o *= w < drop.thresh ? drop.scale : 0.f;
+            o *= dropout_factor1(drop, lin);
           }
           dyn[base + i] = from_f32<DyT>(o);
         }
