@@ -4,7 +4,10 @@
 // and reduced with warp shuffles; K/V (or Q/dO) tiles stream through a double-buffered cp.async pipeline.
 // Semantics: reference transformer.py:20-31,44-45 — logits MULTIPLIED by sqrt(head_size) (scale is an
 // argument), no mask, heads are column slices of the packed [M,3E] qkv buffer, output concatenated in [M,E].
+#include <cstdlib>
+
 #include "common.cuh"
+#include "kernels.h"
 
 namespace vb {
 
@@ -443,8 +446,18 @@ int bwd_launch(const bf16* qkv, const bf16* d_o, const float* lse, const float* 
 int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B, int T, int H, int hs,
                cudaStream_t stream);
 
+// VITB200_ATTN=legacy forces the mma.sync kernels everywhere (A/B comparison and tests of the generic path).
+static bool use_tc_attention(int T, int hs) {
+  static const bool legacy = [] {
+    const char* e = getenv("VITB200_ATTN");
+    return e != nullptr && e[0] == 'l';
+  }();
+  return !legacy && attn_tc_supported(T, hs);
+}
+
 int attn_bf16_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
                       cudaStream_t stream) {
+  if (use_tc_attention(T, hs)) return attn_tc_forward(qkv, out, lse, B, T, H, hs, scale, stream);
   switch (hs) {
     case 16: return fwd_launch<16>(qkv, out, lse, B, T, H, scale, stream);
     case 32: return fwd_launch<32>(qkv, out, lse, B, T, H, scale, stream);

@@ -1,0 +1,295 @@
+// Fused self-attention on the 5th-gen tensor cores for the ViT shapes (head_size 64, T <= 256 tokens: the whole key
+// axis of one (image, head) fits ONE tcgen05.mma in N, so softmax is single-pass, never online).
+//
+//   S = Q K^T            tcgen05.mma SS: A = Q tile [128 x 64] (smem, K-major), B = K [TP x 64] (smem, K-major),
+//                        D = S [128 lanes x TP fp32 columns] in TENSOR MEMORY            (TP = T rounded up to 16)
+//   P = exp2(S*c - max)  softmax warps: one thread per query row reads its row of S with tcgen05.ld, finds the
+//                        max, exponentiates, and writes P back IN PLACE as packed bf16 (tcgen05.st) over S
+//   O = P V              tcgen05.mma TS: A = P straight from tensor memory, B = V [TP x 64] (smem, MN-major),
+//                        D = O [128 x 64] in the columns of the S region that P no longer needs
+//   out = O / rowsum     same softmax warps drain O, normalise, write bf16 rows + the log-sum-exp
+//
+// One persistent CTA per SM walks over (image, head) items; warp 0 = TMA producer (2-deep Q/K/V ring), warp 1 = MMA
+// issuer, warps 2-5 / 6-9 = softmax + epilogue for query rows 0-127 / 128-255.  Nothing of size T x T touches HBM.
+// Semantics: reference transformer.py:20-31,44-45 — logits MULTIPLIED by sqrt(head_size) (scale is an argument),
+// no mask, heads are column slices of the packed [M,3E] qkv buffer, output concatenated in [M,E].
+#include <cuda.h>
+#include <cstdlib>
+
+#include "common.cuh"
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace vb {
+
+namespace {
+
+constexpr int HS = 64;                  // head size (one 128-byte swizzle row of bf16)
+constexpr int QT = 128;                 // query rows per tile = UMMA M
+constexpr int KV_ROWS = 256;            // rows staged for K / V / Q per item (2 TMA boxes of 128)
+constexpr int TILE_BYTES = KV_ROWS * HS * 2;        // 32 KB
+constexpr int STAGE_BYTES = 3 * TILE_BYTES;         // Q | K | V
+constexpr int kStages = 2;
+constexpr int kThreads = 64 + 8 * 32;
+constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 256 + 1024;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+struct FwdParams {
+  int T, TP, H, items;   // TP = T rounded up to a multiple of 16 (UMMA N and PV K extent)
+  float scale_log2;      // scale * log2(e)
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict__ out, float* __restrict__ lse,
+                   const FwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * STAGE_BYTES);
+  uint64_t* kv_full = bars;             // [2]  TMA -> MMA
+  uint64_t* kv_empty = bars + 2;        // [2]  MMA -> TMA
+  uint64_t* s_full = bars + 4;          // [2]  per query tile: S ready (MMA -> softmax)
+  uint64_t* p_ready = bars + 6;         // [2]  P written (softmax -> MMA)
+  uint64_t* o_full = bars + 8;          // [2]  O ready (MMA -> softmax)
+  uint64_t* t_free = bars + 10;         // [2]  tile's tensor-memory region drained (softmax -> MMA)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int E = p.H * HS;
+
+  if (threadIdx.x == 0) {
+    ptx::tma_prefetch_desc(&tm_qkv);
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&kv_full[s], 1);
+      ptx::mbar_init(&kv_empty[s], 1);
+      ptx::mbar_init(&s_full[s], 1);
+      ptx::mbar_init(&p_ready[s], 4);
+      ptx::mbar_init(&o_full[s], 1);
+      ptx::mbar_init(&t_free[s], 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_ptr, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  // tensor-memory map per query tile t: [t*256, t*256+TP) S (fp32) -> [t*256, +TP/2) P (bf16 pairs), O at t*256+128
+  // (TP <= 256: P needs <= 128 columns, O 64 columns; S is dead once P is written)
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int it = 0;
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        const int b = item / p.H, h = item - b * p.H;
+        ptx::mbar_wait(&kv_empty[st], ph ^ 1u);
+        ptx::mbar_arrive_expect_tx(&kv_full[st], STAGE_BYTES);
+        uint8_t* base = smem + st * STAGE_BYTES;
+        const int row0 = b * p.T;
+#pragma unroll
+        for (int sec = 0; sec < 3; ++sec)
+#pragma unroll
+          for (int half = 0; half < 2; ++half)
+            ptx::tma_load_2d(base + sec * TILE_BYTES + half * (QT * HS * 2), &tm_qkv, &kv_full[st],
+                             sec * E + h * HS, row0 + half * QT);
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      const uint32_t idesc_s = ptx::make_idesc_bf16_f32(QT, p.TP, 0, 0);   // S: M=128, N=TP, A,B K-major
+      const uint32_t idesc_o = ptx::make_idesc_bf16_f32(QT, HS, 0, 1);     // O: M=128, N=64, B (=V) MN-major
+      const int ntile = p.T > QT ? 2 : 1;
+      int it = 0;
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;       // phase of the 2-deep smem ring
+        const uint32_t tp = it & 1;              // phase of the per-item barriers
+        const uint32_t sq = ptx::smem_u32(smem + st * STAGE_BYTES);
+        const uint32_t sk = sq + TILE_BYTES, sv = sk + TILE_BYTES;
+        ptx::mbar_wait(&kv_full[st], ph);
+        ptx::tc_fence_after();
+        for (int t = 0; t < ntile; ++t) {
+          ptx::mbar_wait(&t_free[t], tp ^ 1u);
+          ptx::tc_fence_after();
+          const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
+#pragma unroll
+          for (int k = 0; k < HS / 16; ++k) {
+            const uint64_t da = ptx::make_smem_desc_sw128(sq + t * (QT * HS * 2) + k * 32, 16, 1024);
+            const uint64_t db = ptx::make_smem_desc_sw128(sk + k * 32, 16, 1024);
+            ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&s_full[t]);
+        }
+        for (int t = 0; t < ntile; ++t) {
+          ptx::mbar_wait(&p_ready[t], tp);
+          ptx::tc_fence_after();
+          const uint32_t a_p = tmem_base + static_cast<uint32_t>(t * 256);
+          const uint32_t d_o = a_p + 128;
+          for (int k = 0; k < p.TP / 16; ++k) {
+            // V as MN-major B: 16 key rows per k-step = 16 * 128 B; 8-row groups 1024 B apart
+            const uint64_t db = ptx::make_smem_desc_sw128(sv + k * 2048, 64 * 128, 1024);
+            ptx::umma_f16_ts(d_o, a_p + static_cast<uint32_t>(k * 8), db, idesc_o, k > 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&o_full[t]);
+        }
+        ptx::umma_commit(&kv_empty[st]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax + epilogue: one thread per query row
+    const int t = (warp - 2) >> 2;               // query tile of this warp
+    const int q = warp & 3;                      // tensor-memory lane quarter
+    const int row = t * QT + q * 32 + lane;      // query index inside the item
+    const bool tile_live = t * QT < p.T;
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(t * 256);
+    const int nchunk = (p.TP + 31) / 32;
+    int it = 0;
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+      if (!tile_live) continue;
+      const uint32_t tp = it & 1;
+      const int b = item / p.H, h = item - b * p.H;
+      ptx::mbar_wait(&s_full[t], tp);
+      ptx::tc_fence_after();
+      // pass 1: row maximum of the raw logits over the T valid keys (full chunks unmasked, tail chunk masked)
+      const int nfull = p.T / 32;                // chunks whose 32 keys are all valid
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+      for (int c = 0; c < nfull; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(c * 32), r);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(r[j]));
+          mx1 = fmaxf(mx1, __uint_as_float(r[j + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(r[j + 2]));
+          mx3 = fmaxf(mx3, __uint_as_float(r[j + 3]));
+        }
+      }
+      if (nfull < nchunk) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(nfull * 32), r);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (nfull * 32 + j < p.T) mx0 = fmaxf(mx0, __uint_as_float(r[j]));
+      }
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      const float sl2 = p.scale_log2;
+      const float mneg = -mx * sl2;              // scale > 0: max commutes with the scaling
+      // pass 2: p = exp2(s*c - m), row sum in fp32, P written over S as packed bf16
+      float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+      for (int c = 0; c < nfull; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(c * 32), r);
+        ptx::tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; j += 2) {
+          const float p0 = ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg));
+          const float p1 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg));
+          const float p2 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 2]), sl2, mneg));
+          const float p3 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 3]), sl2, mneg));
+          l0 += p0; l1 += p1; l2 += p2; l3 += p3;
+          pk[j] = pack_bf16x2(p0, p1);
+          pk[j + 1] = pack_bf16x2(p2, p3);
+        }
+        ptx::tmem_st_32x16(t_row + static_cast<uint32_t>(c * 16), pk);
+      }
+      if (nfull < nchunk) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(nfull * 32), r);
+        ptx::tmem_ld_wait();
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int k0 = nfull * 32 + 2 * j;
+          const float p0 = k0 < p.T ? ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg)) : 0.f;
+          const float p1 = k0 + 1 < p.T ? ptx::ex2(fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg)) : 0.f;
+          l0 += p0; l1 += p1;
+          pk[j] = pack_bf16x2(p0, p1);
+        }
+        ptx::tmem_st_32x16(t_row + static_cast<uint32_t>(nfull * 16), pk);
+      }
+      const float l = (l0 + l1) + (l2 + l3);
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&p_ready[t]);
+      // epilogue: O / l -> bf16 row, log-sum-exp
+      ptx::mbar_wait(&o_full[t], tp);
+      ptx::tc_fence_after();
+      const float inv = 1.f / l;
+      const bool live = row < p.T;
+      bf16* orow = out + (static_cast<int64_t>(b) * p.T + row) * E + h * HS;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_row + 128u + static_cast<uint32_t>(c * 32), r);
+        ptx::tmem_ld_wait();
+        if (live) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 o;
+            o.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]) * inv, __uint_as_float(r[8 * j + 1]) * inv);
+            o.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]) * inv, __uint_as_float(r[8 * j + 3]) * inv);
+            o.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]) * inv, __uint_as_float(r[8 * j + 5]) * inv);
+            o.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]) * inv, __uint_as_float(r[8 * j + 7]) * inv);
+            *reinterpret_cast<uint4*>(orow + c * 32 + j * 8) = o;
+          }
+        }
+      }
+      if (live && lse != nullptr)
+        lse[(static_cast<int64_t>(b) * p.H + h) * p.T + row] = (mx * sl2) * kLn2 + logf(l);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&t_free[t]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace
+
+bool attn_tc_supported(int T, int hs) { return hs == HS && T >= 1 && T <= 256; }
+
+int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
+                    cudaStream_t stream) {
+  if (!attn_tc_supported(T, hs)) {
+    set_error("attention (tcgen05): needs head_size 64 and T <= 256 (got hs=%d T=%d)", hs, T);
+    return kErrUnsupported;
+  }
+  VB_REQUIRE(scale > 0.f, "attention: scale must be positive");
+  VB_REQUIRE(aligned16(qkv) && aligned16(out), "attention: qkv/out must be 16-byte aligned");
+  const int E = H * hs;
+  const int64_t M = static_cast<int64_t>(B) * T;
+  CUtensorMap tm;
+  VB_PROPAGATE(make_tmap_bf16(&tm, qkv, M, 3 * static_cast<int64_t>(E), 3 * static_cast<int64_t>(E), HS, QT));
+  static bool attr_done = false;
+  if (!attr_done) {
+    VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    attr_done = true;
+  }
+  FwdParams p;
+  p.T = T; p.TP = (T + 15) / 16 * 16; p.H = H; p.items = B * H;
+  p.scale_log2 = scale * kLog2e;
+  ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * static_cast<double>(T) * hs, 1, stream);
+  const int grid = p.items < num_sms() ? p.items : num_sms();
+  attn_tc_fwd_kernel<<<grid, kThreads, SMEM_BYTES, stream>>>(tm, out, lse, p);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+}  // namespace vb

@@ -317,10 +317,13 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
+}  // namespace
+
 // 2-D bf16 tensor map over a row-major matrix [rows][ld] whose logical width is `cols`;
 // box = box_cols (inner, <= 64 elements = 128 B) x box_rows, 128B swizzle, OOB reads return zero.
-int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_cols,
+int make_tmap_bf16(void* map_out, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_cols,
                    int box_rows) {
+  CUtensorMap* map = static_cast<CUtensorMap*>(map_out);
   EncodeTiledFn enc = get_encode_fn();
   if (enc == nullptr) {
     set_error("cuTensorMapEncodeTiled entry point not available");
@@ -340,6 +343,8 @@ int make_tmap_bf16(CUtensorMap* map, const void* base, int64_t rows, int64_t col
   }
   return kOk;
 }
+
+namespace {
 
 template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI>
 int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,

@@ -18,6 +18,10 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
 int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int64_t lda, const float* B,
              int64_t ldb, int splits, const GemmEpilogue& ep, cudaStream_t stream);
 
+// 2-D bf16 TMA descriptor over a row-major matrix [rows][ld] of logical width `cols`; box = box_cols x box_rows,
+// 128-byte swizzle, out-of-bounds reads return zero (defined in gemm_tc.cu; opaque 128-byte CUtensorMap)
+int make_tmap_bf16(void* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_cols, int box_rows);
+
 // layer norm
 int ln_forward(const float* x, const float* gamma, const float* beta, void* y, bool y_bf16, float* mean,
                float* rstd, int M, int E, float eps, cudaStream_t stream);
@@ -37,6 +41,11 @@ int attn_bf16_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int 
                       cudaStream_t stream);
 int attn_bf16_backward(const bf16* qkv, const bf16* out, const bf16* d_o, const float* lse, float* delta, bf16* dqkv,
                        int B, int T, int H, int hs, float scale, cudaStream_t stream);
+
+// tcgen05 attention (head_size 64, T <= 256); returns kErrUnsupported outside that envelope
+int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
+                    cudaStream_t stream);
+bool attn_tc_supported(int T, int hs);
 
 // bandwidth kernels
 int im2col(const float* x, void* A, bool out_bf16, int B, int C, int Hi, int Wi, int P, int Kpad, cudaStream_t s);
