@@ -171,9 +171,11 @@ def test_bf16_peaked_softmax_no_worse_than_autocast_reference(lib):
     f_logits, _, f_grads = _oracle_on_gpu(sd, x, y, cfg)
     a_logits, _, a_grads = _autocast_oracle(sd, x, y, cfg)
     assert rel_err(logits, f_logits) < max(2e-2, 1.25 * rel_err(a_logits, f_logits))
-    ours_cos = min(cosine(mine[k], f_grads[k]) for k in f_grads)
-    auto_cos = min(cosine(a_grads[k], f_grads[k]) for k in f_grads)
-    assert ours_cos > min(0.999, auto_cos - 0.1), (ours_cos, auto_cos)   # chaotic regime: both are O(0.1) off
+    # the per-tensor minimum is a coin flip here (4 gradient-carrying rows, near one-hot softmax: one flipped argmax
+    # moves a whole tensor), so the gate is on the MEAN gradient cosine over all tensors
+    ours_cos = sum(cosine(mine[k], f_grads[k]) for k in f_grads) / len(f_grads)
+    auto_cos = sum(cosine(a_grads[k], f_grads[k]) for k in f_grads) / len(f_grads)
+    assert ours_cos > min(0.999, auto_cos - 0.02), (ours_cos, auto_cos)
 
 
 def test_autocast_selects_bf16_kernels(lib):

@@ -474,6 +474,7 @@ int attn_bf16_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int 
 int attn_bf16_backward(const bf16* qkv, const bf16* out, const bf16* d_o, const float* lse, float* delta, bf16* dqkv,
                        int B, int T, int H, int hs, float scale, cudaStream_t stream) {
   VB_PROPAGATE(attn_delta(out, d_o, true, delta, B, T, H, hs, stream));
+  if (use_tc_attention(T, hs)) return attn_tc_backward(qkv, d_o, lse, delta, dqkv, B, T, H, hs, scale, stream);
   switch (hs) {
     case 16: return bwd_launch<16>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
     case 32: return bwd_launch<32>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);

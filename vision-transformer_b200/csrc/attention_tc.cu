@@ -261,6 +261,265 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
   }
 }
 
+
+// ====================================================================================================== backward
+// Two kernels with one skeleton (MODE 0: dQ, rows = queries, columns = keys; MODE 1: dK/dV, rows = keys, columns =
+// queries — the transposed orientation, because a tensor-memory A operand cannot be transposed):
+//   MODE 0:  S = Q_t K^T, dP = dO_t V^T            -> dS = P o (dP - delta) * scale         -> dQ_t = dS K
+//   MODE 1:  S^T = K_t Q^T, dP^T = V_t dO^T        -> P^T, dS^T                              -> dV_t = P^T dO, dK_t = dS^T Q
+// with P = exp2(S*c - lse*log2e) recomputed from the saved log-sum-exp (no row reductions in backward).  S / dP live
+// in tensor-memory columns [0,TP) / [256,256+TP); the bf16 results overwrite them in place and feed TS-MMAs whose
+// accumulators sit in the dead upper halves ([128,192) and [384,448)).  One (item, 128-row tile) unit is in flight
+// per CTA; 8 element-wise warps split its columns (2 threads per row, chunk-interleaved, one 64-thread named
+// barrier per round keeps the in-place overwrite race-free).
+constexpr int kBwdThreads = 64 + 8 * 32;
+constexpr int kStatBytes = 2048;            // lse*log2e [256] | delta*scale [256] per stage
+
+struct BwdParams {
+  int T, TP, H, items, stages;
+  int tile_bytes, stage_bytes;              // TP*128, 4*tile_bytes + kStatBytes
+  float scale, scale_log2;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
+                   const float* __restrict__ lse, const float* __restrict__ delta, bf16* __restrict__ dqkv,
+                   const BwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // barriers live AFTER the stages and the over-read pad (see host side)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.stages * p.stage_bytes + (32768 - p.tile_bytes));
+  uint64_t* kv_full = bars;         // [2] TMA bytes landed
+  uint64_t* st_full = bars + 2;     // [2] row statistics staged (32 producer lanes)
+  uint64_t* kv_empty = bars + 4;    // [2]
+  uint64_t* sd_full = bars + 6;     // S and dP ready
+  uint64_t* ew_done = bars + 7;     // bf16 operands written (8 warps)
+  uint64_t* acc_full = bars + 8;    // output accumulators ready
+  uint64_t* t_free = bars + 9;      // accumulators drained (8 warps)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 10);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int E = p.H * HS;
+  const int ntile = p.T > QT ? 2 : 1;
+
+  if (threadIdx.x == 0) {
+    ptx::tma_prefetch_desc(&tm_qkv);
+    ptx::tma_prefetch_desc(&tm_do);
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&kv_full[s], 1);
+      ptx::mbar_init(&st_full[s], 32);
+      ptx::mbar_init(&kv_empty[s], 1);
+    }
+    ptx::mbar_init(sd_full, 1);
+    ptx::mbar_init(ew_done, 8);
+    ptx::mbar_init(acc_full, 1);
+    ptx::mbar_init(t_free, 8);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_ptr, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ producer: TMA tiles + row statistics
+    int it = 0;
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+      const int st = p.stages == 2 ? (it & 1) : 0;
+      const uint32_t ph = p.stages == 2 ? ((it >> 1) & 1) : (it & 1);
+      const int b = item / p.H, h = item - b * p.H;
+      ptx::mbar_wait(&kv_empty[st], ph ^ 1u);
+      uint8_t* base = smem + st * p.stage_bytes;
+      if (lane == 0) {
+        ptx::mbar_arrive_expect_tx(&kv_full[st], 4 * p.tile_bytes);
+        const int row0 = b * p.T;
+        ptx::tma_load_2d(base + 0 * p.tile_bytes, &tm_qkv, &kv_full[st], 0 * E + h * HS, row0);
+        ptx::tma_load_2d(base + 1 * p.tile_bytes, &tm_qkv, &kv_full[st], 1 * E + h * HS, row0);
+        ptx::tma_load_2d(base + 2 * p.tile_bytes, &tm_qkv, &kv_full[st], 2 * E + h * HS, row0);
+        ptx::tma_load_2d(base + 3 * p.tile_bytes, &tm_do, &kv_full[st], h * HS, row0);
+      }
+      float* stat = reinterpret_cast<float*>(base + 4 * p.tile_bytes);
+      const float* lrow = lse + static_cast<int64_t>(item) * p.T;
+      const float* drow = delta + static_cast<int64_t>(item) * p.T;
+      for (int j = lane; j < 256; j += 32) {
+        stat[j] = j < p.T ? lrow[j] * kLog2e : INFINITY;        // +inf => p = 0 for padded rows / columns
+        stat[256 + j] = j < p.T ? drow[j] * p.scale : 0.f;
+      }
+      ptx::mbar_arrive(&st_full[st]);
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      const uint32_t idesc_s = ptx::make_idesc_bf16_f32(QT, p.TP, 0, 0);
+      const uint32_t idesc_o = ptx::make_idesc_bf16_f32(QT, HS, 0, 1);
+      int it = 0, u = 0;
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+        const int st = p.stages == 2 ? (it & 1) : 0;
+        const uint32_t ph = p.stages == 2 ? ((it >> 1) & 1) : (it & 1);
+        const uint32_t sq = ptx::smem_u32(smem + st * p.stage_bytes);
+        const uint32_t sk = sq + p.tile_bytes, sv = sk + p.tile_bytes, sdo = sv + p.tile_bytes;
+        // MODE 0: rows from Q / dO, columns from K / V, output B = K.   MODE 1: rows from K / V, columns Q / dO.
+        const uint32_t a1 = MODE == 0 ? sq : sk, b1 = MODE == 0 ? sk : sq;
+        const uint32_t a2 = MODE == 0 ? sdo : sv, b2 = MODE == 0 ? sv : sdo;
+        ptx::mbar_wait(&kv_full[st], ph);
+        ptx::tc_fence_after();
+        for (int t = 0; t < ntile; ++t, ++u) {
+          const uint32_t up = u & 1;
+          ptx::mbar_wait(t_free, up ^ 1u);
+          ptx::tc_fence_after();
+#pragma unroll
+          for (int k = 0; k < HS / 16; ++k)
+            ptx::umma_f16(tmem_base, ptx::make_smem_desc_sw128(a1 + t * (QT * 128) + k * 32, 16, 1024),
+                          ptx::make_smem_desc_sw128(b1 + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
+#pragma unroll
+          for (int k = 0; k < HS / 16; ++k)
+            ptx::umma_f16(tmem_base + 256u, ptx::make_smem_desc_sw128(a2 + t * (QT * 128) + k * 32, 16, 1024),
+                          ptx::make_smem_desc_sw128(b2 + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
+          ptx::umma_commit(sd_full);
+          ptx::mbar_wait(ew_done, up);
+          ptx::tc_fence_after();
+          if (MODE == 0) {
+            for (int k = 0; k < p.TP / 16; ++k)     // dQ = dS K
+              ptx::umma_f16_ts(tmem_base + 128u, tmem_base + static_cast<uint32_t>(k * 8),
+                               ptx::make_smem_desc_sw128(sk + k * 2048, 64 * 128, 1024), idesc_o, k > 0 ? 1u : 0u);
+          } else {
+            for (int k = 0; k < p.TP / 16; ++k)     // dV = P^T dO
+              ptx::umma_f16_ts(tmem_base + 128u, tmem_base + static_cast<uint32_t>(k * 8),
+                               ptx::make_smem_desc_sw128(sdo + k * 2048, 64 * 128, 1024), idesc_o, k > 0 ? 1u : 0u);
+            for (int k = 0; k < p.TP / 16; ++k)     // dK = dS^T Q
+              ptx::umma_f16_ts(tmem_base + 384u, tmem_base + 256u + static_cast<uint32_t>(k * 8),
+                               ptx::make_smem_desc_sw128(sq + k * 2048, 64 * 128, 1024), idesc_o, k > 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(acc_full);
+        }
+        ptx::umma_commit(&kv_empty[st]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ element-wise warps: 2 threads per row
+    const int q = warp & 3;                      // tensor-memory lane quarter
+    const int part = (warp - 2) >> 2;            // which chunk parity / which half of the output columns
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const int nchunk = (p.TP + 31) / 32;
+    const int nround = (nchunk + 1) / 2;
+    const float sl2 = p.scale_log2, scale = p.scale;
+    int it = 0, u = 0;
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+      const int st = p.stages == 2 ? (it & 1) : 0;
+      const uint32_t ph = p.stages == 2 ? ((it >> 1) & 1) : (it & 1);
+      const int b = item / p.H, h = item - b * p.H;
+      const float* stat = reinterpret_cast<const float*>(smem + st * p.stage_bytes + 4 * p.tile_bytes);
+      ptx::mbar_wait(&st_full[st], ph);
+      for (int t = 0; t < ntile; ++t, ++u) {
+        const uint32_t up = u & 1;
+        const int row = t * QT + q * 32 + lane;  // query (MODE 0) or key (MODE 1) index of this thread
+        float lse2r = 0.f, dscr = 0.f;
+        if (MODE == 0) { lse2r = stat[row]; dscr = stat[256 + row]; }
+        ptx::mbar_wait(sd_full, up);
+        ptx::tc_fence_after();
+        for (int rd = 0; rd < nround; ++rd) {
+          const int c = 2 * rd + part;
+          const bool active = c < nchunk;
+          uint32_t pk0[16], pk1[16];
+          if (active) {
+            uint32_t rs[32], rp[32];
+            ptx::tmem_ld_32x32(lane_base + static_cast<uint32_t>(c * 32), rs);
+            ptx::tmem_ld_32x32(lane_base + 256u + static_cast<uint32_t>(c * 32), rp);
+            ptx::tmem_ld_wait();
+            if (MODE == 0) {
+              if (c * 32 + 32 <= p.T) {            // all 32 keys valid (warp-uniform): no per-element predicates
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const float e0 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j]), sl2, -lse2r)) *
+                                   fmaf(__uint_as_float(rp[2 * j]), scale, -dscr);
+                  const float e1 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j + 1]), sl2, -lse2r)) *
+                                   fmaf(__uint_as_float(rp[2 * j + 1]), scale, -dscr);
+                  pk0[j] = pack_bf16x2(e0, e1);
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const int k0 = c * 32 + 2 * j;
+                  float e0 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j]), sl2, -lse2r));
+                  float e1 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j + 1]), sl2, -lse2r));
+                  e0 = k0 < p.T ? e0 * fmaf(__uint_as_float(rp[2 * j]), scale, -dscr) : 0.f;
+                  e1 = k0 + 1 < p.T ? e1 * fmaf(__uint_as_float(rp[2 * j + 1]), scale, -dscr) : 0.f;
+                  pk0[j] = pack_bf16x2(e0, e1);
+                }
+              }
+            } else {
+              const float4* l4 = reinterpret_cast<const float4*>(stat + c * 32);
+              const float4* d4 = reinterpret_cast<const float4*>(stat + 256 + c * 32);
+#pragma unroll
+              for (int j4 = 0; j4 < 8; ++j4) {
+                const float4 lv = l4[j4], dv = d4[j4];
+                const float lj[4] = {lv.x, lv.y, lv.z, lv.w}, dj[4] = {dv.x, dv.y, dv.z, dv.w};
+                float pe[4], de[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  pe[i] = ptx::ex2(fmaf(__uint_as_float(rs[4 * j4 + i]), sl2, -lj[i]));
+                  de[i] = pe[i] * fmaf(__uint_as_float(rp[4 * j4 + i]), scale, -dj[i]);
+                }
+                pk0[2 * j4] = pack_bf16x2(pe[0], pe[1]); pk0[2 * j4 + 1] = pack_bf16x2(pe[2], pe[3]);
+                pk1[2 * j4] = pack_bf16x2(de[0], de[1]); pk1[2 * j4 + 1] = pack_bf16x2(de[2], de[3]);
+              }
+            }
+          }
+          // both threads of every row have READ chunks 2rd and 2rd+1 before either overwrites columns [32rd, 32rd+32)
+          asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+          if (active) {
+            ptx::tmem_st_32x16(lane_base + static_cast<uint32_t>(c * 16), pk0);
+            if (MODE == 1) ptx::tmem_st_32x16(lane_base + 256u + static_cast<uint32_t>(c * 16), pk1);
+          }
+        }
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(ew_done);
+        // drain: this warp takes columns [32*part, 32*part+32) of each 64-column accumulator
+        ptx::mbar_wait(acc_full, up);
+        ptx::tc_fence_after();
+        const bool live = row < p.T;
+        bf16* grow = dqkv + (static_cast<int64_t>(b) * p.T + row) * (3 * static_cast<int64_t>(E)) + h * HS + part * 32;
+#pragma unroll
+        for (int o = 0; o < (MODE == 0 ? 1 : 2); ++o) {
+          uint32_t r[32];
+          ptx::tmem_ld_32x32(lane_base + (o == 0 ? 128u : 384u) + static_cast<uint32_t>(part * 32), r);
+          ptx::tmem_ld_wait();
+          // MODE 0: dQ -> section 0.  MODE 1: accumulator 0 = dV -> section 2, accumulator 1 = dK -> section 1.
+          bf16* dst = grow + (MODE == 0 ? 0 : (o == 0 ? 2 : 1)) * static_cast<int64_t>(E);
+          if (live) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 v;
+              v.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+              v.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+              v.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+              v.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+              *reinterpret_cast<uint4*>(dst + j * 8) = v;
+            }
+          }
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(t_free);
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
 }  // namespace
 
 bool attn_tc_supported(int T, int hs) { return hs == HS && T >= 1 && T <= 256; }
@@ -288,6 +547,39 @@ int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H,
   ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * static_cast<double>(T) * hs, 1, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
   attn_tc_fwd_kernel<<<grid, kThreads, SMEM_BYTES, stream>>>(tm, out, lse, p);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+
+int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B, int T,
+                     int H, int hs, float scale, cudaStream_t stream) {
+  if (!attn_tc_supported(T, hs)) {
+    set_error("attention (tcgen05): needs head_size 64 and T <= 256 (got hs=%d T=%d)", hs, T);
+    return kErrUnsupported;
+  }
+  VB_REQUIRE(scale > 0.f, "attention: scale must be positive");
+  VB_REQUIRE(aligned16(qkv) && aligned16(d_o) && aligned16(dqkv), "attention: operands must be 16-byte aligned");
+  const int E = H * hs;
+  const int64_t M = static_cast<int64_t>(B) * T;
+  BwdParams p;
+  p.T = T; p.TP = (T + 15) / 16 * 16; p.H = H; p.items = B * H;
+  p.tile_bytes = p.TP * 128;
+  p.stage_bytes = 4 * p.tile_bytes + kStatBytes;
+  const int pad = 32768 - p.tile_bytes;      // an A tile of rows [128,256) may over-read past a TP-row operand
+  p.stages = (2 * p.stage_bytes + pad + 256 + 1024 <= 227 * 1024) ? 2 : 1;
+  p.scale = scale; p.scale_log2 = scale * kLog2e;
+  const int smem = p.stages * p.stage_bytes + pad + 256 + 1024;
+  CUtensorMap tq, td;
+  VB_PROPAGATE(make_tmap_bf16(&tq, qkv, M, 3 * static_cast<int64_t>(E), 3 * static_cast<int64_t>(E), HS, p.TP));
+  VB_PROPAGATE(make_tmap_bf16(&td, d_o, M, E, E, HS, p.TP));
+  VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * static_cast<double>(T) * hs, 2, stream);
+  const int grid = p.items < num_sms() ? p.items : num_sms();
+  attn_tc_bwd_kernel<1><<<grid, kBwdThreads, smem, stream>>>(tq, td, lse, delta, dqkv, p);
+  VB_CHECK_LAUNCH();
+  attn_tc_bwd_kernel<0><<<grid, kBwdThreads, smem, stream>>>(tq, td, lse, delta, dqkv, p);
   VB_CHECK_LAUNCH();
   return kOk;
 }

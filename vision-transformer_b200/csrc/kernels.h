@@ -46,6 +46,8 @@ int attn_bf16_backward(const bf16* qkv, const bf16* out, const bf16* d_o, const 
 int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
                     cudaStream_t stream);
 bool attn_tc_supported(int T, int hs);
+int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B, int T,
+                     int H, int hs, float scale, cudaStream_t stream);
 
 // bandwidth kernels
 int im2col(const float* x, void* A, bool out_bf16, int B, int C, int Hi, int Wi, int P, int Kpad, cudaStream_t s);
