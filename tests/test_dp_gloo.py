@@ -1,0 +1,107 @@
+"""CPU, world_size 2 over gloo: the exchange step of the data-parallel path (train_dp.BucketReducer) — bucket layout
+covers the gradient arena exactly once, buckets are launched in the order backward completes them, and after
+finish() every rank holds the element-wise SUM (AdamW folds 1/world into its gradient read)."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "vision-transformer_b200"))
+import train_dp  # noqa: E402
+
+CFG = dict(C=3, P=4, E=32, H=2, L=5, T=17, B=2, classes=3)
+
+
+def _layout():
+    layout = train_dp.param_layout(**CFG)
+    offs, total = train_dp.arena_offsets(layout)
+    return layout, offs, total
+
+
+@pytest.mark.parametrize("bucket_elems", [1, 5000, 30000, 10 ** 9])
+def test_buckets_tile_the_arena_in_backward_order(bucket_elems):
+    layout, offs, total = _layout()
+    buckets = train_dp.make_buckets(layout, offs, total, bucket_elems)
+    # contiguous, descending, covering [0, total) exactly once
+    assert buckets[0][1] == total and buckets[-1][0] == 0
+    for (a, b, _), (a2, b2, _) in zip(buckets, buckets[1:]):
+        assert a < b and b2 == a
+    # the stage that closes a bucket is the LAST one (in backward order) with parameters inside it
+    order = ["head"] + list(range(CFG["L"] - 1, -1, -1)) + ["embed"]
+    closing = [order.index(st) for _, _, st in buckets]
+    assert closing == sorted(closing)
+    for a, b, st in buckets:
+        inside = {stage for (stage, _, _, _), (o, n) in zip(layout, offs) if a <= o < b}
+        assert max(order.index(s) for s in inside) == order.index(st)
+    if bucket_elems == 10 ** 9:
+        assert len(buckets) == 1 and buckets[0][2] == "embed"
+    if bucket_elems == 1:
+        assert len(buckets) == CFG["L"] + 2
+
+
+def test_arena_offsets_are_aligned_and_disjoint():
+    layout, offs, total = _layout()
+    end = 0
+    for (o, n) in offs:
+        assert o % train_dp.ALIGN == 0 and o >= end
+        end = o + n
+    assert total >= end and total % train_dp.ALIGN == 0
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, bucket_elems, out):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        layout, offs, total = _layout()
+        buckets = train_dp.make_buckets(layout, offs, total, bucket_elems)
+        gen = torch.Generator().manual_seed(100 + rank)
+        g = torch.randn(total, generator=gen)
+        mine = g.clone()
+        red = train_dp.BucketReducer(g, buckets, dist.group.WORLD, world)
+        handles, launched = [], []
+        for stage in ["head"] + list(range(CFG["L"] - 1, -1, -1)) + ["embed"]:
+            before = len(handles)
+            red.ready(stage, handles)
+            launched += [stage] * (len(handles) - before)
+        red.finish(handles)
+        others = [torch.randn(total, generator=torch.Generator().manual_seed(100 + r)) for r in range(world)]
+        expect = torch.stack(others).sum(0)
+        ok = torch.allclose(g, expect, rtol=0, atol=1e-6) and torch.equal(mine, others[rank])
+        ok = ok and launched == [st for _, _, st in buckets]
+        # parameters broadcast from rank 0 the way DPTrainer.broadcast_parameters does it
+        p = torch.full((total,), float(rank))
+        dist.broadcast(p, src=0)
+        ok = ok and bool((p == 0).all())
+        out[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("bucket_elems", [5000, 10 ** 9])
+def test_world2_bucketed_allreduce_sums_gradients(bucket_elems):
+    world = 2
+    with mp.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_worker, args=(world, _free_port(), bucket_elems, out), nprocs=world, join=True)
+        assert dict(out) == {0: True, 1: True}
+
+
+def test_single_rank_reducer_is_a_no_op():
+    layout, offs, total = _layout()
+    g = torch.ones(total)
+    red = train_dp.BucketReducer(g, train_dp.make_buckets(layout, offs, total, 5000), None, 1)
+    handles = []
+    red.ready("head", handles)
+    red.finish(handles)
+    assert handles == [] and bool((g == 1).all())

@@ -139,7 +139,8 @@ def _attn_ref(qkv, B, T, H, hs, scale):
 
 
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("B,T,H,hs", [(2, 197, 3, 64), (1, 257, 2, 64), (2, 65, 2, 80), (3, 17, 2, 32), (1, 577, 1, 80)])
+@pytest.mark.parametrize("B,T,H,hs", [(2, 197, 3, 64), (1, 257, 2, 64), (2, 65, 2, 80), (3, 17, 2, 32), (1, 577, 1, 80),
+                                       (5, 256, 2, 64), (3, 128, 1, 64), (2, 100, 3, 64), (7, 5, 2, 64), (40, 129, 12, 64)])
 def test_attention_fwd_bwd(lib, dt, B, T, H, hs):
     C = _C()
     torch.manual_seed(5)

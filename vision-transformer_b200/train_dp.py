@@ -79,6 +79,40 @@ def make_buckets(layout, offs, total, bucket_elems):
     return buckets
 
 
+class BucketReducer:
+    """The one exchange step of the data-parallel path: sum-all-reduce of contiguous gradient-arena buckets, each
+    launched as soon as the backward stage that completes it has been enqueued.  On CUDA the collective runs on a
+    side stream behind an event recorded on the compute stream (so it overlaps the remaining backward); on CPU
+    tensors (gloo, used by the world_size-2 tests) the same calls run without streams."""
+
+    def __init__(self, flat_grad, buckets, process_group=None, world_size=1):
+        self.g, self.buckets, self.pg, self.world = flat_grad, buckets, process_group, int(world_size)
+        self.cuda = flat_grad.is_cuda
+        if self.cuda and self.world > 1:
+            self.stream = torch.cuda.Stream(device=flat_grad.device)
+            self.events = [torch.cuda.Event() for _ in buckets]
+
+    def ready(self, stage, handles):
+        """Launch the all-reduce of every bucket completed by `stage`'s backward (already enqueued)."""
+        if self.world <= 1:
+            return
+        for k, (a, b, st) in enumerate(self.buckets):
+            if st != stage:
+                continue
+            if self.cuda:
+                self.events[k].record(torch.cuda.current_stream(self.g.device))
+                with torch.cuda.stream(self.stream):
+                    self.stream.wait_event(self.events[k])
+                    handles.append(torch.distributed.all_reduce(self.g[a:b], group=self.pg, async_op=True))
+            else:
+                handles.append(torch.distributed.all_reduce(self.g[a:b], group=self.pg, async_op=True))
+
+    @staticmethod
+    def finish(handles):
+        for h in handles:
+            h.wait()  # CUDA: the compute stream waits for the reduced buckets; the host does not block
+
+
 # ---------------------------------------------------------------------------------------------------- trainer
 class DPTrainer:
     def __init__(self, *, input_channels=3, num_classes=2, image_size=224, patch_size=16, embedding_size=768,
@@ -148,12 +182,11 @@ class DPTrainer:
 
         # host <-> device staging for step_host()
         self.copy_stream = torch.cuda.Stream(device=dev)
-        self.comm_stream = torch.cuda.Stream(device=dev) if self.world > 1 else None
+        self.reducer = BucketReducer(self.g, self.buckets, self.pg, self.world)
         self._in = [(torch.empty(self.B, self.C, self.img, self.img, dtype=torch.float32, device=dev),
                      torch.empty(self.B, dtype=torch.int64, device=dev)) for _ in range(2)]
         self._in_ready = [torch.cuda.Event() for _ in range(2)]
         self._in_free = [torch.cuda.Event() for _ in range(2)]
-        self._bucket_ev = [torch.cuda.Event() for _ in self.buckets]
         self._slot = 0
         self.loss_host = torch.zeros(64, dtype=torch.float32).pin_memory()
         self._loss_ev = [torch.cuda.Event() for _ in range(64)]
@@ -259,16 +292,7 @@ class DPTrainer:
         return self.logits
 
     def _bucket_ready(self, stage, handles):
-        """Launch the all-reduce of every bucket completed by `stage`'s backward (already enqueued)."""
-        if self.world <= 1:
-            return
-        cur = torch.cuda.current_stream(self.dev)
-        for k, (a, b, st) in enumerate(self.buckets):
-            if st == stage:
-                self._bucket_ev[k].record(cur)
-                with torch.cuda.stream(self.comm_stream):
-                    self.comm_stream.wait_event(self._bucket_ev[k])
-                    handles.append(torch.distributed.all_reduce(self.g[a:b], group=self.pg, async_op=True))
+        self.reducer.ready(stage, handles)
 
     def backward(self, labels, d):
         pl, L = self.plan, _C.lib()
@@ -285,8 +309,7 @@ class DPTrainer:
             self._bucket_ready(i, handles)
         pl.embed_bwd(d, self.embed_g, self.gstream, self.emb_acts)
         self._bucket_ready("embed", handles)
-        for h in handles:
-            h.wait()  # the compute stream waits for the reduced buckets; the host does not block
+        self.reducer.finish(handles)
 
     def optimizer_step(self):
         self.step_no += 1
@@ -322,8 +345,8 @@ class DPTrainer:
         cur.wait_event(self._in_ready[k])
         d = self._dims(True)
         self.forward(x, d)
-        self._in_free[k].record(cur)  # images are only read by the patch gather at the top of forward
         self.backward(y, d)
+        self._in_free[k].record(cur)  # the labels are read by the loss kernel at the top of backward
         self.optimizer_step()
         li = (self.step_no - 1) % self.loss_host.numel()
         self.loss_host[li:li + 1].copy_(self.loss, non_blocking=True)
