@@ -95,10 +95,12 @@ int vitb200_gemm(const vitb200_gemm_args* args, void* stream);
 int vitb200_ln_fwd(const float* x, const float* gamma, const float* beta, void* y, int y_dtype, float* mean,
                    float* rstd, int M, int E, float eps, void* stream);
 /* LayerNorm backward.  g (fp32 [M,E]) receives dx (add_to_g: g += dx).  dgamma/dbeta are ACCUMULATED.
- * dyn (optional, dy_dtype) = cast(g_new * dropout factors) — the operand of the next backward GEMM. */
+ * dyn (optional, dy_dtype) = cast(g_new * dropout factors) — the operand of the next backward GEMM;
+ * dyn_colsum (optional, fp32 [E], needs dyn) += column sums of dyn = the bias gradient of the Linear whose
+ * dropout-ed output fed this LayerNorm's residual input (transformer.py:46,58). */
 int vitb200_ln_bwd(const void* dy, int dy_dtype, const float* x, const float* mean, const float* rstd,
                    const float* gamma, float* g, int add_to_g, float* dgamma, float* dbeta, void* dyn,
-                   vitb200_dropout dyn_dropout, int M, int E, void* stream);
+                   float* dyn_colsum, vitb200_dropout dyn_dropout, int M, int E, void* stream);
 
 /* Multi-head self-attention core (transformer.py:20-31,44-45): qkv [B*T, 3E] packed (q | k | v, head h at
  * columns h*hs), logits * scale (the reference MULTIPLIES by sqrt(hs)), softmax, @v, heads concatenated into
@@ -180,8 +182,10 @@ typedef struct {
   const void* w_fc1;  const float* b_fc1;  /* [4E, E] */
   const void* w_fc2;  const float* b_fc2;  /* [E, 4E] */
 } vitb200_block_params;
+/* b_fc2 == NULL: the producer of dy_in already accumulated this layer's fc2 bias gradient (see b_fc2_prev).
+ * b_fc2_prev (optional): fc2 bias gradient of layer-1; the last kernel of this call adds colsum(dy_out) to it. */
 typedef struct {
-  float *ln1_w, *ln1_b, *ln2_w, *ln2_b, *w_qkv, *w_proj, *b_proj, *w_fc1, *b_fc1, *w_fc2, *b_fc2;
+  float *ln1_w, *ln1_b, *ln2_w, *ln2_b, *w_qkv, *w_proj, *b_proj, *w_fc1, *b_fc1, *w_fc2, *b_fc2, *b_fc2_prev;
 } vitb200_block_grads;
 int64_t vitb200_block_act_bytes(const vitb200_dims* d);
 int64_t vitb200_block_scratch_bytes(const vitb200_dims* d);
@@ -203,6 +207,11 @@ int vitb200_head_fwd(const vitb200_dims* d, const vitb200_head_params* p, const 
 /* Produces g (fp32 [B*T,E], zero except token 0) and dy_out = cast(g * fc2-dropout mask of layer n_layers-1). */
 int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_params* p, const vitb200_head_grads* gr,
                      const void* acts, const float* dlogits, float* g, void* dy_out, void* scratch, void* stream);
+
+/* sizeof() of the ABI structs as this library was compiled, for binding self-checks.
+ * which: 0 dims, 1 dropout, 2 gemm_args, 3 adamw_hyper, 4 block_params, 5 block_grads, 6 head_params, 7 prof_entry;
+ * -1 for anything else. */
+int64_t vitb200_abi_sizeof(int which);
 
 #ifdef __cplusplus
 }

@@ -38,6 +38,13 @@ def test_struct_layouts_match_header_sizes():
     assert ctypes.sizeof(_C.AdamWHyper) == 28
     assert ctypes.sizeof(_C.BlockParams) == 11 * 8
     assert ctypes.sizeof(_C.GemmArgs) == 168
+    # and against the sizes the library itself was compiled with
+    lib = _C.lib()
+    lib.vitb200_abi_sizeof.restype = ctypes.c_int64
+    for which, cls in enumerate((_C.Dims, _C.Dropout, _C.GemmArgs, _C.AdamWHyper, _C.BlockParams, _C.BlockGrads,
+                                 _C.HeadParams, _C.ProfEntry)):
+        assert lib.vitb200_abi_sizeof(which) == ctypes.sizeof(cls), cls.__name__
+    assert lib.vitb200_abi_sizeof(99) == -1
 
 
 def test_error_channel_without_gpu():

@@ -118,8 +118,8 @@ def test_layernorm_fwd_bwd(lib, M, E):
     g = g0.clone()
     dgam, dbet = torch.zeros(E, device=DEV), torch.zeros(E, device=DEV)
     C.check(lib.vitb200_ln_bwd(dy.data_ptr(), C.F32, x.data_ptr(), mean.data_ptr(), rstd.data_ptr(), w.data_ptr(),
-                               g.data_ptr(), 1, dgam.data_ptr(), dbet.data_ptr(), None, C.Dropout(0, 0, 0), M, E,
-                               C.stream_ptr()))
+                               g.data_ptr(), 1, dgam.data_ptr(), dbet.data_ptr(), None, None, C.Dropout(0, 0, 0),
+                               M, E, C.stream_ptr()))
     assert rel_err(g - g0, x.grad) < 2e-5
     assert rel_err(dgam, w.grad) < 2e-5
     assert rel_err(dbet, b.grad) < 2e-5
@@ -128,6 +128,44 @@ def test_layernorm_fwd_bwd(lib, M, E):
         C.check(lib.vitb200_ln_fwd(x.data_ptr(), w.data_ptr(), b.data_ptr(), yb.data_ptr(), C.BF16, mean.data_ptr(),
                                    rstd.data_ptr(), M, E, 1e-5, C.stream_ptr()))
         assert rel_err(yb, y_ref) < 8e-3
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("M,E,add", [(197 * 7, 768, 1), (1000, 384, 1), (333, 1024, 0), (64, 8, 1), (4099, 192, 0),
+                                     (50, 3072, 1), (9, 100, 1)])
+def test_layernorm_bwd_masked_operand_and_bias_grad(lib, dt, M, E, add):
+    """The fused outputs of the LayerNorm backward: g (+)= dx, dyn = cast(g_new * dropout factors) and
+    dyn_colsum += column sums of dyn — bulk-copy ring kernel (E % 8 == 0, E <= 1024) and the generic one."""
+    if dt == torch.bfloat16 and E % 8:
+        pytest.skip("bf16 rows need 16-byte pitch")
+    C = _C()
+    torch.manual_seed(5)
+    x = (torch.randn(M, E, device=DEV) * 1.5 - 0.3).requires_grad_(True)
+    w = (1 + 0.1 * torch.randn(E, device=DEV)).requires_grad_(True)
+    b = torch.zeros(E, device=DEV, requires_grad=True)
+    dy = torch.randn(M, E, device=DEV).to(dt)
+    torch.nn.functional.layer_norm(x, (E,), w, b, 1e-5).backward(dy.float())
+    mean = x.detach().mean(1).contiguous()
+    rstd = (x.detach().var(1, unbiased=False) + 1e-5).rsqrt().contiguous()
+    g0 = torch.randn(M, E, device=DEV)
+    g = g0.clone()
+    dgam, dbet = torch.ones(E, device=DEV), torch.ones(E, device=DEV)   # accumulate on top of existing values
+    csum = torch.full((E,), 2.0, device=DEV)
+    dyn = torch.empty(M, E, device=DEV, dtype=dt)
+    code = C.BF16 if dt == torch.bfloat16 else C.F32
+    C.check(lib.vitb200_ln_bwd(dy.data_ptr(), code, x.data_ptr(), mean.data_ptr(), rstd.data_ptr(), w.data_ptr(),
+                               g.data_ptr(), add, dgam.data_ptr(), dbet.data_ptr(), dyn.data_ptr(), csum.data_ptr(),
+                               C.Dropout(0.2, 77, 5), M, E, C.stream_ptr()))
+    g_ref = x.grad + (g0 if add else 0)
+    assert rel_err(g, g_ref) < 2e-5
+    assert rel_err(dgam - 1, w.grad) < 3e-5
+    assert rel_err(dbet - 1, b.grad) < 3e-5
+    keep = torch.empty(M * E, dtype=torch.uint8, device=DEV)
+    C.check(lib.vitb200_dropout_mask(keep.data_ptr(), M * E, C.Dropout(0.2, 77, 5), C.stream_ptr()))
+    dyn_ref = g_ref * keep.reshape(M, E).float() / 0.8
+    assert rel_err(dyn, dyn_ref) < (5e-3 if dt == torch.bfloat16 else 2e-5)
+    assert ((dyn == 0) == (keep.reshape(M, E) == 0)).float().mean().item() > 0.9999
+    assert rel_err(csum - 2, dyn_ref.sum(0)) < (5e-3 if dt == torch.bfloat16 else 5e-5)
 
 
 # ------------------------------------------------------------------------------------------------ attention

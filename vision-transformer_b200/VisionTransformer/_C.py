@@ -71,11 +71,12 @@ EMBED_FIELDS_P = ("w_f32", "w_lp", "bias", "cls", "pos")
 EMBED_FIELDS_G = ("w", "bias", "cls", "pos")
 BLOCK_FIELDS_P = ("ln1_w", "ln1_b", "ln2_w", "ln2_b", "w_qkv", "w_proj", "b_proj", "w_fc1", "b_fc1", "w_fc2", "b_fc2")
 BLOCK_FIELDS_G = ("ln1_w", "ln1_b", "ln2_w", "ln2_b", "w_qkv", "w_proj", "b_proj", "w_fc1", "b_fc1", "w_fc2", "b_fc2")
+BLOCK_GRADS_STRUCT = BLOCK_FIELDS_G + ("b_fc2_prev",)  # vitb200_block_grads: own gradients + the chained bias pointer
 HEAD_FIELDS = ("w1", "b1", "ln_w", "ln_b", "w3", "b3")
 EmbedParams = _ptr_struct("EmbedParams", EMBED_FIELDS_P)
 EmbedGrads = _ptr_struct("EmbedGrads", EMBED_FIELDS_G)
 BlockParams = _ptr_struct("BlockParams", BLOCK_FIELDS_P)
-BlockGrads = _ptr_struct("BlockGrads", BLOCK_FIELDS_G)
+BlockGrads = _ptr_struct("BlockGrads", BLOCK_GRADS_STRUCT)
 HeadParams = _ptr_struct("HeadParams", HEAD_FIELDS)
 HeadGrads = _ptr_struct("HeadGrads", HEAD_FIELDS)
 
@@ -102,6 +103,8 @@ def _declare(L):
     L.vitb200_gemm.argtypes = [ctypes.POINTER(GemmArgs), c_void_p]
     L.vitb200_gemm.restype = c_int
     L.vitb200_launch_count.restype = c_int64
+    L.vitb200_abi_sizeof.argtypes = [c_int]
+    L.vitb200_abi_sizeof.restype = c_int64
     L.vitb200_prof_class_name.argtypes = [c_int]
     L.vitb200_prof_class_name.restype = ctypes.c_char_p
     L.vitb200_prof_begin.restype = c_int
@@ -111,7 +114,7 @@ def _declare(L):
     sig = {
         "vitb200_ln_fwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],
         "vitb200_ln_bwd": [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
-                           c_void_p, Dropout, c_int, c_int, c_void_p],
+                           c_void_p, c_void_p, Dropout, c_int, c_int, c_void_p],
         "vitb200_attn_fwd": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p],
         "vitb200_attn_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                              c_float, c_void_p],
@@ -146,7 +149,7 @@ def _declare(L):
 
 EXPORTS = (
     "vitb200_last_error", "vitb200_version", "vitb200_device_ok", "vitb200_launch_count", "vitb200_prof_class_name",
-    "vitb200_prof_begin", "vitb200_prof_end", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
+    "vitb200_prof_begin", "vitb200_prof_end", "vitb200_abi_sizeof", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
     "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
     "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
     "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_bwd",

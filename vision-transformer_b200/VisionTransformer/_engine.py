@@ -61,7 +61,7 @@ class Plan:
 
     def block_bwd(self, d, layer, params, grads, x_in, acts, g, dy_in, dy_out, scratch):
         p = self._fill(_C.BlockParams, _C.BLOCK_FIELDS_P, params)
-        gr = self._fill(_C.BlockGrads, _C.BLOCK_FIELDS_G, grads)
+        gr = self._fill(_C.BlockGrads, _C.BLOCK_GRADS_STRUCT, grads)
         _C.check(_C.lib().vitb200_block_bwd(ctypes.byref(d), layer, ctypes.byref(p), ctypes.byref(gr), x_in.data_ptr(),
                                             acts.data_ptr(), g.data_ptr(), dy_in.data_ptr(),
                                             None if dy_out is None else dy_out.data_ptr(), scratch.data_ptr(),
@@ -89,6 +89,22 @@ class Plan:
     def new_lp(self, device):
         """[M, E] buffer in the activation dtype (masked gradient operands)."""
         return torch.empty(self.M, self.E, dtype=self.dtype, device=device)
+
+
+def chain_block_grads(block_grads):
+    """Per-layer gradient dicts for a whole-model backward: the LayerNorm-1 backward of layer i+1 already sums the
+    fc2 bias gradient of layer i (it produces the masked gradient that sum runs over), so layer i passes
+    b_fc2 = None (skip) and layer i+1 passes b_fc2_prev = layer i's b_fc2.  The last layer keeps its own b_fc2:
+    its incoming gradient is produced by the classifier head."""
+    out = []
+    n = len(block_grads)
+    for i, g in enumerate(block_grads):
+        c = dict(g)
+        c["b_fc2_prev"] = block_grads[i - 1]["b_fc2"] if i > 0 else None
+        if i < n - 1:
+            c["b_fc2"] = None
+        out.append(c)
+    return out
 
 
 # ---- small op wrappers used by the sub-module Functions and by tests -----------------------------------------

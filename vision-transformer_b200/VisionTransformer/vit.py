@@ -197,9 +197,10 @@ class _ViTFn(torch.autograd.Function):
                                   L.vitb200_head_act_bytes(ctypes.byref(d)), 256), dtype=torch.uint8, device=dev)
         hg = dict(zip(_C.HEAD_FIELDS, gv[4 + 11 * nL:]))
         eng.Plan.head_bwd(plan, d, hp, hg, head_acts, dlogits.contiguous().float(), g, dy_a, scratch)
+        bgs = eng.chain_block_grads([dict(zip(_C.BLOCK_FIELDS_G, gv[4 + 11 * i: 4 + 11 * (i + 1)]))
+                                     for i in range(nL)])
         for i in range(nL - 1, -1, -1):
-            bg = dict(zip(_C.BLOCK_FIELDS_G, gv[4 + 11 * i: 4 + 11 * (i + 1)]))
-            eng.Plan.block_bwd(plan, d, i, blk_params[i], bg, xs[i], blk_acts[i], g, dy_a, dy_b, scratch)
+            eng.Plan.block_bwd(plan, d, i, blk_params[i], bgs[i], xs[i], blk_acts[i], g, dy_a, dy_b, scratch)
             blk_acts[i] = None  # release this block's activations as soon as they are consumed
             dy_a, dy_b = dy_b, dy_a
         eg = dict(zip(_C.EMBED_FIELDS_G, gv[:4]))

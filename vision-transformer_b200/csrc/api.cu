@@ -145,4 +145,18 @@ int vitb200_gemm(const vitb200_gemm_args* a, void* stream) {
                   static_cast<const float*>(a->B), a->ldb, a->splits, ep, s);
 }
 
+int64_t vitb200_abi_sizeof(int which) {
+  switch (which) {
+    case 0: return sizeof(vitb200_dims);
+    case 1: return sizeof(vitb200_dropout);
+    case 2: return sizeof(vitb200_gemm_args);
+    case 3: return sizeof(vitb200_adamw_hyper);
+    case 4: return sizeof(vitb200_block_params);
+    case 5: return sizeof(vitb200_block_grads);
+    case 6: return sizeof(vitb200_head_params);
+    case 7: return sizeof(vitb200_prof_entry);
+    default: return -1;
+  }
+}
+
 }  // extern "C"

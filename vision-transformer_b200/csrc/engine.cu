@@ -250,7 +250,7 @@ int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_par
   e = make_ep(dn, F);
   VB_PROPAGATE(gemm_f32(B, F, Cc, 0, 1, dlogits, Cc, p->w3, F, 1, e, s));
   // LayerNorm(4E) backward in place (dn := d a), then GELU'
-  VB_PROPAGATE(ln_backward(dn, false, a.a, a.mean, a.rstd, p->ln_w, dn, 0, gr->ln_w, gr->ln_b, nullptr,
+  VB_PROPAGATE(ln_backward(dn, false, a.a, a.mean, a.rstd, p->ln_w, dn, 0, gr->ln_w, gr->ln_b, nullptr, nullptr,
                            make_dropout(0.f, 0, 0), B, F, s));
   VB_PROPAGATE(gelu_backward(a.h1, dn, static_cast<int64_t>(B) * F, s));
   // first linear: dW1 += dh1^T x0 ; db1 ; dx0 = dh1 W1
@@ -337,7 +337,7 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
   l = Lin(); l.M = E; l.N = F; l.K = M; l.a_major = 1; l.b_major = 1; l.A = dy_in; l.lda = E; l.B = a.h; l.ldb = F;
   l.ep = make_ep(gr->w_fc2, F); l.ep.accumulate = 1; l.out_f32 = true;
   VB_PROPAGATE(run_lin(bf, l, s));
-  VB_PROPAGATE(colsum(dy_in, bf, E, gr->b_fc2, M, E, s));
+  if (gr->b_fc2) VB_PROPAGATE(colsum(dy_in, bf, E, gr->b_fc2, M, E, s));
   // dh[M,4E] = (dy W2) * (h > 0)
   l = Lin(); l.M = M; l.N = F; l.K = E; l.b_major = 1; l.A = dy_in; l.lda = E; l.B = p->w_fc2; l.ldb = F;
   l.ep = make_ep(sc.s1, F); l.ep.mask_aux = a.h; l.ep.col_sum = gr->b_fc1; l.out_f32 = !bf;  // db1 += colsum(dh), fused
@@ -352,14 +352,13 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
   VB_PROPAGATE(run_lin(bf, l, s));
   // LN2 backward: g += dx ; emits s3 = cast(g * proj-dropout mask)
   VB_PROPAGATE(ln_backward(sc.s2, bf, a.x_mid, a.mean2, a.rstd2, p->ln2_w, g, 1, gr->ln2_w, gr->ln2_b, sc.s3,
-                           make_dropout(d->dropout_p, d->seed, drop_stream(layer, 0)), M, E, s));
+                           gr->b_proj, make_dropout(d->dropout_p, d->seed, drop_stream(layer, 0)), M, E, s));
 
   // ---- attention branch
-  // dWproj[E,E] += s3^T attn ; dbproj += colsum(s3)
+  // dWproj[E,E] += s3^T attn  (dbproj += colsum(s3) came out of the LN2 backward above)
   l = Lin(); l.M = E; l.N = E; l.K = M; l.a_major = 1; l.b_major = 1; l.A = sc.s3; l.lda = E; l.B = a.attn; l.ldb = E;
   l.ep = make_ep(gr->w_proj, E); l.ep.accumulate = 1; l.out_f32 = true;
   VB_PROPAGATE(run_lin(bf, l, s));
-  VB_PROPAGATE(colsum(sc.s3, bf, E, gr->b_proj, M, E, s));
   // dO[M,E] = s3 Wproj
   l = Lin(); l.M = M; l.N = E; l.K = E; l.b_major = 1; l.A = sc.s3; l.lda = E; l.B = p->w_proj; l.ldb = E;
   l.ep = make_ep(sc.s2, E); l.out_f32 = !bf;
@@ -378,7 +377,7 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
   // LN1 backward: g += dx ; emits dy_out = cast(g * fc2-dropout mask of layer-1) for the previous block
   const Dropout prev = make_dropout(layer > 0 ? d->dropout_p : 0.f, d->seed, drop_stream(layer - 1, 1));
   return ln_backward(sc.s2, bf, x_in, a.mean1, a.rstd1, p->ln1_w, g, 1, gr->ln1_w, gr->ln1_b,
-                     layer > 0 ? dy_out : nullptr, prev, M, E, s);
+                     layer > 0 ? dy_out : nullptr, layer > 0 ? gr->b_fc2_prev : nullptr, prev, M, E, s);
 }
 
 // ================================================================================================ single ops
@@ -388,8 +387,8 @@ int vitb200_ln_fwd(const float* x, const float* gamma, const float* beta, void* 
 }
 int vitb200_ln_bwd(const void* dy, int dy_dtype, const float* x, const float* mean, const float* rstd,
                    const float* gamma, float* g, int add_to_g, float* dgamma, float* dbeta, void* dyn,
-                   vitb200_dropout dd, int M, int E, void* stream) {
-  return ln_backward(dy, dy_dtype == VITB200_BF16, x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta, dyn,
+                   float* dyn_colsum, vitb200_dropout dd, int M, int E, void* stream) {
+  return ln_backward(dy, dy_dtype == VITB200_BF16, x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta, dyn, dyn_colsum,
                      make_dropout(dd.p, dd.seed, dd.stream), M, E, static_cast<cudaStream_t>(stream));
 }
 int vitb200_attn_fwd(const void* qkv, void* out, float* lse, int dtype, int B, int T, int H, int hs, float scale,

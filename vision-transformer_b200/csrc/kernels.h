@@ -27,7 +27,7 @@ int ln_forward(const float* x, const float* gamma, const float* beta, void* y, b
                float* rstd, int M, int E, float eps, cudaStream_t stream);
 int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean, const float* rstd,
                 const float* gamma, float* g, int add_to_g, float* dgamma, float* dbeta, void* dyn,
-                const Dropout& drop, int M, int E, cudaStream_t stream);
+                float* dyn_colsum, const Dropout& drop, int M, int E, cudaStream_t stream);
 
 // attention
 int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B, int T, int H, int hs,

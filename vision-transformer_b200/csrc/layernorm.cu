@@ -5,10 +5,14 @@
 //             shared memory then atomically into fp32 grads, and optionally emits the dropout-masked,
 //             down-cast gradient the next GEMM consumes (so no separate cast/mask pass exists).
 #include "common.cuh"
+#include "kernels.h"
+#include "ptx.cuh"
 
 namespace vb {
 
 namespace {
+
+using namespace ptx;
 
 constexpr int LN_WARPS = 8;
 constexpr int LN_THREADS = LN_WARPS * 32;
@@ -213,6 +217,186 @@ ln_bwd_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, const flo
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Backward, bulk-copy ring version (E % 8 == 0, E <= 1024): one persistent CTA per SM, 8 warps, each warp owns a ring
+// of NST row slots in shared memory.  Lane 0 of a warp issues 1-D bulk copies (x row, old g row, dy row) NST-1 rows
+// ahead of the row being processed, so ~2 rows per warp (~120 KB per SM) are in flight while the warp computes;
+// the row statistics, dgamma / dbeta / bias-gradient partial sums stay in registers.  The dropout keep-bits of a
+// row are generated once per 8 elements (lane l owns Philox blocks l, l+32, ...) and handed to the two lanes that
+// need them with one shuffle per chunk.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int LNB_WARPS = 8;
+constexpr int LNB_MAX_STAGES = 4;
+
+template <typename DyT, int CH>
+__global__ void __launch_bounds__(LNB_WARPS * 32, 1)
+ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
+                   const float* __restrict__ rstd_in, const float* __restrict__ gamma, float* __restrict__ g,
+                   int add_to_g, float* __restrict__ dgamma, float* __restrict__ dbeta, DyT* __restrict__ dyn,
+                   float* __restrict__ dyn_colsum, const Dropout drop, int M, int E, int nst) {
+  extern __shared__ __align__(128) uint8_t lnb_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* s_gamma = reinterpret_cast<float*>(lnb_smem);
+  float* s_acc = s_gamma + E;  // dgamma | dbeta | colsum(dyn)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_acc + 3 * static_cast<size_t>(E));
+  const uint32_t row_x = E * 4u, row_g = add_to_g ? E * 4u : 0u, row_dy = E * static_cast<uint32_t>(sizeof(DyT));
+  const uint32_t stage_bytes = row_x + row_g + row_dy;
+  uint64_t* bar = bars + warp * LNB_MAX_STAGES;
+  const uint32_t ring = smem_u32(bars + LNB_WARPS * LNB_MAX_STAGES) + warp * nst * stage_bytes;
+  const uint32_t sgam = smem_u32(s_gamma);
+
+  for (int i = threadIdx.x; i < E; i += blockDim.x) s_gamma[i] = __ldg(gamma + i);
+  for (int i = threadIdx.x; i < 3 * E; i += blockDim.x) s_acc[i] = 0.f;
+  if (lane == 0) {
+    for (int st = 0; st < nst; ++st) mbar_init(bar + st, 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+
+  const int E4 = E >> 2;
+  const int w0 = blockIdx.x * LNB_WARPS + warp, stride = gridDim.x * LNB_WARPS;
+  const int nrows = w0 < M ? (M - w0 + stride - 1) / stride : 0;
+  auto issue = [&](int it) {  // lane 0
+    const int st = it % nst;
+    const int64_t off = (static_cast<int64_t>(w0) + static_cast<int64_t>(it) * stride) * E;
+    const uint32_t dst = ring + st * stage_bytes;
+    mbar_arrive_expect_tx(bar + st, stage_bytes);
+    bulk_load_1d(dst, x + off, row_x, bar + st);
+    if (add_to_g) bulk_load_1d(dst + row_x, g + off, row_g, bar + st);
+    bulk_load_1d(dst + row_x + row_g, dy + off, row_dy, bar + st);
+  };
+  if (lane == 0)
+    for (int it = 0; it < nst - 1 && it < nrows; ++it) issue(it);
+
+  float rg[CH][4], rb[CH][4], rc[CH][4];
+#pragma unroll
+  for (int k = 0; k < CH; ++k)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { rg[k][j] = 0.f; rb[k][j] = 0.f; rc[k][j] = 0.f; }
+  const bool masked = dyn != nullptr && drop.p > 0.f;
+  const float inv_e = 1.f / static_cast<float>(E);
+  float mean_l = 0.f, rstd_l = 0.f;
+
+  for (int it = 0; it < nrows; ++it) {
+    if ((it & 31) == 0) {  // statistics of this warp's next 32 rows, one per lane
+      const int r = it + lane;
+      if (r < nrows) {
+        const int64_t m = static_cast<int64_t>(w0) + static_cast<int64_t>(r) * stride;
+        mean_l = __ldg(mean_in + m);
+        rstd_l = __ldg(rstd_in + m);
+      }
+    }
+    if (lane == 0 && it + nst - 1 < nrows) issue(it + nst - 1);
+    const float mean = __shfl_sync(0xffffffffu, mean_l, it & 31), rstd = __shfl_sync(0xffffffffu, rstd_l, it & 31);
+    const int st = it % nst;
+    const int64_t base = (static_cast<int64_t>(w0) + static_cast<int64_t>(it) * stride) * E;
+    uint32_t keep[(CH + 1) / 2];
+    if (masked) {  // independent of the loads: overlaps the wait below
+#pragma unroll
+      for (int c = 0; c < (CH + 1) / 2; ++c)
+        keep[c] = dropout_keep8(drop, (static_cast<uint64_t>(base) >> 3) + lane + 32 * c);
+    }
+    mbar_wait(bar + st, (it / nst) & 1);
+    const uint32_t sx = ring + st * stage_bytes, sg = sx + row_x, sdy = sg + row_g;
+
+    float h[CH][4], d[CH][4];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < CH; ++k) {
+      const int i = lane + 32 * k;
+      if (i < E4) {
+        const float4 xv = lds128(sx + 16 * i);
+        const float4 gm = lds128(sgam + 16 * i);
+        if constexpr (sizeof(DyT) == 2) {
+          const uint2 raw = lds64(sdy + 8 * i);
+          d[k][0] = __uint_as_float(raw.x << 16); d[k][1] = __uint_as_float(raw.x & 0xffff0000u);
+          d[k][2] = __uint_as_float(raw.y << 16); d[k][3] = __uint_as_float(raw.y & 0xffff0000u);
+        } else {
+          const float4 dv = lds128(sdy + 16 * i);
+          d[k][0] = dv.x; d[k][1] = dv.y; d[k][2] = dv.z; d[k][3] = dv.w;
+        }
+        h[k][0] = (xv.x - mean) * rstd; h[k][1] = (xv.y - mean) * rstd;
+        h[k][2] = (xv.z - mean) * rstd; h[k][3] = (xv.w - mean) * rstd;
+        const float gg[4] = {gm.x, gm.y, gm.z, gm.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float t = d[k][j] * gg[j];
+          s1 += t;
+          s2 = fmaf(t, h[k][j], s2);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { h[k][j] = 0.f; d[k][j] = 0.f; }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    s1 *= inv_e;
+    s2 *= inv_e;
+
+#pragma unroll
+    for (int k = 0; k < CH; ++k) {
+      const int i = lane + 32 * k;
+      uint32_t kb = 0xfu;
+      if (masked) kb = __shfl_sync(0xffffffffu, keep[k >> 1], (k & 1) * 16 + (lane >> 1)) >> ((lane & 1) * 4);
+      if (i < E4) {
+        const float4 gm = lds128(sgam + 16 * i);
+        const float gg[4] = {gm.x, gm.y, gm.z, gm.w};
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          o[j] = rstd * (d[k][j] * gg[j] - s1 - h[k][j] * s2);
+          rg[k][j] = fmaf(d[k][j], h[k][j], rg[k][j]);
+          rb[k][j] += d[k][j];
+        }
+        if (add_to_g) {
+          const float4 old = lds128(sg + 16 * i);
+          o[0] += old.x; o[1] += old.y; o[2] += old.z; o[3] += old.w;
+        }
+        reinterpret_cast<float4*>(g + base)[i] = make_float4(o[0], o[1], o[2], o[3]);
+        if (dyn != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            o[j] = masked ? ((kb >> j) & 1u ? o[j] * drop.scale : 0.f) : o[j];
+            rc[k][j] += o[j];
+          }
+          if constexpr (sizeof(DyT) == 2) {
+            uint2 pk;
+            pk.x = pack_bf16x2(o[0], o[1]);
+            pk.y = pack_bf16x2(o[2], o[3]);
+            reinterpret_cast<uint2*>(dyn + base)[i] = pk;
+          } else {
+            reinterpret_cast<float4*>(dyn + base)[i] = make_float4(o[0], o[1], o[2], o[3]);
+          }
+        }
+      }
+    }
+    __syncwarp();  // every lane is done with this slot before lane 0 refills it in the next iteration
+  }
+
+#pragma unroll
+  for (int k = 0; k < CH; ++k) {
+    const int i = lane + 32 * k;
+    if (i < E4) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        atomicAdd(&s_acc[i * 4 + j], rg[k][j]);
+        atomicAdd(&s_acc[E + i * 4 + j], rb[k][j]);
+        if (dyn_colsum) atomicAdd(&s_acc[2 * E + i * 4 + j], rc[k][j]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < E; i += blockDim.x) {
+    if (dgamma) atomicAdd(dgamma + i, s_acc[i]);
+    if (dbeta) atomicAdd(dbeta + i, s_acc[E + i]);
+    if (dyn_colsum) atomicAdd(dyn_colsum + i, s_acc[2 * E + i]);
+  }
+}
+
 // warps per CTA such that the per-warp row caches stay under ~96 KB of shared memory
 int ln_warps(int E, int rows_per_warp, int fixed_rows) {
   int w = (96 * 1024 / (E * 4) - fixed_rows) / rows_per_warp;
@@ -249,16 +433,48 @@ int ln_forward(const float* x, const float* gamma, const float* beta, void* y, b
 
 int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean, const float* rstd,
                 const float* gamma, float* g, int add_to_g, float* dgamma, float* dbeta, void* dyn,
-                const Dropout& drop, int M, int E, cudaStream_t stream) {
+                float* dyn_colsum, const Dropout& drop, int M, int E, cudaStream_t stream) {
   VB_REQUIRE(M > 0 && E > 0, "ln_backward: empty input");
+  VB_REQUIRE(dyn_colsum == nullptr || dyn != nullptr, "ln_backward: dyn_colsum needs dyn");
+  const double es = dy_bf16 ? 2 : 4;  // bytes: x read, dy read, g write (+read when add_to_g), dyn write, stats
+  ProfScope prof(kProfLnBwd, static_cast<double>(M) * E * (4 + es + 4 + (add_to_g ? 4 : 0) + (dyn ? es : 0)) + 8.0 * M,
+                 1, stream);
+  // ---- ring kernel
+  if ((E & 7) == 0 && E <= 1024 && M >= 4 * LNB_WARPS) {
+    const size_t stage = static_cast<size_t>(E) * (4 + (add_to_g ? 4 : 0) + (dy_bf16 ? 2 : 4));
+    const size_t fixed = static_cast<size_t>(E) * 16 + LNB_WARPS * LNB_MAX_STAGES * 8;
+    int nst = static_cast<int>((216 * 1024 - fixed) / (LNB_WARPS * stage));
+    if (nst > LNB_MAX_STAGES) nst = LNB_MAX_STAGES;
+    if (nst >= 2) {
+      const size_t smem = fixed + static_cast<size_t>(nst) * LNB_WARPS * stage;
+      const int ch = ceil_div(E, 128);
+      const int grid = std::min(num_sms(), ceil_div(M, LNB_WARPS));
+#define VB_LN_RING(T, C)                                                                                          \
+  do {                                                                                                            \
+    VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
+                                       static_cast<int>(smem)));                                                  \
+    ln_bwd_ring_kernel<T, C><<<grid, LNB_WARPS * 32, smem, stream>>>(                                             \
+        static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta, static_cast<T*>(dyn),        \
+        dyn_colsum, drop, M, E, nst);                                                                             \
+  } while (0)
+#define VB_LN_RING_CH(T)                                                                                          \
+  do {                                                                                                            \
+    if (ch <= 1) VB_LN_RING(T, 1); else if (ch <= 2) VB_LN_RING(T, 2); else if (ch <= 3) VB_LN_RING(T, 3);        \
+    else if (ch <= 4) VB_LN_RING(T, 4); else if (ch <= 6) VB_LN_RING(T, 6); else VB_LN_RING(T, 8);                \
+  } while (0)
+      if (dy_bf16) VB_LN_RING_CH(bf16); else VB_LN_RING_CH(float);
+#undef VB_LN_RING_CH
+#undef VB_LN_RING
+      VB_CHECK_LAUNCH();
+      return kOk;
+    }
+  }
+  // ---- generic kernel (odd E, very wide rows, tiny M)
   const int nw = ln_warps(E, 2, 2);
   const size_t smem = (2 + 2 * static_cast<size_t>(nw)) * E * sizeof(float);
   VB_REQUIRE(smem <= 200 * 1024, "ln_backward: row too long (E=%d)", E);
   // fewer, fatter CTAs than forward: each CTA ends with 2*E global atomics
   const int grid = ln_grid(M, nw, 2);
-  const double es = dy_bf16 ? 2 : 4;  // bytes: x read, dy read, g write (+read when add_to_g), dyn write, stats
-  ProfScope prof(kProfLnBwd, static_cast<double>(M) * E * (4 + es + 4 + (add_to_g ? 4 : 0) + (dyn ? es : 0)) + 8.0 * M,
-                 1, stream);
   const int vpl = ((E & 3) == 0 && E <= 512) ? 4 : ((E & 3) == 0 && E <= 1024) ? 8 : ((E & 3) == 0 && E <= 1536) ? 12 : 0;
 #define VB_LN_BWD(T, V)                                                                                          \
   do {                                                                                                           \
@@ -276,6 +492,7 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
   }
 #undef VB_LN_BWD
   VB_CHECK_LAUNCH();
+  if (dyn_colsum) VB_PROPAGATE(colsum(dyn, dy_bf16, E, dyn_colsum, M, E, stream));
   return kOk;
 }
 

@@ -161,7 +161,7 @@ class DPTrainer:
         self.embed_p["w_lp"] = self.shadow[o:o + n] if self.shadow is not None else None
         self.embed_g = ptrs("embed", _C.EMBED_FIELDS_G, grads=True)
         self.block_p = [ptrs(i, _C.BLOCK_FIELDS_P, lowp=lp) for i in range(self.L)]
-        self.block_g = [ptrs(i, _C.BLOCK_FIELDS_G, grads=True) for i in range(self.L)]
+        self.block_g = eng.chain_block_grads([ptrs(i, _C.BLOCK_FIELDS_G, grads=True) for i in range(self.L)])
         self.head_p = ptrs("head", _C.HEAD_FIELDS)
         self.head_g = ptrs("head", _C.HEAD_FIELDS, grads=True)
 
