@@ -79,7 +79,8 @@ typedef struct {
   int row_period;        /* 0 = identity row map */
   int row_group_stride;
   const float* residual; /* [..][ldc] fp32 or NULL (requires out_dtype F32) */
-  int splits;            /* split-K factor (atomic accumulate), 0 = auto only when accumulate != 0 */
+  int splits;            /* split-K factor (atomic accumulate), 0 = auto only when accumulate != 0; -1 (fp32 inputs):
+                          * also allow an atomic split-K into a zeroed C when accumulate == 0 (not bit-reproducible) */
   int accumulate;        /* 1: C += result via fp32 atomics (C must be fp32) */
   float* col_sum;        /* [N] fp32 or NULL: col_sum[n] += sum_m (value stored at C[m,n]) — fused bias gradient */
 } vitb200_gemm_args;

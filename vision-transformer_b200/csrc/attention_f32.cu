@@ -79,6 +79,44 @@ __global__ void attn_delta_kernel(const T_* __restrict__ o, const T_* __restrict
   if (lane == 0) delta[static_cast<int64_t>(bh) * T + i] = s;
 }
 
+// Vectorised variant: one thread per 16-byte chunk, CPH consecutive lanes make up one (token, head) slice
+// (CPH = hs * sizeof(T) / 16, a power of two), partial dot products combined with CPH-wide shuffles.  Fully
+// coalesced: the kernel streams o and dO exactly once.
+template <typename T_, int CPH>
+__global__ void __launch_bounds__(256)
+attn_delta_vec_kernel(const uint4* __restrict__ o, const uint4* __restrict__ d_o, float* __restrict__ delta,
+                      int64_t total_chunks, int T, int H) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; c < total_chunks + (threadIdx.x & 31);
+       c += stride) {  // whole warps stay in the loop (shuffles); blockDim and stride are multiples of CPH
+    float s = 0.f;
+    if (c < total_chunks) {
+      const uint4 a = __ldcs(o + c), b = __ldcs(d_o + c);
+      if constexpr (sizeof(T_) == 2) {
+        const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          s = fmaf(__uint_as_float(av[j] << 16), __uint_as_float(bv[j] << 16), s);
+          s = fmaf(__uint_as_float(av[j] & 0xffff0000u), __uint_as_float(bv[j] & 0xffff0000u), s);
+        }
+      } else {
+        s = __uint_as_float(a.x) * __uint_as_float(b.x) + __uint_as_float(a.y) * __uint_as_float(b.y) +
+            __uint_as_float(a.z) * __uint_as_float(b.z) + __uint_as_float(a.w) * __uint_as_float(b.w);
+      }
+    }
+#pragma unroll
+    for (int o2 = CPH / 2; o2 > 0; o2 >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o2);
+    if (c < total_chunks && (c & (CPH - 1)) == 0) {
+      const int64_t hr = c / CPH;                 // (token, head)
+      const int64_t tok = hr / H;
+      const int h = static_cast<int>(hr - tok * H);
+      const int64_t b = tok / T;
+      const int i = static_cast<int>(tok - b * T);
+      delta[(b * H + h) * T + i] = s;
+    }
+  }
+}
+
 // dQ: one warp per query row i.  ds_ij = p_ij (dP_ij - delta_i) * scale ; dq_i = sum_j ds_ij k_j
 __global__ void __launch_bounds__(AF_WARPS * 32)
 attn_f32_bwd_dq_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, const float* __restrict__ lse,
@@ -176,6 +214,30 @@ int set_smem(K kern, size_t smem) {
 int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B, int T, int H, int hs,
                cudaStream_t stream) {
   ProfScope prof(kProfAttnBwd, 0.0, 1, stream);
+  const int cph = hs * (is_bf16 ? 2 : 4) / 16;
+  if (hs * (is_bf16 ? 2 : 4) % 16 == 0 && (cph & (cph - 1)) == 0 && cph >= 1 && cph <= 32 && aligned16(o) &&
+      aligned16(d_o)) {
+    const int64_t chunks = static_cast<int64_t>(B) * T * H * cph;
+    const int grid_v = static_cast<int>(std::min<int64_t>((chunks + 255) / 256, static_cast<int64_t>(num_sms()) * 16));
+    const uint4* o4 = static_cast<const uint4*>(o);
+    const uint4* d4 = static_cast<const uint4*>(d_o);
+#define VB_DELTA(T, C) attn_delta_vec_kernel<T, C><<<grid_v, 256, 0, stream>>>(o4, d4, delta, chunks, T_, H)
+    const int T_ = T;
+    if (is_bf16) {
+      switch (cph) {
+        case 1: VB_DELTA(bf16, 1); break; case 2: VB_DELTA(bf16, 2); break; case 4: VB_DELTA(bf16, 4); break;
+        case 8: VB_DELTA(bf16, 8); break; case 16: VB_DELTA(bf16, 16); break; default: VB_DELTA(bf16, 32); break;
+      }
+    } else {
+      switch (cph) {
+        case 1: VB_DELTA(float, 1); break; case 2: VB_DELTA(float, 2); break; case 4: VB_DELTA(float, 4); break;
+        case 8: VB_DELTA(float, 8); break; case 16: VB_DELTA(float, 16); break; default: VB_DELTA(float, 32); break;
+      }
+    }
+#undef VB_DELTA
+    VB_CHECK_LAUNCH();
+    return kOk;
+  }
   const int total_warps = B * H * T;
   const int threads = 256;
   const int grid = ceil_div(total_warps * 32, threads);

@@ -267,19 +267,92 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
 // queries — the transposed orientation, because a tensor-memory A operand cannot be transposed):
 //   MODE 0:  S = Q_t K^T, dP = dO_t V^T            -> dS = P o (dP - delta) * scale         -> dQ_t = dS K
 //   MODE 1:  S^T = K_t Q^T, dP^T = V_t dO^T        -> P^T, dS^T                              -> dV_t = P^T dO, dK_t = dS^T Q
-// with P = exp2(S*c - lse*log2e) recomputed from the saved log-sum-exp (no row reductions in backward).  S / dP live
-// in tensor-memory columns [0,TP) / [256,256+TP); the bf16 results overwrite them in place and feed TS-MMAs whose
-// accumulators sit in the dead upper halves ([128,192) and [384,448)).  One (item, 128-row tile) unit is in flight
-// per CTA; 8 element-wise warps split its columns (2 threads per row, chunk-interleaved, one 64-thread named
-// barrier per round keeps the in-place overwrite race-free).
+// with P = exp2(S*c - lse*log2e) recomputed from the saved log-sum-exp (no row reductions in backward).
+//
+// A unit = one (image, head) item x one 128-row tile.  Its columns are cut into nchk chunks of <= W columns; chunks
+// flow through TWO tensor-memory slots ([S | dP], 2W columns each) so that the three engines overlap:
+//   MMA thread    : S/dP of chunk g+1 is issued BEFORE the output MMAs of chunk g (tensor pipe never waits on math)
+//   element-wise  : warps 2-5 own slot 0 (even chunks), warps 6-9 own slot 1 (odd chunks); one thread per row reads
+//                   fp32 S/dP, writes bf16 P/dS back IN PLACE (ascending, so it only overwrites what it already read)
+//   output MMAs   : TS form, A = the bf16 chunk straight from tensor memory, accumulate over the unit's chunks into
+//                   two accumulators at columns 384..447 | 448..511 (MODE 0: dQ split by k-step parity, MODE 1: dV | dK)
+// Both groups drain half of each accumulator (32 columns) once a unit's last chunk is committed.
 constexpr int kBwdThreads = 64 + 8 * 32;
 constexpr int kStatBytes = 2048;            // lse*log2e [256] | delta*scale [256] per stage
 
 struct BwdParams {
   int T, TP, H, items, stages;
+  int W, nchk;                              // chunk width (multiple of 16) and chunks per unit
   int tile_bytes, stage_bytes;              // TP*128, 4*tile_bytes + kStatBytes
   float scale, scale_log2;
+  int dbg;                                  // timing experiments only (VITB200_ATTN_DBG), 0 in production
+  long long* trace;                         // optional event trace of CTA 0 (tools/attn_trace.py), else nullptr
 };
+
+#define VB_TR(tag)                                                                      \
+  do {                                                                                  \
+    if (trbuf != nullptr && trn < 512) trbuf[trn++] = (clock64() << 8) | (tag);         \
+  } while (0)
+
+template <int N>
+__device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&r)[N]) {
+  if constexpr (N == 32) ptx::tmem_ld_32x32(taddr, r); else ptx::tmem_ld_32x16(taddr, r);
+}
+template <int N>
+__device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[N]) {
+  if constexpr (N == 16) ptx::tmem_st_32x16(taddr, r); else ptx::tmem_st_32x8(taddr, r);
+}
+
+// N columns [c0, c0+N) of one chunk (global column index gcol0 .. gcol0+N-1) for this thread's row.
+template <int MODE, int N>
+__device__ __forceinline__ void bwd_piece(uint32_t tS, uint32_t tP, int c0, int gcol0, int T, float sl2, float scale,
+                                          float lse2r, float dscr, const float* __restrict__ stat) {
+  uint32_t rs[N], rp[N];
+  tmem_ld_n<N>(tS + static_cast<uint32_t>(c0), rs);
+  tmem_ld_n<N>(tP + static_cast<uint32_t>(c0), rp);
+  ptx::tmem_ld_wait();
+  uint32_t pk0[N / 2], pk1[N / 2];
+  if (MODE == 0) {
+    if (gcol0 + N <= T) {                  // all keys valid (warp-uniform): no per-element predicates
+#pragma unroll
+      for (int j = 0; j < N / 2; ++j) {
+        const float e0 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j]), sl2, -lse2r)) *
+                         fmaf(__uint_as_float(rp[2 * j]), scale, -dscr);
+        const float e1 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j + 1]), sl2, -lse2r)) *
+                         fmaf(__uint_as_float(rp[2 * j + 1]), scale, -dscr);
+        pk0[j] = pack_bf16x2(e0, e1);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < N / 2; ++j) {
+        const int k0 = gcol0 + 2 * j;
+        float e0 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j]), sl2, -lse2r));
+        float e1 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j + 1]), sl2, -lse2r));
+        e0 = k0 < T ? e0 * fmaf(__uint_as_float(rp[2 * j]), scale, -dscr) : 0.f;
+        e1 = k0 + 1 < T ? e1 * fmaf(__uint_as_float(rp[2 * j + 1]), scale, -dscr) : 0.f;
+        pk0[j] = pack_bf16x2(e0, e1);
+      }
+    }
+  } else {
+    const float4* l4 = reinterpret_cast<const float4*>(stat + gcol0);
+    const float4* d4 = reinterpret_cast<const float4*>(stat + 256 + gcol0);
+#pragma unroll
+    for (int j4 = 0; j4 < N / 4; ++j4) {
+      const float4 lv = l4[j4], dv = d4[j4];
+      const float lj[4] = {lv.x, lv.y, lv.z, lv.w}, dj[4] = {dv.x, dv.y, dv.z, dv.w};
+      float pe[4], de[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        pe[i] = ptx::ex2(fmaf(__uint_as_float(rs[4 * j4 + i]), sl2, -lj[i]));
+        de[i] = pe[i] * fmaf(__uint_as_float(rp[4 * j4 + i]), scale, -dj[i]);
+      }
+      pk0[2 * j4] = pack_bf16x2(pe[0], pe[1]); pk0[2 * j4 + 1] = pack_bf16x2(pe[2], pe[3]);
+      pk1[2 * j4] = pack_bf16x2(de[0], de[1]); pk1[2 * j4 + 1] = pack_bf16x2(de[2], de[3]);
+    }
+  }
+  tmem_st_n<N / 2>(tS + static_cast<uint32_t>(c0 >> 1), pk0);
+  if (MODE == 1) tmem_st_n<N / 2>(tP + static_cast<uint32_t>(c0 >> 1), pk1);
+}
 
 template <int MODE>
 __global__ void __launch_bounds__(kBwdThreads, 1)
@@ -290,18 +363,23 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   // barriers live AFTER the stages and the over-read pad (see host side)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.stages * p.stage_bytes + (32768 - p.tile_bytes));
-  uint64_t* kv_full = bars;         // [2] TMA bytes landed
-  uint64_t* st_full = bars + 2;     // [2] row statistics staged (32 producer lanes)
-  uint64_t* kv_empty = bars + 4;    // [2]
-  uint64_t* sd_full = bars + 6;     // S and dP ready
-  uint64_t* ew_done = bars + 7;     // bf16 operands written (8 warps)
-  uint64_t* acc_full = bars + 8;    // output accumulators ready
-  uint64_t* t_free = bars + 9;      // accumulators drained (8 warps)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* kv_full = bars;          // [2] TMA bytes landed
+  uint64_t* st_full = bars + 2;      // [2] row statistics staged (32 producer lanes)
+  uint64_t* kv_empty = bars + 4;     // [2]
+  uint64_t* sd_full = bars + 6;      // [2] S and dP of the chunk in slot s are ready
+  uint64_t* ew_done = bars + 8;      // [2] bf16 operands of slot s written (4 warps)
+  uint64_t* slot_free = bars + 10;   // [2] output MMAs that read slot s have completed
+  uint64_t* acc_full = bars + 12;    // unit's accumulators complete
+  uint64_t* acc_free = bars + 13;    // accumulators drained (8 warps)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int E = p.H * HS;
   const int ntile = p.T > QT ? 2 : 1;
+  const int nchk = p.nchk, W = p.W;
+  const bool dual = p.TP >= 32;      // MODE 0: a unit's first chunk then has >= 2 k-steps, so both accumulators get initialised
+  constexpr uint32_t kAcc0 = 384u;   // MODE 0: dQ (even k-steps) | MODE 1: dV
+  constexpr uint32_t kAcc1 = 448u;   // MODE 0: dQ (odd k-steps)  | MODE 1: dK
 
   if (threadIdx.x == 0) {
     ptx::tma_prefetch_desc(&tm_qkv);
@@ -310,11 +388,12 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       ptx::mbar_init(&kv_full[s], 1);
       ptx::mbar_init(&st_full[s], 32);
       ptx::mbar_init(&kv_empty[s], 1);
+      ptx::mbar_init(&sd_full[s], 1);
+      ptx::mbar_init(&ew_done[s], 4);
+      ptx::mbar_init(&slot_free[s], 1);
     }
-    ptx::mbar_init(sd_full, 1);
-    ptx::mbar_init(ew_done, 8);
     ptx::mbar_init(acc_full, 1);
-    ptx::mbar_init(t_free, 8);
+    ptx::mbar_init(acc_free, 8);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -355,161 +434,181 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
     if (lane == 0) {
-      const uint32_t idesc_s = ptx::make_idesc_bf16_f32(QT, p.TP, 0, 0);
+      long long* trbuf = (p.trace != nullptr && blockIdx.x == 0) ? p.trace + MODE * 2048 : nullptr;
+      int trn = 0;
       const uint32_t idesc_o = ptx::make_idesc_bf16_f32(QT, HS, 0, 1);
-      int it = 0, u = 0;
+      struct Pending { uint32_t sq, sk, sdo; int slot, st, col0, wc, u; uint32_t gph; bool first, last, last_item; };
+      Pending pd{};
+      bool have = false;
+      auto issue_out = [&](const Pending& c) {
+        VB_TR(4);
+        ptx::mbar_wait(&ew_done[c.slot], c.gph);
+        VB_TR(5);
+        if (c.first) ptx::mbar_wait(acc_free, (static_cast<uint32_t>(c.u) & 1u) ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t tS = tmem_base + static_cast<uint32_t>(c.slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
+        const int k0 = c.col0 / 16, nk = c.wc / 16;
+        // Back-to-back MMAs into ONE accumulator serialise on its latency (~114 clk each, measured); two independent
+        // accumulators interleaved run at ~55 clk each.  MODE 0 therefore splits dQ over two accumulators by k-step
+        // parity (summed in the drain); MODE 1 alternates dV and dK.
+        if (MODE == 0) {
+          for (int k = 0; k < nk; ++k)            // dQ(k parity) += dS K
+            ptx::umma_f16_ts(tmem_base + ((dual && (k & 1)) ? kAcc1 : kAcc0), tS + static_cast<uint32_t>(k * 8),
+                             ptx::make_smem_desc_sw128(c.sk + (k0 + k) * 2048, 64 * 128, 1024), idesc_o,
+                             (c.first && k < (dual ? 2 : 1)) ? 0u : 1u);
+        } else {
+          for (int k = 0; k < nk; ++k) {
+            ptx::umma_f16_ts(tmem_base + kAcc0, tS + static_cast<uint32_t>(k * 8),            // dV += P^T dO
+                             ptx::make_smem_desc_sw128(c.sdo + (k0 + k) * 2048, 64 * 128, 1024), idesc_o,
+                             (c.first && k == 0) ? 0u : 1u);
+            ptx::umma_f16_ts(tmem_base + kAcc1, tP + static_cast<uint32_t>(k * 8),            // dK += dS^T Q
+                             ptx::make_smem_desc_sw128(c.sq + (k0 + k) * 2048, 64 * 128, 1024), idesc_o,
+                             (c.first && k == 0) ? 0u : 1u);
+          }
+        }
+        ptx::umma_commit(&slot_free[c.slot]);
+        VB_TR(6);
+        if (c.last) ptx::umma_commit(acc_full);
+        if (c.last_item) ptx::umma_commit(&kv_empty[c.st]);
+      };
+      int it = 0, u = 0, g = 0;
       for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
         const int st = p.stages == 2 ? (it & 1) : 0;
         const uint32_t ph = p.stages == 2 ? ((it >> 1) & 1) : (it & 1);
         const uint32_t sq = ptx::smem_u32(smem + st * p.stage_bytes);
         const uint32_t sk = sq + p.tile_bytes, sv = sk + p.tile_bytes, sdo = sv + p.tile_bytes;
-        // MODE 0: rows from Q / dO, columns from K / V, output B = K.   MODE 1: rows from K / V, columns Q / dO.
+        // MODE 0: rows from Q / dO, columns from K / V.   MODE 1: rows from K / V, columns from Q / dO.
         const uint32_t a1 = MODE == 0 ? sq : sk, b1 = MODE == 0 ? sk : sq;
         const uint32_t a2 = MODE == 0 ? sdo : sv, b2 = MODE == 0 ? sv : sdo;
+        VB_TR(7);
         ptx::mbar_wait(&kv_full[st], ph);
         ptx::tc_fence_after();
+        VB_TR(8);
         for (int t = 0; t < ntile; ++t, ++u) {
-          const uint32_t up = u & 1;
-          ptx::mbar_wait(t_free, up ^ 1u);
-          ptx::tc_fence_after();
+          for (int j = 0; j < nchk; ++j, ++g) {
+            const int slot = g & 1;
+            const uint32_t gph = (static_cast<uint32_t>(g) >> 1) & 1u;
+            const int col0 = j * W, wc = min(W, p.TP - col0);
+            const uint32_t idesc_s = ptx::make_idesc_bf16_f32(QT, wc, 0, 0);
+            const uint32_t tS = tmem_base + static_cast<uint32_t>(slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
+            VB_TR(1);
+            ptx::mbar_wait(&slot_free[slot], gph ^ 1u);
+            ptx::tc_fence_after();
+            VB_TR(2);
 #pragma unroll
-          for (int k = 0; k < HS / 16; ++k)
-            ptx::umma_f16(tmem_base, ptx::make_smem_desc_sw128(a1 + t * (QT * 128) + k * 32, 16, 1024),
-                          ptx::make_smem_desc_sw128(b1 + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
-#pragma unroll
-          for (int k = 0; k < HS / 16; ++k)
-            ptx::umma_f16(tmem_base + 256u, ptx::make_smem_desc_sw128(a2 + t * (QT * 128) + k * 32, 16, 1024),
-                          ptx::make_smem_desc_sw128(b2 + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
-          ptx::umma_commit(sd_full);
-          ptx::mbar_wait(ew_done, up);
-          ptx::tc_fence_after();
-          if (MODE == 0) {
-            for (int k = 0; k < p.TP / 16; ++k)     // dQ = dS K
-              ptx::umma_f16_ts(tmem_base + 128u, tmem_base + static_cast<uint32_t>(k * 8),
-                               ptx::make_smem_desc_sw128(sk + k * 2048, 64 * 128, 1024), idesc_o, k > 0 ? 1u : 0u);
-          } else {
-            for (int k = 0; k < p.TP / 16; ++k)     // dV = P^T dO
-              ptx::umma_f16_ts(tmem_base + 128u, tmem_base + static_cast<uint32_t>(k * 8),
-                               ptx::make_smem_desc_sw128(sdo + k * 2048, 64 * 128, 1024), idesc_o, k > 0 ? 1u : 0u);
-            for (int k = 0; k < p.TP / 16; ++k)     // dK = dS^T Q
-              ptx::umma_f16_ts(tmem_base + 384u, tmem_base + 256u + static_cast<uint32_t>(k * 8),
-                               ptx::make_smem_desc_sw128(sq + k * 2048, 64 * 128, 1024), idesc_o, k > 0 ? 1u : 0u);
+            for (int k = 0; k < HS / 16; ++k) {   // S and dP interleaved: two independent accumulator chains
+              ptx::umma_f16(tS, ptx::make_smem_desc_sw128(a1 + t * (QT * 128) + k * 32, 16, 1024),
+                            ptx::make_smem_desc_sw128(b1 + col0 * 128 + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
+              ptx::umma_f16(tP, ptx::make_smem_desc_sw128(a2 + t * (QT * 128) + k * 32, 16, 1024),
+                            ptx::make_smem_desc_sw128(b2 + col0 * 128 + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(&sd_full[slot]);
+            VB_TR(3);
+            if (have) issue_out(pd);
+            pd.sq = sq; pd.sk = sk; pd.sdo = sdo; pd.slot = slot; pd.st = st; pd.col0 = col0; pd.wc = wc; pd.u = u;
+            pd.gph = gph; pd.first = j == 0; pd.last = j == nchk - 1;
+            pd.last_item = pd.last && t == ntile - 1;
+            have = true;
           }
-          ptx::umma_commit(acc_full);
         }
-        ptx::umma_commit(&kv_empty[st]);
       }
+      if (have) issue_out(pd);
     }
   } else {
-    // ------------------------------------------------------------------ element-wise warps: 2 threads per row
+    // ------------------------------------------------------------------ element-wise warps: one thread per row
     const int q = warp & 3;                      // tensor-memory lane quarter
-    const int part = (warp - 2) >> 2;            // which chunk parity / which half of the output columns
+    const int grp = (warp - 2) >> 2;             // slot / chunk parity owned by this warp; half of the drain columns
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    const int nchunk = (p.TP + 31) / 32;
-    const int nround = (nchunk + 1) / 2;
+    const uint32_t tS = lane_base + static_cast<uint32_t>(grp * 2 * W), tP = tS + static_cast<uint32_t>(W);
     const float sl2 = p.scale_log2, scale = p.scale;
-    int it = 0, u = 0;
+    const int my_items = blockIdx.x < p.items ? (p.items - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int total_units = my_items * ntile;
+    int next_drain = 0;
+    long long* trbuf = (p.trace != nullptr && blockIdx.x == 0 && q == 0 && lane == 0) ? p.trace + MODE * 2048 + 512 * (1 + grp) : nullptr;
+    int trn = 0;
+
+    auto drain = [&](int u) {
+      const int it_u = u / ntile, t = u - it_u * ntile;
+      const int item = blockIdx.x + it_u * gridDim.x;
+      const int b = item / p.H, h = item - b * p.H;
+      const int row = t * QT + q * 32 + lane;
+      VB_TR(14);
+      ptx::mbar_wait(acc_full, static_cast<uint32_t>(u) & 1u);
+      ptx::tc_fence_after();
+      VB_TR(15);
+      uint32_t r0[32], r1[32];
+      ptx::tmem_ld_32x32(lane_base + kAcc0 + static_cast<uint32_t>(grp * 32), r0);
+      if (MODE == 1 || dual) ptx::tmem_ld_32x32(lane_base + kAcc1 + static_cast<uint32_t>(grp * 32), r1);
+      ptx::tmem_ld_wait();
+      if (MODE == 0 && dual) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r0[j] = __float_as_uint(__uint_as_float(r0[j]) + __uint_as_float(r1[j]));
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(acc_free);
+      if (row < p.T && !(p.dbg & 2)) {
+        bf16* grow = dqkv + (static_cast<int64_t>(b) * p.T + row) * (3 * static_cast<int64_t>(E)) + h * HS + grp * 32;
+        // MODE 0: dQ -> section 0.  MODE 1: accumulator 0 = dV -> section 2, accumulator 1 = dK -> section 1.
+        bf16* d0 = grow + (MODE == 0 ? 0 : 2) * static_cast<int64_t>(E);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 v;
+          v.x = pack_bf16x2(__uint_as_float(r0[8 * j + 0]), __uint_as_float(r0[8 * j + 1]));
+          v.y = pack_bf16x2(__uint_as_float(r0[8 * j + 2]), __uint_as_float(r0[8 * j + 3]));
+          v.z = pack_bf16x2(__uint_as_float(r0[8 * j + 4]), __uint_as_float(r0[8 * j + 5]));
+          v.w = pack_bf16x2(__uint_as_float(r0[8 * j + 6]), __uint_as_float(r0[8 * j + 7]));
+          *reinterpret_cast<uint4*>(d0 + j * 8) = v;
+        }
+        if (MODE == 1) {
+          bf16* d1 = grow + static_cast<int64_t>(E);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 v;
+            v.x = pack_bf16x2(__uint_as_float(r1[8 * j + 0]), __uint_as_float(r1[8 * j + 1]));
+            v.y = pack_bf16x2(__uint_as_float(r1[8 * j + 2]), __uint_as_float(r1[8 * j + 3]));
+            v.z = pack_bf16x2(__uint_as_float(r1[8 * j + 4]), __uint_as_float(r1[8 * j + 5]));
+            v.w = pack_bf16x2(__uint_as_float(r1[8 * j + 6]), __uint_as_float(r1[8 * j + 7]));
+            *reinterpret_cast<uint4*>(d1 + j * 8) = v;
+          }
+        }
+      }
+    };
+
+    int it = 0, u = 0, g = 0;
     for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
       const int st = p.stages == 2 ? (it & 1) : 0;
       const uint32_t ph = p.stages == 2 ? ((it >> 1) & 1) : (it & 1);
-      const int b = item / p.H, h = item - b * p.H;
       const float* stat = reinterpret_cast<const float*>(smem + st * p.stage_bytes + 4 * p.tile_bytes);
       ptx::mbar_wait(&st_full[st], ph);
       for (int t = 0; t < ntile; ++t, ++u) {
-        const uint32_t up = u & 1;
         const int row = t * QT + q * 32 + lane;  // query (MODE 0) or key (MODE 1) index of this thread
         float lse2r = 0.f, dscr = 0.f;
         if (MODE == 0) { lse2r = stat[row]; dscr = stat[256 + row]; }
-        ptx::mbar_wait(sd_full, up);
-        ptx::tc_fence_after();
-        for (int rd = 0; rd < nround; ++rd) {
-          const int c = 2 * rd + part;
-          const bool active = c < nchunk;
-          uint32_t pk0[16], pk1[16];
-          if (active) {
-            uint32_t rs[32], rp[32];
-            ptx::tmem_ld_32x32(lane_base + static_cast<uint32_t>(c * 32), rs);
-            ptx::tmem_ld_32x32(lane_base + 256u + static_cast<uint32_t>(c * 32), rp);
-            ptx::tmem_ld_wait();
-            if (MODE == 0) {
-              if (c * 32 + 32 <= p.T) {            // all 32 keys valid (warp-uniform): no per-element predicates
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                  const float e0 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j]), sl2, -lse2r)) *
-                                   fmaf(__uint_as_float(rp[2 * j]), scale, -dscr);
-                  const float e1 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j + 1]), sl2, -lse2r)) *
-                                   fmaf(__uint_as_float(rp[2 * j + 1]), scale, -dscr);
-                  pk0[j] = pack_bf16x2(e0, e1);
-                }
-              } else {
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                  const int k0 = c * 32 + 2 * j;
-                  float e0 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j]), sl2, -lse2r));
-                  float e1 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j + 1]), sl2, -lse2r));
-                  e0 = k0 < p.T ? e0 * fmaf(__uint_as_float(rp[2 * j]), scale, -dscr) : 0.f;
-                  e1 = k0 + 1 < p.T ? e1 * fmaf(__uint_as_float(rp[2 * j + 1]), scale, -dscr) : 0.f;
-                  pk0[j] = pack_bf16x2(e0, e1);
-                }
-              }
-            } else {
-              const float4* l4 = reinterpret_cast<const float4*>(stat + c * 32);
-              const float4* d4 = reinterpret_cast<const float4*>(stat + 256 + c * 32);
-#pragma unroll
-              for (int j4 = 0; j4 < 8; ++j4) {
-                const float4 lv = l4[j4], dv = d4[j4];
-                const float lj[4] = {lv.x, lv.y, lv.z, lv.w}, dj[4] = {dv.x, dv.y, dv.z, dv.w};
-                float pe[4], de[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  pe[i] = ptx::ex2(fmaf(__uint_as_float(rs[4 * j4 + i]), sl2, -lj[i]));
-                  de[i] = pe[i] * fmaf(__uint_as_float(rp[4 * j4 + i]), scale, -dj[i]);
-                }
-                pk0[2 * j4] = pack_bf16x2(pe[0], pe[1]); pk0[2 * j4 + 1] = pack_bf16x2(pe[2], pe[3]);
-                pk1[2 * j4] = pack_bf16x2(de[0], de[1]); pk1[2 * j4 + 1] = pack_bf16x2(de[2], de[3]);
-              }
-            }
-          }
-          // both threads of every row have READ chunks 2rd and 2rd+1 before either overwrites columns [32rd, 32rd+32)
-          asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
-          if (active) {
-            ptx::tmem_st_32x16(lane_base + static_cast<uint32_t>(c * 16), pk0);
-            if (MODE == 1) ptx::tmem_st_32x16(lane_base + 256u + static_cast<uint32_t>(c * 16), pk1);
-          }
+        for (int j = 0; j < nchk; ++j, ++g) {
+          if ((g & 1) != grp) continue;
+          const int col0 = j * W, wc = min(W, p.TP - col0);
+          VB_TR(10);
+          ptx::mbar_wait(&sd_full[grp], (static_cast<uint32_t>(g) >> 1) & 1u);
+          ptx::tc_fence_after();
+          VB_TR(11);
+          int c0 = 0;
+          if (p.dbg & 1) c0 = wc;                 // experiment: no element-wise work
+          for (; c0 + 32 <= wc; c0 += 32)
+            bwd_piece<MODE, 32>(tS, tP, c0, col0 + c0, p.T, sl2, scale, lse2r, dscr, stat);
+          if (c0 < wc) bwd_piece<MODE, 16>(tS, tP, c0, col0 + c0, p.T, sl2, scale, lse2r, dscr, stat);
+          ptx::tmem_st_wait();
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&ew_done[grp]);
+          VB_TR(12);
+          // accumulators of every unit whose last chunk is <= g are (about to be) complete: take my half
+          while (next_drain < total_units && (next_drain + 1) * nchk - 1 <= g) drain(next_drain++);
         }
-        ptx::tmem_st_wait();
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(ew_done);
-        // drain: this warp takes columns [32*part, 32*part+32) of each 64-column accumulator
-        ptx::mbar_wait(acc_full, up);
-        ptx::tc_fence_after();
-        const bool live = row < p.T;
-        bf16* grow = dqkv + (static_cast<int64_t>(b) * p.T + row) * (3 * static_cast<int64_t>(E)) + h * HS + part * 32;
-#pragma unroll
-        for (int o = 0; o < (MODE == 0 ? 1 : 2); ++o) {
-          uint32_t r[32];
-          ptx::tmem_ld_32x32(lane_base + (o == 0 ? 128u : 384u) + static_cast<uint32_t>(part * 32), r);
-          ptx::tmem_ld_wait();
-          // MODE 0: dQ -> section 0.  MODE 1: accumulator 0 = dV -> section 2, accumulator 1 = dK -> section 1.
-          bf16* dst = grow + (MODE == 0 ? 0 : (o == 0 ? 2 : 1)) * static_cast<int64_t>(E);
-          if (live) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 v;
-              v.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
-              v.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
-              v.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
-              v.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
-              *reinterpret_cast<uint4*>(dst + j * 8) = v;
-            }
-          }
-        }
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(t_free);
       }
     }
+    while (next_drain < total_units) drain(next_drain++);
+    VB_TR(16);
   }
 
   ptx::tc_fence_before();
@@ -569,7 +668,15 @@ int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const f
   const int pad = 32768 - p.tile_bytes;      // an A tile of rows [128,256) may over-read past a TP-row operand
   p.stages = (2 * p.stage_bytes + pad + 256 + 1024 <= 227 * 1024) ? 2 : 1;
   p.scale = scale; p.scale_log2 = scale * kLog2e;
+  static const int dbg = getenv("VITB200_ATTN_DBG") ? atoi(getenv("VITB200_ATTN_DBG")) : 0;
+  p.dbg = dbg;
+  p.trace = getenv("VITB200_ATTN_TRACE") ? reinterpret_cast<long long*>(strtoull(getenv("VITB200_ATTN_TRACE"), nullptr, 0)) : nullptr;
   const int smem = p.stages * p.stage_bytes + pad + 256 + 1024;
+  // chunk width: two [S | dP] slots of 2W columns + the accumulators must fit 512 tensor-memory columns
+  auto chunking = [&](int wmax) {
+    p.nchk = ceil_div(p.TP, wmax);
+    p.W = ceil_div(ceil_div(p.TP, p.nchk), 16) * 16;
+  };
   CUtensorMap tq, td;
   VB_PROPAGATE(make_tmap_bf16(&tq, qkv, M, 3 * static_cast<int64_t>(E), 3 * static_cast<int64_t>(E), HS, p.TP));
   VB_PROPAGATE(make_tmap_bf16(&td, d_o, M, E, E, HS, p.TP));
@@ -577,6 +684,7 @@ int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const f
   VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * static_cast<double>(T) * hs, 2, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
+  chunking(96);    // two slots of 2W columns + two 64-column accumulators: 4W + 128 <= 512
   attn_tc_bwd_kernel<1><<<grid, kBwdThreads, smem, stream>>>(tq, td, lse, delta, dqkv, p);
   VB_CHECK_LAUNCH();
   attn_tc_bwd_kernel<0><<<grid, kBwdThreads, smem, stream>>>(tq, td, lse, delta, dqkv, p);

@@ -259,7 +259,7 @@ int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_par
   VB_PROPAGATE(gemm_f32(F, E, B, 1, 1, dn, F, a.x0, E, 1, e, s));
   VB_PROPAGATE(colsum(dn, false, F, gr->b1, B, F, s));
   e = make_ep(dx0, E);
-  VB_PROPAGATE(gemm_f32(B, E, F, 0, 1, dn, F, p->w1, E, 1, e, s));
+  VB_PROPAGATE(gemm_f32(B, E, F, 0, 1, dn, F, p->w1, E, -1, e, s));  // few tiles, K = 4E: atomic split-K allowed
   // scatter into the residual-stream gradient (token 0 only) + masked low-precision copy for the last fc2
   const Dropout dr = make_dropout(d->dropout_p, d->seed, drop_stream(n_layers - 1, 1));
   return head_scatter(dx0, g, dy_out, is_bf16(d), dr, B, d->T, E, s);

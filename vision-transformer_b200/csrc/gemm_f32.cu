@@ -11,8 +11,9 @@ namespace {
 
 constexpr int FBM = 128, FBN = 128, FBK = 8, FTHREADS = 256;
 
-__device__ __forceinline__ float epilogue_store1_f32(const GemmEpilogue& ep, int m, int n, int N, float v) {
-  if (ep.bias != nullptr) v += __ldg(ep.bias + n);
+// first: this CTA holds the first K-split (the additive epilogue terms are applied exactly once per element)
+__device__ __forceinline__ float epilogue_store1_f32(const GemmEpilogue& ep, int m, int n, int N, float v, bool first) {
+  if (ep.bias != nullptr && first) v += __ldg(ep.bias + n);
   if (ep.relu) v = fmaxf(v, 0.f);
   const int64_t off = epi_out_row(ep, m) * ep.ldc + n;
   if (ep.mask_aux != nullptr) v = reinterpret_cast<const float*>(ep.mask_aux)[off] > 0.f ? v : 0.f;
@@ -20,11 +21,11 @@ __device__ __forceinline__ float epilogue_store1_f32(const GemmEpilogue& ep, int
     const uint64_t lin = static_cast<uint64_t>(m) * static_cast<uint64_t>(N) + static_cast<uint64_t>(n);
     v *= dropout_factor1(ep.drop, lin);
   }
-  if (ep.row_add != nullptr) {
+  if (ep.row_add != nullptr && first) {
     const int pr = ep.row_period > 0 ? (m % ep.row_period) : m;
     v += __ldg(ep.row_add + static_cast<int64_t>(pr) * N + n);
   }
-  if (ep.residual != nullptr) v += ep.residual[off];
+  if (ep.residual != nullptr && first) v += ep.residual[off];
   float* c = reinterpret_cast<float*>(ep.C) + off;
   if (ep.accumulate) atomicAdd(c, v);
   else *c = v;
@@ -100,7 +101,7 @@ gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int n = n0 + tx * 8 + j;
-      if (n < N) cs[j] += epilogue_store1_f32(ep, m, n, N, acc[i][j]);
+      if (n < N) cs[j] += epilogue_store1_f32(ep, m, n, N, acc[i][j], blockIdx.z == 0);
     }
   }
   if (ep.col_sum != nullptr) {
@@ -112,14 +113,54 @@ gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
   }
 }
 
+// Skinny output (N <= 16, both operands K-major): one warp per output row, lanes stride over K with 16-byte loads,
+// fixed-order warp reduction => bit-reproducible.  The classifier's last Linear (N = num_classes) lands here.
+__global__ void __launch_bounds__(256)
+gemm_f32_skinny_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ B, int64_t ldb, int M, int N,
+                       int K, int vec, const GemmEpilogue ep) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= M) return;
+  const float* a = A + static_cast<int64_t>(warp) * lda;
+  for (int n = 0; n < N; ++n) {
+    const float* b = B + static_cast<int64_t>(n) * ldb;
+    float s = 0.f;
+    if (vec) {
+      for (int k = lane * 4; k < K; k += 128) {
+        const float4 av = *reinterpret_cast<const float4*>(a + k), bv = __ldg(reinterpret_cast<const float4*>(b + k));
+        s = fmaf(av.x, bv.x, s); s = fmaf(av.y, bv.y, s); s = fmaf(av.z, bv.z, s); s = fmaf(av.w, bv.w, s);
+      }
+    } else {
+      for (int k = lane; k < K; k += 32) s = fmaf(a[k], __ldg(b + k), s);
+    }
+    s = warp_sum(s);
+    if (lane == 0) epilogue_store1_f32(ep, warp, n, N, s, true);
+  }
+}
+
 }  // namespace
 
 int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int64_t lda, const float* B,
              int64_t ldb, int splits, const GemmEpilogue& ep_in, cudaStream_t stream) {
   VB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_f32: empty problem M=%d N=%d K=%d", M, N, K);
   GemmEpilogue ep = ep_in;
+  if (N <= 16 && a_major == 0 && b_major == 0 && !ep.accumulate && ep.col_sum == nullptr && M >= 32) {
+    ProfScope prof(kProfGemmF32, 2.0 * M * N * K, 1, stream);
+    const int vec = (K & 3) == 0 && (lda & 3) == 0 && (ldb & 3) == 0 && aligned16(A) && aligned16(B);
+    gemm_f32_skinny_kernel<<<ceil_div(M * 32, 256), 256, 0, stream>>>(A, lda, B, ldb, M, N, K, vec, ep);
+    VB_CHECK_LAUNCH();
+    return kOk;
+  }
   int s = ep.accumulate ? splits : 1;
   const int tiles = ceil_div(M, FBM) * ceil_div(N, FBN);
+  // Few output tiles but a long K (the classifier head, M = batch): split K across CTAs into a zeroed output.
+  // Only for epilogues that are linear in the accumulator (bias / row_add / residual are added by split 0).
+  // Atomic accumulation order is not reproducible, so this is opt-in (splits == -1; backward call sites).
+  if (splits == -1 && !ep.accumulate && 2 * tiles <= num_sms() && K >= 256 && !ep.relu && ep.mask_aux == nullptr &&
+      ep.drop.p <= 0.f && ep.col_sum == nullptr && ep.row_period == 0 && ep.residual == nullptr) {
+    VB_CHECK_CUDA(cudaMemset2DAsync(ep.C, static_cast<size_t>(ep.ldc) * 4, 0, static_cast<size_t>(N) * 4, M, stream));
+    ep.accumulate = 1;
+    s = 0;
+  }
   if (s <= 0) {
     s = ceil_div(2 * num_sms(), tiles);
     const int max_s = K / 64 > 0 ? K / 64 : 1;
