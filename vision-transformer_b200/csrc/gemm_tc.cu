@@ -20,18 +20,21 @@ namespace {
 constexpr int BM = 128;          // UMMA M (cta_group::1)
 constexpr int BK = 64;           // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kStages = 4;
 constexpr int kEpiWarps = 8;         // 2 per TMEM lane quarter: each pair splits the accumulator columns
 constexpr int kThreads = 64 + kEpiWarps * 32;
 
-template <int BN>
+// CG = 1: one CTA owns a 128 x BN tile.  CG = 2: a CTA PAIR (cluster of 2, tcgen05 cta_group::2) owns a 256 x BN tile;
+// each CTA stages its own 128 rows of A and HALF of the B tile, the leader issues M = 256 MMAs that read both halves,
+// so every SM pulls a third less operand traffic through L2 and shared memory per output element.
+template <int BN, int CG>
 struct TileCfg {
-  static constexpr int A_BYTES = BM * BK * 2;       // 16 KB
-  static constexpr int B_BYTES = BN * BK * 2;       // 32 KB @ BN=256
+  static constexpr int STAGES = CG == 2 ? 6 : 4;
+  static constexpr int A_BYTES = BM * BK * 2;            // 16 KB
+  static constexpr int B_BYTES = BN * BK * 2 / CG;       // 32 KB @ BN=256 (16 KB per CTA of a pair)
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_BYTES = 256;
   static constexpr int STG_BYTES = kEpiWarps * 32 * 128;   // per epilogue warp: 32 rows x 32 fp32 transpose buffer
-  static constexpr int SMEM_BYTES = kStages * STAGE_BYTES + BAR_BYTES + STG_BYTES + 1024;  // +1024 alignment slack
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES + 1024;  // +1024 alignment slack
   static constexpr int TMEM_COLS = 2 * BN;
 };
 
@@ -41,11 +44,16 @@ struct TcParams {
   int splits, kb_per_split, kb_total;
 };
 
-template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI>
+template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                const TcParams p, const GemmEpilogue ep) {
-  using Cfg = TileCfg<BN>;
+  using Cfg = TileCfg<BN, CG>;
+  constexpr int kStages = Cfg::STAGES;
+  // pair rank / work-unit walk: a unit is one (tile, split); CTAs of a pair walk the same units
+  const uint32_t rank = CG == 2 ? ptx::cluster_ctarank() : 0u;
+  const int walker = CG == 2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int nwalkers = CG == 2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::STAGE_BYTES);
@@ -68,16 +76,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tmem_full[s], 1);
-      ptx::mbar_init(&tmem_empty[s], kEpiWarps);
+      ptx::mbar_init(&tmem_empty[s], kEpiWarps * CG);   // pair: the leader's barrier collects both CTAs' epilogue warps
     }
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
-    ptx::tmem_alloc(tmem_ptr, Cfg::TMEM_COLS);
-    ptx::tmem_relinquish();
+    if constexpr (CG == 2) {
+      ptx::tmem_alloc_pair(tmem_ptr, Cfg::TMEM_COLS);
+      ptx::tmem_relinquish_pair();
+    } else {
+      ptx::tmem_alloc(tmem_ptr, Cfg::TMEM_COLS);
+      ptx::tmem_relinquish();
+    }
   }
   ptx::tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) ptx::cluster_sync(); else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
@@ -86,31 +99,36 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      for (int w = walker; w < total_work; w += nwalkers) {
         const int split = w / tiles;
         const int tile = w - split * tiles;
         const int m_blk = tile / p.n_tiles;
         const int n_blk = tile - m_blk * p.n_tiles;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+        const int m_row = (m_blk * CG + static_cast<int>(rank)) * BM;          // my 128 rows of A
+        const int n_row = n_blk * BN + static_cast<int>(rank) * (BN / CG);     // my share of the B tile
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1u);
-          ptx::mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+          // pair: the leader's barrier expects the bytes of BOTH CTAs; the peer's copies are credited to it
+          if (CG == 1 || rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], CG * Cfg::STAGE_BYTES);
           uint8_t* sA = smem + stage * Cfg::STAGE_BYTES;
           uint8_t* sB = sA + Cfg::A_BYTES;
+          auto load = [&](uint8_t* dst, const CUtensorMap* tm, int c0, int c1) {
+            if constexpr (CG == 2) ptx::tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
+            else ptx::tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
+          };
           if constexpr (AMAJ == 0) {
-            ptx::tma_load_2d(sA, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
+            load(sA, &tma_a, kb * BK, m_row);
           } else {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              ptx::tma_load_2d(sA + j * (BK * 128), &tma_a, &full_bar[stage], m_blk * BM + j * 64, kb * BK);
+            for (int j = 0; j < BM / 64; ++j) load(sA + j * (BK * 128), &tma_a, m_row + j * 64, kb * BK);
           }
           if constexpr (BMAJ == 0) {
-            ptx::tma_load_2d(sB, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+            load(sB, &tma_b, kb * BK, n_row);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              ptx::tma_load_2d(sB + j * (BK * 128), &tma_b, &full_bar[stage], n_blk * BN + j * 64, kb * BK);
+            for (int j = 0; j < BN / CG / 64; ++j) load(sB + j * (BK * 128), &tma_b, n_row + j * 64, kb * BK);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
@@ -118,8 +136,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(BM, BN, AMAJ, BMAJ);
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(BM * CG, BN, AMAJ, BMAJ);
       // K-major: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.
       // MN-major: 64-wide MN slabs BK*128 B apart (LBO), 8 k-rows = 1024 B (SBO), k-step = 16 rows * 128 B.
       constexpr uint32_t a_lbo = AMAJ == 0 ? 16 : BK * 128, a_sbo = 1024, a_kstep = AMAJ == 0 ? 32 : 2048;
@@ -128,7 +146,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+      for (int w = walker; w < total_work; w += nwalkers) {
         const int split = w / tiles;
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
@@ -144,12 +162,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t da = ptx::make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, a_sbo);
             const uint64_t db = ptx::make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, b_sbo);
-            ptx::umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if constexpr (CG == 2) ptx::umma_f16_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else ptx::umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          ptx::umma_commit(&empty_bar[stage]);   // smem slot reusable once these MMAs retire
+          // smem slot reusable once these MMAs retire (pair: in both CTAs)
+          if constexpr (CG == 2) ptx::umma_commit_pair(&empty_bar[stage], 3); else ptx::umma_commit(&empty_bar[stage]);
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        ptx::umma_commit(&tmem_full[acc]);        // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (pair: each CTA drains its own 128 lanes)
+        if constexpr (CG == 2) ptx::umma_commit_pair(&tmem_full[acc], 3); else ptx::umma_commit(&tmem_full[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
@@ -166,12 +187,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     const int cg = lane & 3;             // 8-column group within the chunk
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
+    for (int w = walker; w < total_work; w += nwalkers) {
       const int split = w / tiles;
       const int tile = w - split * tiles;
       const int m_blk = tile / p.n_tiles;
       const int n_blk = tile - m_blk * p.n_tiles;
-      const int m0 = m_blk * BM + q * 32;
+      const int m0 = (m_blk * CG + static_cast<int>(rank)) * BM + q * 32;
       // While the mainloop of this tile is still running: pull the epilogue's read-side operands (residual rows,
       // dReLU mask rows) of my 32 x (BN/2) sub-tile into L2, one row segment per lane.
       if (VB_EPI(kEpiResidual | kEpiMask, ep.residual != nullptr || ep.mask_aux != nullptr)) {
@@ -280,16 +301,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       ptx::tmem_ld_wait();
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+      if (lane == 0) {
+        if constexpr (CG == 2) ptx::mbar_arrive_cluster(&tmem_empty[acc], 0); else ptx::mbar_arrive(&tmem_empty[acc]);
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) ptx::cluster_sync(); else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if constexpr (CG == 2) ptx::tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS); else ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
@@ -346,11 +369,11 @@ int make_tmap_bf16(void* map_out, const void* base, int64_t rows, int64_t cols, 
 
 namespace {
 
-template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI>
-int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
-              cudaStream_t stream) {
-  using Cfg = TileCfg<BN>;
-  auto kern = gemm_tc_kernel<AMAJ, BMAJ, BN, OutT, EPI>;
+template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG>
+int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
+                 cudaStream_t stream) {
+  using Cfg = TileCfg<BN, CG>;
+  auto kern = gemm_tc_kernel<AMAJ, BMAJ, BN, OutT, EPI, CG>;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
@@ -358,11 +381,37 @@ int launch_tc(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, c
   });
   VB_CHECK_CUDA(attr_err);
   ProfScope prof(kProfGemmTc, 2.0 * p.M * p.N * p.K, 1, stream);
-  const int total = p.m_tiles * p.n_tiles * p.splits;
-  const int grid = total < num_sms() ? total : num_sms();
-  kern<<<grid, kThreads, Cfg::SMEM_BYTES, stream>>>(ta, tb, p, ep);
+  const int total = p.m_tiles * p.n_tiles * p.splits;     // work units (one per CTA, or per CTA pair)
+  if constexpr (CG == 1) {
+    const int grid = total < num_sms() ? total : num_sms();
+    kern<<<grid, kThreads, Cfg::SMEM_BYTES, stream>>>(ta, tb, p, ep);
+  } else {
+    const int pairs = num_sms() / 2;
+    const int grid = 2 * (total < pairs ? total : pairs);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, ep));
+  }
   VB_CHECK_LAUNCH();
   return kOk;
+}
+
+// pairs = true: operands / TcParams were prepared for 256-row tiles and half-width B boxes
+template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI>
+int launch_tc(bool pairs, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
+              cudaStream_t stream) {
+  if (pairs) return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 2>(ta, tb, p, ep, stream);
+  return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 1>(ta, tb, p, ep, stream);
 }
 
 }  // namespace
@@ -379,22 +428,27 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   VB_REQUIRE(ep.residual == nullptr || out_f32, "gemm_tc: residual add needs an fp32 output");
   constexpr int BN = 256;
 
+  // CTA pairs (256-row tiles) whenever there is more than one 128-row tile of output; VITB200_GEMM_CG=1|2 forces.
+  static const int force_cg = getenv("VITB200_GEMM_CG") ? atoi(getenv("VITB200_GEMM_CG")) : 0;
+  const int cg = force_cg == 1 || force_cg == 2 ? force_cg : (M > BM ? 2 : 1);
+  const bool pairs = cg == 2;
+
   CUtensorMap ta, tb;
   if (a_major == 0) VB_PROPAGATE(make_tmap_bf16(&ta, A, M, K, lda, BK, BM));
   else              VB_PROPAGATE(make_tmap_bf16(&ta, A, K, M, lda, 64, BK));
-  if (b_major == 0) VB_PROPAGATE(make_tmap_bf16(&tb, B, N, K, ldb, BK, BN));
+  if (b_major == 0) VB_PROPAGATE(make_tmap_bf16(&tb, B, N, K, ldb, BK, BN / cg));
   else              VB_PROPAGATE(make_tmap_bf16(&tb, B, K, N, ldb, 64, BK));
 
   TcParams p;
   p.M = M; p.N = N; p.K = K;
-  p.m_tiles = ceil_div(M, BM);
+  p.m_tiles = ceil_div(M, BM * cg);
   p.n_tiles = ceil_div(N, BN);
   p.kb_total = ceil_div(K, BK);
   int s = splits;
   if (!ep.accumulate) s = 1;
   if (s <= 0) {  // auto: aim for ~2 waves of work units, at least 4 k-blocks per split
     const int tiles = p.m_tiles * p.n_tiles;
-    s = ceil_div(2 * num_sms(), tiles);
+    s = ceil_div(2 * (num_sms() / cg), tiles);
     const int max_s = p.kb_total / 4 > 0 ? p.kb_total / 4 : 1;
     if (s > max_s) s = max_s;
     if (s < 1) s = 1;
@@ -405,29 +459,29 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   // Hot call sites of the training step get a compile-time-specialised epilogue; anything else runs the generic one.
   const uint32_t f = epi_flags(ep);
 #define VB_TC(AM, BM_, T, FL) \
-  if (f == (FL)) return launch_tc<AM, BM_, BN, T, (FL)>(ta, tb, p, ep, stream)
+  if (f == (FL)) return launch_tc<AM, BM_, BN, T, (FL)>(pairs, ta, tb, p, ep, stream)
   if (a_major == 0 && b_major == 0) {
     if (out_f32) {
       VB_TC(0, 0, float, 0u);
       VB_TC(0, 0, float, kEpiBias | kEpiResidual);
       VB_TC(0, 0, float, kEpiBias | kEpiDrop | kEpiResidual);
       VB_TC(0, 0, float, kEpiBias | kEpiRowMap);
-      return launch_tc<0, 0, BN, float, kEpiGeneric>(ta, tb, p, ep, stream);
+      return launch_tc<0, 0, BN, float, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
     }
     VB_TC(0, 0, bf16, 0u);
     VB_TC(0, 0, bf16, kEpiBias | kEpiRelu);
-    return launch_tc<0, 0, BN, bf16, kEpiGeneric>(ta, tb, p, ep, stream);
+    return launch_tc<0, 0, BN, bf16, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
   } else if (a_major == 0 && b_major == 1) {
-    if (out_f32) return launch_tc<0, 1, BN, float, kEpiGeneric>(ta, tb, p, ep, stream);
+    if (out_f32) return launch_tc<0, 1, BN, float, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
     VB_TC(0, 1, bf16, 0u);
     VB_TC(0, 1, bf16, kEpiMask | kEpiColSum);
-    return launch_tc<0, 1, BN, bf16, kEpiGeneric>(ta, tb, p, ep, stream);
+    return launch_tc<0, 1, BN, bf16, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
   } else if (a_major == 1 && b_major == 1) {
     if (out_f32) {
       VB_TC(1, 1, float, kEpiAccum);
-      return launch_tc<1, 1, BN, float, kEpiGeneric>(ta, tb, p, ep, stream);
+      return launch_tc<1, 1, BN, float, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
     }
-    return launch_tc<1, 1, BN, bf16, kEpiGeneric>(ta, tb, p, ep, stream);
+    return launch_tc<1, 1, BN, bf16, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
   }
 #undef VB_TC
   set_error("gemm_tc: operand major combination a=%d b=%d not instantiated", a_major, b_major);
