@@ -200,7 +200,9 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
                       void* stream);
 
 /* Classifier head on token 0 (vit.py:69-74,80): Linear(E,4E) -> GELU(erf) -> LayerNorm(4E) -> Linear(4E,cls); fp32. */
-typedef struct { const float *w1, *b1, *ln_w, *ln_b, *w3, *b3; } vitb200_head_params;
+/* w1_lp (optional, bf16 copy of w1): in bf16 mode the two large head products (x0 W1^T and its backward pair) run
+ * on the tensor-core path, as they do under the reference's autocast; NULL keeps the whole head in fp32. */
+typedef struct { const float *w1, *b1, *ln_w, *ln_b, *w3, *b3; const void* w1_lp; } vitb200_head_params;
 typedef struct { float *w1, *b1, *ln_w, *ln_b, *w3, *b3; } vitb200_head_grads;
 int64_t vitb200_head_act_bytes(const vitb200_dims* d);
 int vitb200_head_fwd(const vitb200_dims* d, const vitb200_head_params* p, const float* x_last, float* logits,

@@ -92,3 +92,69 @@ def test_trainer_step_host_matches_step(lib):
     assert diff.max().item() <= 3 * 2 * 1e-3
     with pytest.raises(RuntimeError, match="Sizes of tensors must match"):
         tr_a.step(x[:2].cuda(), y[:2].cuda())
+
+
+# ---------------------------------------------------------------------------------------------- data parallel
+def _dp_worker(rank, world, port, out):
+    """One rank of a 2-process data-parallel step.  Both ranks share cuda:0 (gloo moves the buckets), so the real
+    DPTrainer exchange path — bucket events, side stream, async all-reduce, 1/world inside AdamW — runs on one GPU."""
+    import os
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import train_dp
+        E, H, L, B, P, img, classes = 64, 2, 3, 2, 8, 32, 3
+        tr = train_dp.DPTrainer(input_channels=3, num_classes=classes, image_size=img, patch_size=P, embedding_size=E,
+                                num_heads=H, num_blocks=L, batch_size=B, dtype=torch.float32, dropout_p=0.0, lr=1e-3,
+                                process_group=dist.group.WORLD, world_size=world, bucket_mb=0.05)
+        cfg = ref_vit.Cfg(3, classes, (img // P) ** 2, E, P, H, L, B)
+        sd = ref_vit.random_state_dict(cfg, seed=31)
+        tr.load_state_dict(sd)
+        tr.broadcast_parameters(0)
+        gen = torch.Generator().manual_seed(32)
+        x = torch.rand(world * B, 3, img, img, generator=gen)
+        y = torch.randint(0, classes, (world * B,), generator=gen)
+        xs, ys = x[rank * B:(rank + 1) * B], y[rank * B:(rank + 1) * B]
+        d = tr._dims(False)
+        tr.forward(xs.cuda(), d)
+        tr.backward(ys.cuda(), d)
+        torch.cuda.synchronize()
+        # expectation: SUM over ranks of each rank's local-mean-loss gradient (oracle, fp32)
+        expect = None
+        for r in range(world):
+            _, _, g = ref_vit.loss_and_grads(sd, x[r * B:(r + 1) * B], y[r * B:(r + 1) * B], cfg)
+            expect = g if expect is None else {k: expect[k] + g[k] for k in g}
+        mine = tr.grads_by_ref_key()
+        worst = max(rel_err(mine[k], expect[k]) for k in expect)
+        nb = len(tr.buckets)
+        # the optimizer divides by world: parameters after one step == AdamW on the averaged gradient
+        mine_c = {k: v.clone().cpu() for k, v in mine.items()}
+        tr.optimizer_step()
+        new = tr.state_dict()
+        ok_step = True
+        for k in sd:
+            p = sd[k].clone()
+            ref_vit.adamw_step(p, mine_c[k] / world, torch.zeros_like(p), torch.zeros_like(p), 1, lr=1e-3)
+            ok_step = ok_step and torch.allclose(new[k].cpu(), p, rtol=1e-4, atol=2e-6)
+        out[rank] = (float(worst), int(nb), bool(ok_step))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_data_parallel_step_matches_oracle(lib):
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_dp_worker, args=(2, port, out), nprocs=2, join=True)
+        res = dict(out)
+    assert set(res) == {0, 1}
+    for r, (worst, nb, ok_step) in res.items():
+        assert nb >= 3, "the test must exercise several buckets"
+        assert worst < 1e-4, (r, worst)
+        assert ok_step, r

@@ -73,11 +73,12 @@ BLOCK_FIELDS_P = ("ln1_w", "ln1_b", "ln2_w", "ln2_b", "w_qkv", "w_proj", "b_proj
 BLOCK_FIELDS_G = ("ln1_w", "ln1_b", "ln2_w", "ln2_b", "w_qkv", "w_proj", "b_proj", "w_fc1", "b_fc1", "w_fc2", "b_fc2")
 BLOCK_GRADS_STRUCT = BLOCK_FIELDS_G + ("b_fc2_prev",)  # vitb200_block_grads: own gradients + the chained bias pointer
 HEAD_FIELDS = ("w1", "b1", "ln_w", "ln_b", "w3", "b3")
+HEAD_PARAMS_STRUCT = HEAD_FIELDS + ("w1_lp",)  # vitb200_head_params: fp32 parameters + the optional bf16 copy of w1
 EmbedParams = _ptr_struct("EmbedParams", EMBED_FIELDS_P)
 EmbedGrads = _ptr_struct("EmbedGrads", EMBED_FIELDS_G)
 BlockParams = _ptr_struct("BlockParams", BLOCK_FIELDS_P)
 BlockGrads = _ptr_struct("BlockGrads", BLOCK_GRADS_STRUCT)
-HeadParams = _ptr_struct("HeadParams", HEAD_FIELDS)
+HeadParams = _ptr_struct("HeadParams", HEAD_PARAMS_STRUCT)
 HeadGrads = _ptr_struct("HeadGrads", HEAD_FIELDS)
 
 _lib = None

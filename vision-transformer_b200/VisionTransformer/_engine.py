@@ -68,12 +68,12 @@ class Plan:
                                             _C.stream_ptr()))
 
     def head_fwd(self, d, params, x_last, logits, acts):
-        p = self._fill(_C.HeadParams, _C.HEAD_FIELDS, params)
+        p = self._fill(_C.HeadParams, _C.HEAD_PARAMS_STRUCT, params)
         _C.check(_C.lib().vitb200_head_fwd(ctypes.byref(d), ctypes.byref(p), x_last.data_ptr(), logits.data_ptr(),
                                            acts.data_ptr(), _C.stream_ptr()))
 
     def head_bwd(self, d, params, grads, acts, dlogits, g, dy_out, scratch):
-        p = self._fill(_C.HeadParams, _C.HEAD_FIELDS, params)
+        p = self._fill(_C.HeadParams, _C.HEAD_PARAMS_STRUCT, params)
         gr = self._fill(_C.HeadGrads, _C.HEAD_FIELDS, grads)
         _C.check(_C.lib().vitb200_head_bwd(ctypes.byref(d), self.L, ctypes.byref(p), ctypes.byref(gr), acts.data_ptr(),
                                            dlogits.data_ptr(), g.data_ptr(), dy_out.data_ptr(), scratch.data_ptr(),

@@ -163,6 +163,7 @@ class _ViTFn(torch.autograd.Function):
                 xs = xs[-2:]
 
         hp = dict(zip(_C.HEAD_FIELDS, (t.detach() for t in params[4 + 11 * nL:])))
+        hp["w1_lp"] = model._w(params[4 + 11 * nL]) if dt == torch.bfloat16 else None   # bf16 shadow of mlp.0.weight
         head_acts = nb(L.vitb200_head_act_bytes(ctypes.byref(d)))
         logits = torch.empty(B, classes, dtype=torch.float32, device=dev)
         eng.Plan.head_fwd(plan, d, hp, xs[-1], logits, head_acts)

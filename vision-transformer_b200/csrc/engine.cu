@@ -81,7 +81,11 @@ EmbedGeom embed_geom(const vitb200_dims* d) {
 // ------------------------------------------------------------------------------------------------ head
 struct HeadActs {
   float *x0, *h1, *a, *n, *mean, *rstd;
+  bf16* x0_lp;   // [B,E] bf16 copy of token 0 (tensor-core path of the first Linear)
 };
+inline bool head_lp(const vitb200_dims* d, const vitb200_head_params* p) {
+  return is_bf16(d) && p->w1_lp != nullptr && d->E % 8 == 0;
+}
 HeadActs carve_head(const vitb200_dims* d, void* acts, size_t* total = nullptr) {
   Carver c(acts);
   HeadActs h;
@@ -92,6 +96,7 @@ HeadActs carve_head(const vitb200_dims* d, void* acts, size_t* total = nullptr) 
   h.n = c.take<float>(B * 4 * E * 4);
   h.mean = c.take<float>(B * 4);
   h.rstd = c.take<float>(B * 4);
+  h.x0_lp = c.take<bf16>(B * E * 2);
   if (total) *total = c.off;
   return h;
 }
@@ -225,7 +230,12 @@ int vitb200_head_fwd(const vitb200_dims* d, const vitb200_head_params* p, const 
   VB_PROPAGATE(gather_row0(x_last, a.x0, B, d->T, E, s));
   GemmEpilogue ep = make_ep(a.h1, F);
   ep.bias = p->b1;
-  VB_PROPAGATE(gemm_f32(B, F, E, 0, 0, a.x0, E, p->w1, E, 1, ep, s));
+  if (head_lp(d, p)) {
+    VB_PROPAGATE(cast_f32_to_bf16(a.x0, a.x0_lp, static_cast<int64_t>(B) * E, s));
+    VB_PROPAGATE(gemm_tc_bf16(B, F, E, 0, 0, a.x0_lp, E, p->w1_lp, E, true, 1, ep, s));
+  } else {
+    VB_PROPAGATE(gemm_f32(B, F, E, 0, 0, a.x0, E, p->w1, E, 1, ep, s));
+  }
   VB_PROPAGATE(gelu_forward(a.h1, a.a, static_cast<int64_t>(B) * F, s));
   VB_PROPAGATE(ln_forward(a.a, p->ln_w, p->ln_b, a.n, false, a.mean, a.rstd, B, F, d->ln_eps, s));
   GemmEpilogue ep3 = make_ep(logits, d->classes);
@@ -254,12 +264,22 @@ int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_par
                            make_dropout(0.f, 0, 0), B, F, s));
   VB_PROPAGATE(gelu_backward(a.h1, dn, static_cast<int64_t>(B) * F, s));
   // first linear: dW1 += dh1^T x0 ; db1 ; dx0 = dh1 W1
-  e = make_ep(gr->w1, E);
-  e.accumulate = 1;
-  VB_PROPAGATE(gemm_f32(F, E, B, 1, 1, dn, F, a.x0, E, 1, e, s));
   VB_PROPAGATE(colsum(dn, false, F, gr->b1, B, F, s));
-  e = make_ep(dx0, E);
-  VB_PROPAGATE(gemm_f32(B, E, F, 0, 1, dn, F, p->w1, E, -1, e, s));  // few tiles, K = 4E: atomic split-K allowed
+  if (head_lp(d, p)) {
+    bf16* dn_lp = c.take<bf16>(static_cast<size_t>(B) * F * 2);
+    VB_PROPAGATE(cast_f32_to_bf16(dn, dn_lp, static_cast<int64_t>(B) * F, s));
+    e = make_ep(gr->w1, E);
+    e.accumulate = 1;
+    VB_PROPAGATE(gemm_tc_bf16(F, E, B, 1, 1, dn_lp, F, a.x0_lp, E, true, 0, e, s));
+    e = make_ep(dx0, E);
+    VB_PROPAGATE(gemm_tc_bf16(B, E, F, 0, 1, dn_lp, F, p->w1_lp, E, true, 1, e, s));
+  } else {
+    e = make_ep(gr->w1, E);
+    e.accumulate = 1;
+    VB_PROPAGATE(gemm_f32(F, E, B, 1, 1, dn, F, a.x0, E, 1, e, s));
+    e = make_ep(dx0, E);
+    VB_PROPAGATE(gemm_f32(B, E, F, 0, 1, dn, F, p->w1, E, -1, e, s));  // few tiles, K = 4E: atomic split-K allowed
+  }
   // scatter into the residual-stream gradient (token 0 only) + masked low-precision copy for the last fc2
   const Dropout dr = make_dropout(d->dropout_p, d->seed, drop_stream(n_layers - 1, 1));
   return head_scatter(dx0, g, dy_out, is_bf16(d), dr, B, d->T, E, s);

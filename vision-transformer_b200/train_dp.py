@@ -163,6 +163,8 @@ class DPTrainer:
         self.block_p = [ptrs(i, _C.BLOCK_FIELDS_P, lowp=lp) for i in range(self.L)]
         self.block_g = eng.chain_block_grads([ptrs(i, _C.BLOCK_FIELDS_G, grads=True) for i in range(self.L)])
         self.head_p = ptrs("head", _C.HEAD_FIELDS)
+        o, n, _ = self._views[("head", "w1")]
+        self.head_p["w1_lp"] = self.shadow[o:o + n] if self.shadow is not None else None
         self.head_g = ptrs("head", _C.HEAD_FIELDS, grads=True)
 
         # activations / scratch, allocated once
