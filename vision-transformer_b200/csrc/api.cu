@@ -6,6 +6,7 @@
 #include <vector>
 
 #include "../../include/vitb200.h"
+#include <cstdlib>
 #include "common.cuh"
 #include "kernels.h"
 
@@ -69,6 +70,13 @@ ProfScope::~ProfScope() {
   if (slot < static_cast<int>(g_prof_recs.size())) cudaEventRecord(g_prof_recs[slot].e1, stream);
 }
 
+}  // namespace vb
+
+namespace vb {
+bool pdl_enabled() {
+  static const bool on = !(getenv("VITB200_PDL") && atoi(getenv("VITB200_PDL")) == 0);
+  return on;
+}
 }  // namespace vb
 
 extern "C" {

@@ -87,6 +87,8 @@ __global__ void __launch_bounds__(256)
 attn_delta_vec_kernel(const uint4* __restrict__ o, const uint4* __restrict__ d_o, float* __restrict__ delta,
                       int64_t total_chunks, int T, int H) {
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  pdl_wait();
+  pdl_trigger();
   for (int64_t c = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; c < total_chunks + (threadIdx.x & 31);
        c += stride) {  // whole warps stay in the loop (shuffles); blockDim and stride are multiples of CPH
     float s = 0.f;
@@ -221,7 +223,8 @@ int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B
     const int grid_v = static_cast<int>(std::min<int64_t>((chunks + 255) / 256, static_cast<int64_t>(num_sms()) * 16));
     const uint4* o4 = static_cast<const uint4*>(o);
     const uint4* d4 = static_cast<const uint4*>(d_o);
-#define VB_DELTA(T, C) attn_delta_vec_kernel<T, C><<<grid_v, 256, 0, stream>>>(o4, d4, delta, chunks, T_, H)
+#define VB_DELTA(T, C) \
+  VB_CHECK_CUDA(launch_pdl(attn_delta_vec_kernel<T, C>, dim3(grid_v), dim3(256), 0, stream, 1, o4, d4, delta, chunks, T_, H))
     const int T_ = T;
     if (is_bf16) {
       switch (cph) {

@@ -77,6 +77,8 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+  pdl_trigger();
   // tensor-memory map per query tile t: [t*256, t*256+TP) S (fp32) -> [t*256, +TP/2) P (bf16 pairs), O at t*256+128
   // (TP <= 256: P needs <= 128 columns, O 64 columns; S is dead once P is written)
 
@@ -404,6 +406,8 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+  pdl_trigger();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ producer: TMA tiles + row statistics
@@ -645,7 +649,7 @@ int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H,
   p.scale_log2 = scale * kLog2e;
   ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * static_cast<double>(T) * hs, 1, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
-  attn_tc_fwd_kernel<<<grid, kThreads, SMEM_BYTES, stream>>>(tm, out, lse, p);
+  VB_CHECK_CUDA(launch_pdl(attn_tc_fwd_kernel, dim3(grid), dim3(kThreads), SMEM_BYTES, stream, 1, tm, out, lse, p));
   VB_CHECK_LAUNCH();
   return kOk;
 }
@@ -685,9 +689,9 @@ int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const f
   ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * static_cast<double>(T) * hs, 2, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
   chunking(96);    // two slots of 2W columns + two 64-column accumulators: 4W + 128 <= 512
-  attn_tc_bwd_kernel<1><<<grid, kBwdThreads, smem, stream>>>(tq, td, lse, delta, dqkv, p);
+  VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<1>, dim3(grid), dim3(kBwdThreads), smem, stream, 1, tq, td, lse, delta, dqkv, p));
   VB_CHECK_LAUNCH();
-  attn_tc_bwd_kernel<0><<<grid, kBwdThreads, smem, stream>>>(tq, td, lse, delta, dqkv, p);
+  VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<0>, dim3(grid), dim3(kBwdThreads), smem, stream, 1, tq, td, lse, delta, dqkv, p));
   VB_CHECK_LAUNCH();
   return kOk;
 }

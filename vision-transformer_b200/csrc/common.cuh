@@ -27,6 +27,43 @@ constexpr int kErrUnsupported = -3;
 
 #define VB_CHECK_LAUNCH() VB_CHECK_CUDA(cudaGetLastError())
 
+// ---------------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  A kernel launched through launch_pdl() may begin (block scheduling + its prologue:
+// barrier init, tensor-memory allocation, descriptor prefetch) while the previous kernel of the stream is still
+// draining; it MUST execute pdl_wait() before its first access to global memory, which blocks until the previous grid
+// has completed and flushed.  pdl_trigger() lets the next kernel of the stream start launching.  VITB200_PDL=0 turns
+// the launch attribute off (the device-side instructions are then no-ops).
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();  // api.cu
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              int cluster_x, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  unsigned n = 0;
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = static_cast<unsigned>(cluster_x);
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 #define VB_REQUIRE(cond, ...)          \
   do {                                 \
     if (!(cond)) {                     \

@@ -93,6 +93,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   if constexpr (CG == 2) ptx::cluster_sync(); else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();      // everything above overlapped the previous kernel's tail; global memory is touched only below
+  pdl_trigger();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -384,23 +386,11 @@ int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
   const int total = p.m_tiles * p.n_tiles * p.splits;     // work units (one per CTA, or per CTA pair)
   if constexpr (CG == 1) {
     const int grid = total < num_sms() ? total : num_sms();
-    kern<<<grid, kThreads, Cfg::SMEM_BYTES, stream>>>(ta, tb, p, ep);
+    VB_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), Cfg::SMEM_BYTES, stream, 1, ta, tb, p, ep));
   } else {
     const int pairs = num_sms() / 2;
     const int grid = 2 * (total < pairs ? total : pairs);
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    VB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, ep));
+    VB_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), Cfg::SMEM_BYTES, stream, 2, ta, tb, p, ep));
   }
   VB_CHECK_LAUNCH();
   return kOk;

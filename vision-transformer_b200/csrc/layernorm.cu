@@ -26,6 +26,8 @@ ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
   float* row = ln_smem + static_cast<size_t>(warp) * E;
   const bool vec = (E & 3) == 0;
+  pdl_wait();
+  pdl_trigger();
   for (int m = blockIdx.x * nw + warp; m < M; m += gridDim.x * nw) {
     const float* xr = x + static_cast<int64_t>(m) * E;
     float s = 0.f;
@@ -92,6 +94,8 @@ ln_bwd_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, const flo
   float* dyr = xh + E;                                                                   // dy row
   for (int i = threadIdx.x; i < 2 * E; i += blockDim.x) ln_smem[i] = 0.f;
   __syncthreads();
+  pdl_wait();
+  pdl_trigger();
   constexpr bool vec = VPL > 0;
   constexpr int NACC = VPL > 0 ? VPL * 4 : 1;
   float rg[NACC], rb[NACC];
@@ -245,12 +249,14 @@ ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, cons
   const uint32_t ring = smem_u32(bars + LNB_WARPS * LNB_MAX_STAGES) + warp * nst * stage_bytes;
   const uint32_t sgam = smem_u32(s_gamma);
 
-  for (int i = threadIdx.x; i < E; i += blockDim.x) s_gamma[i] = __ldg(gamma + i);
   for (int i = threadIdx.x; i < 3 * E; i += blockDim.x) s_acc[i] = 0.f;
   if (lane == 0) {
     for (int st = 0; st < nst; ++st) mbar_init(bar + st, 1);
     fence_barrier_init();
   }
+  pdl_wait();
+  pdl_trigger();
+  for (int i = threadIdx.x; i < E; i += blockDim.x) s_gamma[i] = __ldg(gamma + i);
   __syncthreads();
 
   const int E4 = E >> 2;
@@ -422,10 +428,10 @@ int ln_forward(const float* x, const float* gamma, const float* beta, void* y, b
   ProfScope prof(kProfLnFwd, static_cast<double>(M) * E * (4 + (y_bf16 ? 2 : 4)) + 8.0 * M, 1, stream);
   if (y_bf16) {
     if (smem > 48 * 1024) VB_CHECK_CUDA(cudaFuncSetAttribute(ln_fwd_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    ln_fwd_kernel<bf16><<<grid, nw * 32, smem, stream>>>(x, gamma, beta, static_cast<bf16*>(y), mean, rstd, M, E, eps);
+    VB_CHECK_CUDA(launch_pdl(ln_fwd_kernel<bf16>, dim3(grid), dim3(nw * 32), smem, stream, 1, x, gamma, beta, static_cast<bf16*>(y), mean, rstd, M, E, eps));
   } else {
     if (smem > 48 * 1024) VB_CHECK_CUDA(cudaFuncSetAttribute(ln_fwd_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    ln_fwd_kernel<float><<<grid, nw * 32, smem, stream>>>(x, gamma, beta, static_cast<float*>(y), mean, rstd, M, E, eps);
+    VB_CHECK_CUDA(launch_pdl(ln_fwd_kernel<float>, dim3(grid), dim3(nw * 32), smem, stream, 1, x, gamma, beta, static_cast<float*>(y), mean, rstd, M, E, eps));
   }
   VB_CHECK_LAUNCH();
   return kOk;
@@ -453,9 +459,9 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
   do {                                                                                                            \
     VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
                                        static_cast<int>(smem)));                                                  \
-    ln_bwd_ring_kernel<T, C><<<grid, LNB_WARPS * 32, smem, stream>>>(                                             \
-        static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta, static_cast<T*>(dyn),        \
-        dyn_colsum, drop, M, E, nst);                                                                             \
+    VB_CHECK_CUDA(launch_pdl(ln_bwd_ring_kernel<T, C>, dim3(grid), dim3(LNB_WARPS * 32), smem, stream, 1,         \
+                             static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta,         \
+                             static_cast<T*>(dyn), dyn_colsum, drop, M, E, nst));                                 \
   } while (0)
 #define VB_LN_RING_CH(T)                                                                                          \
   do {                                                                                                            \
@@ -481,9 +487,9 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
     if (smem > 48 * 1024)                                                                                        \
       VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<T, V>, cudaFuncAttributeMaxDynamicSharedMemorySize,       \
                                          static_cast<int>(smem)));                                               \
-    ln_bwd_kernel<T, V><<<grid, nw * 32, smem, stream>>>(static_cast<const T*>(dy), x, mean, rstd, gamma, g,  \
-                                                            add_to_g, dgamma, dbeta, static_cast<T*>(dyn), drop, \
-                                                            M, E);                                               \
+    VB_CHECK_CUDA(launch_pdl(ln_bwd_kernel<T, V>, dim3(grid), dim3(nw * 32), smem, stream, 1,                     \
+                             static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta,        \
+                             static_cast<T*>(dyn), drop, M, E));                                                 \
   } while (0)
   if (dy_bf16) {
     if (vpl == 4) VB_LN_BWD(bf16, 4); else if (vpl == 8) VB_LN_BWD(bf16, 8); else if (vpl == 12) VB_LN_BWD(bf16, 12); else VB_LN_BWD(bf16, 0);
