@@ -55,8 +55,9 @@ typedef struct {
  *   a_major == MAJOR_K : A stored row-major [M][lda];   MAJOR_MN: A stored [K][lda] (transposed view)
  *   b_major == MAJOR_K : B stored row-major [N][ldb];   MAJOR_MN: B stored [K][ldb]
  * Epilogue, applied in this order to v = acc:
- *   +bias[n]  ->  relu  ->  (mask_aux[m,n] > 0 ? v : 0)  ->  dropout  ->  +row_add[(m % row_period), n]
- *   -> +residual[orow, n]  ->  store / atomic-add into C[orow, n]  (-> column sums into col_sum)
+ *   +bias[n]  ->  relu  ->  (mask_aux[m,n] > 0 ? v : 0)  ->  (mask_bits bit set ? v : 0)  ->  dropout
+ *   ->  +row_add[(m % row_period), n]  ->  +residual[orow, n]  ->  store / atomic-add into C[orow, n]
+ *   (-> column sums into col_sum; -> sign bits of the stored values into bits_out)
  *   with orow = (m / row_period) * row_group_stride + m % row_period when row_period > 0, else m.
  * in_dtype BF16 runs the tcgen05/TMEM/TMA tensor-core kernel (fp32 accumulation); in_dtype F32 runs the
  * fp32 CUDA-core kernel used for the fp32 parity gate.  `splits` > 1 partitions K and accumulates with
@@ -83,6 +84,12 @@ typedef struct {
                           * also allow an atomic split-K into a zeroed C when accumulate == 0 (not bit-reproducible) */
   int accumulate;        /* 1: C += result via fp32 atomics (C must be fp32) */
   float* col_sum;        /* [N] fp32 or NULL: col_sum[n] += sum_m (value stored at C[m,n]) — fused bias gradient */
+  /* Bit masks (BF16 inputs only, N % 32 == 0): word (n / 32) * bits_rows + m covers columns [32*(n/32), +32) of row m.
+   * bits_out: bit = stored value > 0 (the ReLU mask at 1/16 of the activation's bytes, transformer.py:57);
+   * mask_bits: keep v where the bit is set (ReLU backward). */
+  uint32_t* bits_out;
+  const uint32_t* mask_bits;
+  int bits_rows;         /* >= M */
 } vitb200_gemm_args;
 
 int vitb200_gemm(const vitb200_gemm_args* args, void* stream);

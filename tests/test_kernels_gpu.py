@@ -71,6 +71,35 @@ def test_gemm_epilogue_bias_relu_residual_rowmap(lib, dt):
     assert rel_err(cs - 1, ref3.sum(0)) < 1e-5
 
 
+@pytest.mark.parametrize("M,N,K", [(300, 96, 64), (1000, 3072, 128), (128, 32, 16)])
+def test_gemm_relu_sign_bits_roundtrip(lib, M, N, K):
+    """fc1 writes the ReLU mask as 1 bit per element (bits_out); the ReLU backward GEMM consumes it (mask_bits) and
+    must give exactly what re-reading the bf16 activation (mask_aux) gives.  Word (n/32)*rows + m, bit n%32."""
+    C = _C()
+    torch.manual_seed(8)
+    A, B = torch.randn(M, K, device=DEV).bfloat16(), torch.randn(N, K, device=DEV).bfloat16()
+    bias = torch.randn(N, device=DEV)
+    h = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    bits = torch.zeros(N // 32, M, device=DEV, dtype=torch.int32)
+    C.gemm(A, B, h, M=M, N=N, K=K, bias=bias, relu=True, bits_out=bits, bits_rows=M)
+    ref = torch.relu(A.float() @ B.float().t() + bias)
+    assert rel_err(h, ref) < 5e-3
+    unpacked = ((bits.unsqueeze(-1) >> torch.arange(32, device=DEV, dtype=torch.int32)) & 1)   # [N/32, M, 32]
+    unpacked = unpacked.permute(1, 0, 2).reshape(M, N).bool()
+    assert torch.equal(unpacked, h.float() > 0)
+    # backward-style product with an MN-major weight: mask by bits == mask by the activation
+    dy = torch.randn(M, K, device=DEV).bfloat16()
+    W = torch.randn(K, N, device=DEV).bfloat16()
+    a, b = (torch.empty(M, N, device=DEV, dtype=torch.bfloat16) for _ in range(2))
+    cs_a, cs_b = torch.zeros(N, device=DEV), torch.zeros(N, device=DEV)
+    C.gemm(dy, W, a, M=M, N=N, K=K, b_major=C.MAJOR_MN, mask_aux=h, col_sum=cs_a)
+    C.gemm(dy, W, b, M=M, N=N, K=K, b_major=C.MAJOR_MN, mask_bits=bits, bits_rows=M, col_sum=cs_b)
+    assert torch.equal(a, b)
+    assert rel_err(cs_b, cs_a) < 1e-5
+    with pytest.raises(RuntimeError, match="bit masks"):
+        C.gemm(A, B[:40], h[:, :40], M=M, N=40, K=K, relu=True, bits_out=bits, bits_rows=M, ldc=N)
+
+
 def test_gemm_dropout_epilogue_matches_exported_mask(lib):
     C = _C()
     torch.manual_seed(3)

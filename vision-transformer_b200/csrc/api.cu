@@ -141,6 +141,9 @@ int vitb200_gemm(const vitb200_gemm_args* a, void* stream) {
   ep.row_group_stride = a->row_group_stride;
   ep.accumulate = a->accumulate;
   ep.col_sum = a->col_sum;
+  ep.bits_out = a->bits_out;
+  ep.mask_bits = a->mask_bits;
+  ep.bits_rows = a->bits_rows;
   ep.drop = make_dropout(a->dropout.p, a->dropout.seed, a->dropout.stream);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (a->in_dtype == VITB200_BF16) {

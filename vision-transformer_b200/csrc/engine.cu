@@ -53,6 +53,7 @@ GemmEpilogue make_ep(void* C, int64_t ldc) {
   GemmEpilogue ep;
   ep.bias = nullptr; ep.mask_aux = nullptr; ep.row_add = nullptr; ep.residual = nullptr;
   ep.C = C; ep.ldc = ldc; ep.relu = 0; ep.row_period = 0; ep.row_group_stride = 0; ep.accumulate = 0; ep.col_sum = nullptr;
+  ep.bits_out = nullptr; ep.mask_bits = nullptr; ep.bits_rows = 0;
   ep.drop = make_dropout(0.f, 0, 0);
   return ep;
 }
@@ -112,7 +113,9 @@ struct BlockActs {
   void* ln2;     // [M,E]   dtype
   float *mean2, *rstd2;
   void* h;       // [M,4E]  dtype (post-ReLU)
+  uint32_t* hbits;  // [4E/32][M] sign bits of h (bf16 mode, 4E % 32 == 0; else null): the ReLU mask of the backward
 };
+inline bool use_hbits(const vitb200_dims* d) { return is_bf16(d) && (4 * d->E) % 32 == 0; }
 BlockActs carve_block(const vitb200_dims* d, void* acts, size_t* total = nullptr) {
   Carver c(acts);
   BlockActs a;
@@ -128,6 +131,7 @@ BlockActs carve_block(const vitb200_dims* d, void* acts, size_t* total = nullptr
   a.mean2 = c.take<float>(M * 4);
   a.rstd2 = c.take<float>(M * 4);
   a.h = c.take(M * 4 * E * es);
+  a.hbits = use_hbits(d) ? c.take<uint32_t>(M * (4 * E / 32) * 4) : nullptr;
   if (total) *total = c.off;
   return a;
 }
@@ -331,6 +335,7 @@ int vitb200_block_fwd(const vitb200_dims* d, int layer, const vitb200_block_para
   l = Lin();
   l.M = M; l.N = 4 * E; l.K = E; l.A = a.ln2; l.lda = E; l.B = p->w_fc1; l.ldb = E;
   l.ep = make_ep(a.h, 4 * E); l.ep.bias = p->b_fc1; l.ep.relu = 1; l.out_f32 = !bf;
+  if (a.hbits) { l.ep.bits_out = a.hbits; l.ep.bits_rows = M; }
   VB_PROPAGATE(run_lin(bf, l, s));
   l = Lin();
   l.M = M; l.N = E; l.K = 4 * E; l.A = a.h; l.lda = 4 * E; l.B = p->w_fc2; l.ldb = 4 * E;
@@ -360,7 +365,9 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
   if (gr->b_fc2) VB_PROPAGATE(colsum(dy_in, bf, E, gr->b_fc2, M, E, s));
   // dh[M,4E] = (dy W2) * (h > 0)
   l = Lin(); l.M = M; l.N = F; l.K = E; l.b_major = 1; l.A = dy_in; l.lda = E; l.B = p->w_fc2; l.ldb = F;
-  l.ep = make_ep(sc.s1, F); l.ep.mask_aux = a.h; l.ep.col_sum = gr->b_fc1; l.out_f32 = !bf;  // db1 += colsum(dh), fused
+  l.ep = make_ep(sc.s1, F); l.ep.col_sum = gr->b_fc1; l.out_f32 = !bf;  // db1 += colsum(dh), fused
+  if (a.hbits) { l.ep.mask_bits = a.hbits; l.ep.bits_rows = M; }   // 1 bit per element instead of re-reading h
+  else l.ep.mask_aux = a.h;
   VB_PROPAGATE(run_lin(bf, l, s));
   // dW1[4E,E] += dh^T ln2
   l = Lin(); l.M = F; l.N = E; l.K = M; l.a_major = 1; l.b_major = 1; l.A = sc.s1; l.lda = F; l.B = a.ln2; l.ldb = E;

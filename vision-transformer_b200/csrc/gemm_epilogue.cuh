@@ -1,5 +1,5 @@
 // Epilogue shared by the tcgen05 (bf16) and CUDA-core (fp32) contraction kernels.
-// Order: +bias -> relu -> aux mask -> dropout -> +row_add -> +residual -> store / atomic add.
+// Order: +bias -> relu (-> sign bits out) -> aux mask / bit mask -> dropout -> +row_add -> +residual -> store / atomic add.
 #pragma once
 #include "common.cuh"
 
@@ -17,6 +17,10 @@ struct GemmEpilogue {
   int row_group_stride;
   int accumulate;          // atomic add into fp32 C
   float* col_sum;          // [N] or null: col_sum[n] += sum over rows of the stored value (bias gradients)
+  // 1 bit per element, word (n / 32) * bits_rows + m holds columns [32*(n/32), +32) of row m (bit = column % 32):
+  uint32_t* bits_out;        // or null: bit = (stored value > 0)   — the ReLU mask, 1/16 the bytes of the bf16 tensor
+  const uint32_t* mask_bits; // or null: keep v where the bit is set  (tensor-core kernel only, N % 32 == 0)
+  int bits_rows;
   Dropout drop;
 };
 
@@ -25,12 +29,13 @@ struct GemmEpilogue {
 // combination reachable through the C ABI still works.
 enum : uint32_t {
   kEpiBias = 1u, kEpiRelu = 2u, kEpiMask = 4u, kEpiDrop = 8u, kEpiRowMap = 16u, kEpiResidual = 32u, kEpiAccum = 64u,
-  kEpiColSum = 128u, kEpiGeneric = 0x80000000u
+  kEpiColSum = 128u, kEpiBitsOut = 256u, kEpiBitMask = 512u, kEpiGeneric = 0x80000000u
 };
 inline uint32_t epi_flags(const GemmEpilogue& ep) {
   return (ep.bias ? kEpiBias : 0u) | (ep.relu ? kEpiRelu : 0u) | (ep.mask_aux ? kEpiMask : 0u) |
          (ep.drop.p > 0.f ? kEpiDrop : 0u) | ((ep.row_add || ep.row_period > 0) ? kEpiRowMap : 0u) |
-         (ep.residual ? kEpiResidual : 0u) | (ep.accumulate ? kEpiAccum : 0u) | (ep.col_sum ? kEpiColSum : 0u);
+         (ep.residual ? kEpiResidual : 0u) | (ep.accumulate ? kEpiAccum : 0u) | (ep.col_sum ? kEpiColSum : 0u) |
+         (ep.bits_out ? kEpiBitsOut : 0u) | (ep.mask_bits ? kEpiBitMask : 0u);
 }
 #define VB_EPI(flag, cond) ((EPI == ::vb::kEpiGeneric) ? (cond) : ((EPI & (flag)) != 0u))
 
@@ -49,9 +54,12 @@ __device__ __forceinline__ void red_add_f32x4(float* addr, float a, float b, flo
 struct EpiPre {
   float4 r0, r1;   // residual
   uint4 a0, a1;    // mask_aux: 8 x bf16 in a0, or 8 x fp32 in a0|a1
+  uint32_t bits;   // mask_bits word of this row / 32-column group
 };
 template <typename OutT, uint32_t EPI>
-__device__ __forceinline__ void epilogue_fetch8(const GemmEpilogue& ep, int64_t off, EpiPre& pre) {
+__device__ __forceinline__ void epilogue_fetch8(const GemmEpilogue& ep, int64_t off, int m, int n, EpiPre& pre) {
+  if (VB_EPI(kEpiBitMask, ep.mask_bits != nullptr))
+    pre.bits = __ldg(ep.mask_bits + static_cast<int64_t>(n >> 5) * ep.bits_rows + m);
   if (VB_EPI(kEpiResidual, ep.residual != nullptr)) {
     pre.r0 = __ldg(reinterpret_cast<const float4*>(ep.residual + off));
     pre.r1 = __ldg(reinterpret_cast<const float4*>(ep.residual + off + 4));
@@ -89,6 +97,11 @@ __device__ __forceinline__ void epilogue_finish8(const GemmEpilogue& ep, int m, 
 #pragma unroll
       for (int i = 0; i < 8; ++i) v[i] = a[i] > 0.f ? v[i] : 0.f;
     }
+  }
+  if (VB_EPI(kEpiBitMask, ep.mask_bits != nullptr)) {
+    const uint32_t b = pre.bits >> (n & 31);   // n % 8 == 0: my 8 columns are one byte of the word
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = (b >> i) & 1u ? v[i] : 0.f;
   }
   if (VB_EPI(kEpiDrop, ep.drop.p > 0.f)) {
     const uint64_t lin = static_cast<uint64_t>(m) * static_cast<uint64_t>(N) + static_cast<uint64_t>(n);

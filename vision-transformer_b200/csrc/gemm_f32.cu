@@ -142,6 +142,7 @@ gemm_f32_skinny_kernel(const float* __restrict__ A, int64_t lda, const float* __
 int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int64_t lda, const float* B,
              int64_t ldb, int splits, const GemmEpilogue& ep_in, cudaStream_t stream) {
   VB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_f32: empty problem M=%d N=%d K=%d", M, N, K);
+  VB_REQUIRE(ep_in.bits_out == nullptr && ep_in.mask_bits == nullptr, "gemm_f32: bit masks are a tensor-core-path option");
   GemmEpilogue ep = ep_in;
   if (N <= 16 && a_major == 0 && b_major == 0 && !ep.accumulate && ep.col_sum == nullptr && M >= 32) {
     ProfScope prof(kProfGemmF32, 2.0 * M * N * K, 1, stream);

@@ -228,7 +228,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         for (int pass = 0; pass < 4; ++pass) {
           const int m = m0 + pass * 8 + rsub;
           const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
-          if (m < p.M) epilogue_fetch8<OutT, EPI>(ep, orow * ep.ldc + nn, dst[pass]);
+          if (m < p.M) epilogue_fetch8<OutT, EPI>(ep, orow * ep.ldc + nn, m, nn, dst[pass]);
         }
       };
       fetch_chunk(0, pre_nx);
@@ -277,6 +277,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           const int m = m0 + R;
           const float4 lo = ptx::lds128(stg_s + static_cast<uint32_t>(R * 128 + (((2 * cg) ^ (R & 7)) << 4)));
           const float4 hi = ptx::lds128(stg_s + static_cast<uint32_t>(R * 128 + (((2 * cg + 1) ^ (R & 7)) << 4)));
+          uint32_t sign8 = 0;
           if (m < p.M && ncol_ok) {
             float v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
             epilogue_finish8<OutT, EPI>(ep, m, n, p.N, off[pass], v, pre[pass], bias8);
@@ -284,6 +285,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
               for (int i = 0; i < 8; ++i) cs[i] += v[i];
             }
+            if (VB_EPI(kEpiBitsOut, ep.bits_out != nullptr)) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) sign8 |= (v[i] > 0.f ? 1u : 0u) << i;
+            }
+          }
+          if (VB_EPI(kEpiBitsOut, ep.bits_out != nullptr)) {   // warp-uniform: the 4 lanes of a row merge their bytes
+            uint32_t w = sign8 << (8 * cg);
+            w |= __shfl_xor_sync(0xffffffffu, w, 1);
+            w |= __shfl_xor_sync(0xffffffffu, w, 2);
+            if (cg == 0 && m < p.M) ep.bits_out[static_cast<int64_t>(n0 >> 5) * ep.bits_rows + m] = w;
           }
         }
         if (VB_EPI(kEpiColSum, ep.col_sum != nullptr)) {   // warp-uniform
@@ -416,6 +427,8 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   VB_REQUIRE(aligned16(A) && aligned16(B) && aligned16(ep.C), "gemm_tc: operands must be 16-byte aligned");
   VB_REQUIRE(!ep.accumulate || out_f32, "gemm_tc: atomic accumulation needs an fp32 output");
   VB_REQUIRE(ep.residual == nullptr || out_f32, "gemm_tc: residual add needs an fp32 output");
+  VB_REQUIRE((ep.bits_out == nullptr && ep.mask_bits == nullptr) || (N % 32 == 0 && ep.bits_rows >= M),
+             "gemm_tc: bit masks need N %% 32 == 0 and bits_rows >= M (N=%d, bits_rows=%d)", N, ep.bits_rows);
   constexpr int BN = 256;
 
   // CTA pairs (256-row tiles) whenever there is more than one 128-row tile of output; VITB200_GEMM_CG=1|2 forces.
@@ -460,11 +473,13 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
     }
     VB_TC(0, 0, bf16, 0u);
     VB_TC(0, 0, bf16, kEpiBias | kEpiRelu);
+    VB_TC(0, 0, bf16, kEpiBias | kEpiRelu | kEpiBitsOut);
     return launch_tc<0, 0, BN, bf16, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
   } else if (a_major == 0 && b_major == 1) {
     if (out_f32) return launch_tc<0, 1, BN, float, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
     VB_TC(0, 1, bf16, 0u);
     VB_TC(0, 1, bf16, kEpiMask | kEpiColSum);
+    VB_TC(0, 1, bf16, kEpiBitMask | kEpiColSum);
     return launch_tc<0, 1, BN, bf16, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
   } else if (a_major == 1 && b_major == 1) {
     if (out_f32) {
