@@ -152,6 +152,16 @@ def run_reference(args):
 
 
 # ---------------------------------------------------------------------------------------------------- our arm
+def _recorded_traffic(args):
+    """DRAM bytes per gemm_tc_kernel launch from the committed ncu --set full capture (it cannot be measured inside
+    a timed run); only valid for the workload it was captured on."""
+    path = os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")
+    if args.model != "vit_b16" or args.batch != 256 or args.dtype != "bf16" or not os.path.exists(path):
+        return None
+    with open(path) as f:
+        return float(json.load(f)["avg_bytes_per_launch"])
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -252,7 +262,7 @@ def run_b200(args):
     roofline = {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05/TMEM/TMA bf16 contraction, all call sites)",
                 "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": (ach / peak_tf) if peak_tf else None,
                 "peak_source": pk["source"] + ", sustained cuBLAS bf16 (kernel timed inside a long step)",
-                "traffic": None, "launches_per_step": g["launches"] // 2,
+                "traffic": _recorded_traffic(args), "launches_per_step": g["launches"] // 2,
                 "flops_per_launch_avg": g["work"] / max(g["launches"], 1),
                 "share_of_step": g["ms"] / tot_ms}
     step_tflops = tr.flops_per_image() * args.batch / (ms_step * 1e-3) / 1e12  # per GPU
