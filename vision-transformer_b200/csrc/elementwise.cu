@@ -59,9 +59,44 @@ __global__ void cls_rows_kernel(const float* __restrict__ cls, const float* __re
 
 // Embedding backward reductions over the batch: g fp32 [B,T,E] ->
 //   dpos[t,e] += sum_b g[b,t,e];  dcls[b,e] += g[b,T-1,e];  dY[b*N+t, e] = cast(g[b,t,e]) for t < N.
+// Thread = 4 consecutive e of one token t (E % 4 == 0), blockIdx.y = a slice of the batch; dpos partial sums are
+// combined with one atomic per thread, so the grid has B/bchunk times more loads in flight than a per-(t,e) loop.
 template <typename OutT>
 __global__ void embed_bwd_kernel(const float* __restrict__ g, float* __restrict__ dpos, float* __restrict__ dcls,
-                                 OutT* __restrict__ dY, int B, int T, int E) {
+                                 OutT* __restrict__ dY, int B, int T, int E, int bchunk) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;      // float4 index inside one image
+  const int E4 = E >> 2;
+  if (idx >= T * E4) return;
+  const int t = idx / E4, e = (idx - t * E4) * 4;
+  const int N = T - 1;
+  const int b0 = blockIdx.y * bchunk, b1 = min(B, b0 + bchunk);
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+  for (int b = b0; b < b1; ++b) {
+    const float4 v = __ldcs(reinterpret_cast<const float4*>(g + (static_cast<int64_t>(b) * T + t) * E + e));
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    if (t < N) {
+      OutT* o = dY + (static_cast<int64_t>(b) * N + t) * E + e;
+      if constexpr (sizeof(OutT) == 2) {
+        uint2 pk;
+        pk.x = pack_bf16x2(v.x, v.y);
+        pk.y = pack_bf16x2(v.z, v.w);
+        *reinterpret_cast<uint2*>(o) = pk;
+      } else {
+        *reinterpret_cast<float4*>(o) = v;
+      }
+    } else {
+      float* c = dcls + static_cast<int64_t>(b) * E + e;
+      c[0] += v.x; c[1] += v.y; c[2] += v.z; c[3] += v.w;
+    }
+  }
+  float* dp = dpos + static_cast<int64_t>(t) * E + e;
+  atomicAdd(dp, s.x); atomicAdd(dp + 1, s.y); atomicAdd(dp + 2, s.z); atomicAdd(dp + 3, s.w);
+}
+// scalar fallback (E % 4 != 0)
+template <typename OutT>
+__global__ void embed_bwd_scalar_kernel(const float* __restrict__ g, float* __restrict__ dpos, float* __restrict__ dcls,
+                                        OutT* __restrict__ dY, int B, int T, int E) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= T * E) return;
   const int t = idx / E, e = idx - t * E;
@@ -307,9 +342,16 @@ int cls_rows(const float* cls, const float* pos, float* out, int B, int T, int E
 int embed_bwd_reduce(const float* g, float* dpos, float* dcls, void* dY, bool dy_bf16, int B, int T, int E,
                      cudaStream_t s) {
   ProfScope prof(kProfEltwise, 0.0, 1, s);
-  const int grid = ceil_div(T * E, 128);
-  if (dy_bf16) embed_bwd_kernel<bf16><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<bf16*>(dY), B, T, E);
-  else embed_bwd_kernel<float><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<float*>(dY), B, T, E);
+  if (E % 4 == 0 && aligned16(g) && aligned16(dY)) {
+    const int bchunk = B >= 64 ? 16 : B;
+    const dim3 grid(ceil_div(T * (E / 4), 128), ceil_div(B, bchunk));
+    if (dy_bf16) embed_bwd_kernel<bf16><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<bf16*>(dY), B, T, E, bchunk);
+    else embed_bwd_kernel<float><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<float*>(dY), B, T, E, bchunk);
+  } else {
+    const int grid = ceil_div(T * E, 128);
+    if (dy_bf16) embed_bwd_scalar_kernel<bf16><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<bf16*>(dY), B, T, E);
+    else embed_bwd_scalar_kernel<float><<<grid, 128, 0, s>>>(g, dpos, dcls, static_cast<float*>(dY), B, T, E);
+  }
   VB_CHECK_LAUNCH();
   return kOk;
 }
