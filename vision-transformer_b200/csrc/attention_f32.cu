@@ -5,6 +5,7 @@
 // scale = +sqrt(head_size) (MULTIPLIED), softmax over keys, out = wei v; heads are column slices h*hs of the
 // packed [M, 3E] qkv buffer (q | k | v), output written at column h*hs of [M, E] (the torch.cat at :45).
 #include "common.cuh"
+#include "kernels.h"
 
 namespace vb {
 
@@ -252,6 +253,10 @@ int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B
 
 int attn_f32_forward(const float* qkv, float* out, float* lse, int B, int T, int H, int hs, float scale,
                      cudaStream_t stream) {
+  if (attn_f32_tiled_supported(T, hs, qkv, out)) {
+    ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * T * hs, 1, stream);
+    return attn_f32_tiled_forward(qkv, out, lse, nullptr, B, T, H, hs, scale, stream);
+  }
   const size_t smem = static_cast<size_t>(AF_WARPS) * (hs + T) * sizeof(float);
   VB_PROPAGATE(set_smem(attn_f32_fwd_kernel<false>, smem));
   dim3 grid(B * H, ceil_div(T, AF_WARPS));
@@ -262,6 +267,10 @@ int attn_f32_forward(const float* qkv, float* out, float* lse, int B, int T, int
 }
 
 int attn_f32_probs(const float* qkv, float* probs, int B, int T, int H, int hs, float scale, cudaStream_t stream) {
+  if (attn_f32_tiled_supported(T, hs, qkv, probs)) {
+    ProfScope prof(kProfAttnFwd, 2.0 * B * H * T * T * hs, 1, stream);
+    return attn_f32_tiled_forward(qkv, nullptr, nullptr, probs, B, T, H, hs, scale, stream);
+  }
   const size_t smem = static_cast<size_t>(AF_WARPS) * (hs + T) * sizeof(float);
   VB_PROPAGATE(set_smem(attn_f32_fwd_kernel<true>, smem));
   dim3 grid(B * H, ceil_div(T, AF_WARPS));
@@ -274,6 +283,10 @@ int attn_f32_probs(const float* qkv, float* probs, int B, int T, int H, int hs, 
 int attn_f32_backward(const float* qkv, const float* out, const float* d_o, const float* lse, float* delta,
                       float* dqkv, int B, int T, int H, int hs, float scale, cudaStream_t stream) {
   VB_PROPAGATE(attn_delta(out, d_o, false, delta, B, T, H, hs, stream));
+  if (attn_f32_tiled_supported(T, hs, qkv, d_o) && aligned16(dqkv)) {
+    ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * T * hs, 2, stream);
+    return attn_f32_tiled_backward(qkv, d_o, lse, delta, dqkv, B, T, H, hs, scale, stream);
+  }
   dim3 grid(B * H, ceil_div(T, AF_WARPS));
   ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * T * hs, 2, stream);
   const size_t smem_q = static_cast<size_t>(AF_WARPS) * (2 * hs + T) * sizeof(float);

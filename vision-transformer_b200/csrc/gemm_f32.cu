@@ -1,5 +1,5 @@
 // fp32 CUDA-core contraction used when the model runs in fp32 (the 1e-4 parity gate; tensor cores cannot
-// meet it).  128x128x8 tiles, 8x8 register micro-tiles, arbitrary M/N/K/strides, same epilogue semantics as
+// meet it).  128x128x16 tiles double-buffered in shared memory, 8x8 register micro-tiles, arbitrary M/N/K/strides, same epilogue semantics as
 // the tcgen05 kernel.  Replaces the fp32 cuBLAS calls behind nn.Linear / Conv2d of the reference
 // (transformer.py:22-28,46,56-58; vit.py:21-28) and their autograd backward.
 #include "common.cuh"
@@ -9,7 +9,7 @@ namespace vb {
 
 namespace {
 
-constexpr int FBM = 128, FBN = 128, FBK = 8, FTHREADS = 256;
+constexpr int FBM = 128, FBN = 128, FBK = 16, FTHREADS = 256;
 
 // first: this CTA holds the first K-split (the additive epilogue terms are applied exactly once per element)
 __device__ __forceinline__ float epilogue_store1_f32(const GemmEpilogue& ep, int m, int n, int N, float v, bool first) {
@@ -32,13 +32,62 @@ __device__ __forceinline__ float epilogue_store1_f32(const GemmEpilogue& ep, int
   return v;
 }
 
-// A(m,k) = A[m*sam + k*sak], B(n,k) = B[n*sbn + k*sbk]
+// Operand tile loader: 128 (rows) x 16 (k) elements of a K-major ([rows][ld]) or MN-major ([k][ld]) matrix into 8
+// registers per thread.  Fast path: 16-byte loads when the whole tile is in bounds and 16-byte aligned; otherwise
+// guarded scalar loads with zero fill.  store_tile() writes the registers to the [k][row] shared-memory tile.
+template <bool KMAJOR>
+__device__ __forceinline__ void load_tile_regs(const float* __restrict__ P, int64_t ld, int rows, int r0, int k0,
+                                               int k_end, bool vec_ok, float (&v)[8]) {
+  const int tid = threadIdx.x;
+  if (vec_ok && r0 + FBM <= rows && k0 + FBK <= k_end) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int idx = tid + i * FTHREADS;   // float4 index inside the tile
+      float4 t;
+      if (KMAJOR) t = *reinterpret_cast<const float4*>(P + static_cast<int64_t>(r0 + (idx >> 2)) * ld + k0 + ((idx & 3) << 2));
+      else        t = *reinterpret_cast<const float4*>(P + static_cast<int64_t>(k0 + (idx >> 5)) * ld + r0 + ((idx & 31) << 2));
+      v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int idx = tid + i * FTHREADS;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        int r, kk;
+        if (KMAJOR) { r = idx >> 2; kk = ((idx & 3) << 2) + c; } else { kk = idx >> 5; r = ((idx & 31) << 2) + c; }
+        const int gr = r0 + r, gk = k0 + kk;
+        float t = 0.f;
+        if (gr < rows && gk < k_end) t = KMAJOR ? P[static_cast<int64_t>(gr) * ld + gk] : P[static_cast<int64_t>(gk) * ld + gr];
+        v[4 * i + c] = t;
+      }
+    }
+  }
+}
+template <bool KMAJOR>
+__device__ __forceinline__ void store_tile(float (*S)[FBM + 4], const float (&v)[8]) {
+  const int tid = threadIdx.x;
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int idx = tid + i * FTHREADS;
+    if (KMAJOR) {
+      const int r = idx >> 2, kq = (idx & 3) << 2;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) S[kq + c][r] = v[4 * i + c];
+    } else {
+      *reinterpret_cast<float4*>(&S[idx >> 5][(idx & 31) << 2]) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+  }
+}
+
+// A(m,k) = A[m*lda + k] (K-major) or A[k*lda + m]; B(n,k) likewise.  128 x 128 x 16 tiles, double-buffered in shared
+// memory: the global loads of tile k+1 are issued into registers before tile k is multiplied (one barrier per tile).
 template <bool A_KMAJOR, bool B_KMAJOR>
 __global__ void __launch_bounds__(FTHREADS)
 gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ B, int64_t ldb, int M, int N,
-                int K, int k_per_split, const GemmEpilogue ep) {
-  __shared__ float As[FBK][FBM + 4];
-  __shared__ float Bs[FBK][FBN + 4];
+                int K, int k_per_split, const GemmEpilogue ep, int vec_a, int vec_b) {
+  __shared__ __align__(16) float As[2][FBK][FBM + 4];
+  __shared__ __align__(16) float Bs[2][FBK][FBN + 4];
   const int tid = threadIdx.x;
   const int m0 = blockIdx.y * FBM, n0 = blockIdx.x * FBN;
   const int k_begin = blockIdx.z * k_per_split;
@@ -51,36 +100,26 @@ gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
 
+  float ra[8], rb[8];
+  load_tile_regs<A_KMAJOR>(A, lda, M, m0, k_begin, k_end, vec_a != 0, ra);
+  load_tile_regs<B_KMAJOR>(B, ldb, N, n0, k_begin, k_end, vec_b != 0, rb);
+  store_tile<A_KMAJOR>(As[0], ra);
+  store_tile<B_KMAJOR>(Bs[0], rb);
+  __syncthreads();
+  int cur = 0;
   for (int k0 = k_begin; k0 < k_end; k0 += FBK) {
-    // ---- stage tiles (4 elements per thread per operand), coalesced along the contiguous index
-#pragma unroll
-    for (int i = 0; i < (FBM * FBK) / FTHREADS; ++i) {
-      const int e = tid + i * FTHREADS;
-      int r, kk;
-      if (A_KMAJOR) { kk = e % FBK; r = e / FBK; } else { r = e % FBM; kk = e / FBM; }
-      const int gm = m0 + r, gk = k0 + kk;
-      float v = 0.f;
-      if (gm < M && gk < k_end) v = A_KMAJOR ? A[static_cast<int64_t>(gm) * lda + gk] : A[static_cast<int64_t>(gk) * lda + gm];
-      As[kk][r] = v;
+    const bool more = k0 + FBK < k_end;
+    if (more) {
+      load_tile_regs<A_KMAJOR>(A, lda, M, m0, k0 + FBK, k_end, vec_a != 0, ra);
+      load_tile_regs<B_KMAJOR>(B, ldb, N, n0, k0 + FBK, k_end, vec_b != 0, rb);
     }
-#pragma unroll
-    for (int i = 0; i < (FBN * FBK) / FTHREADS; ++i) {
-      const int e = tid + i * FTHREADS;
-      int r, kk;
-      if (B_KMAJOR) { kk = e % FBK; r = e / FBK; } else { r = e % FBN; kk = e / FBN; }
-      const int gn = n0 + r, gk = k0 + kk;
-      float v = 0.f;
-      if (gn < N && gk < k_end) v = B_KMAJOR ? B[static_cast<int64_t>(gn) * ldb + gk] : B[static_cast<int64_t>(gk) * ldb + gn];
-      Bs[kk][r] = v;
-    }
-    __syncthreads();
 #pragma unroll
     for (int kk = 0; kk < FBK; ++kk) {
       float a[8], b[8];
-      const float4 a0 = *reinterpret_cast<const float4*>(&As[kk][ty * 8]);
-      const float4 a1 = *reinterpret_cast<const float4*>(&As[kk][ty * 8 + 4]);
-      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 8]);
-      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[kk][tx * 8 + 4]);
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 8]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[cur][kk][ty * 8 + 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[cur][kk][tx * 8]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[cur][kk][tx * 8 + 4]);
       a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
       b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
 #pragma unroll
@@ -88,7 +127,12 @@ gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
     }
+    if (more) {
+      store_tile<A_KMAJOR>(As[cur ^ 1], ra);   // the other buffer was last read one iteration ago (barrier below)
+      store_tile<B_KMAJOR>(Bs[cur ^ 1], rb);
+    }
     __syncthreads();
+    cur ^= 1;
   }
 
   float cs[8];
@@ -171,16 +215,19 @@ int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int6
   int k_per_split = ceil_div(ceil_div(K, s), FBK) * FBK;
   s = ceil_div(K, k_per_split);
   dim3 grid(ceil_div(N, FBN), ceil_div(M, FBM), s);
+  // 16-byte operand loads need 16-byte aligned rows; K-major tiles additionally start at multiples of 4 in k
+  const int vec_a = aligned16(A) && lda % 4 == 0 && (a_major == 1 || k_per_split % 4 == 0);
+  const int vec_b = aligned16(B) && ldb % 4 == 0 && (b_major == 1 || k_per_split % 4 == 0);
   ProfScope prof(kProfGemmF32, 2.0 * M * N * K, 1, stream);
   VB_REQUIRE(grid.y <= 65535 && grid.z <= 65535, "gemm_f32: grid too large");
   if (a_major == 0 && b_major == 0)
-    gemm_f32_kernel<true, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);
+    gemm_f32_kernel<true, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b);
   else if (a_major == 0 && b_major == 1)
-    gemm_f32_kernel<true, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);
+    gemm_f32_kernel<true, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b);
   else if (a_major == 1 && b_major == 1)
-    gemm_f32_kernel<false, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);
+    gemm_f32_kernel<false, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b);
   else if (a_major == 1 && b_major == 0)
-    gemm_f32_kernel<false, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep);
+    gemm_f32_kernel<false, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b);
   else {
     set_error("gemm_f32: bad operand majors a=%d b=%d", a_major, b_major);
     return kErrInvalid;

@@ -30,6 +30,12 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
                 float* dyn_colsum, const Dropout& drop, int M, int E, cudaStream_t stream);
 
 // attention
+// tiled flash-style fp32 attention (attention_f32_tiled.cu): head sizes that are multiples of 4 up to 128
+bool attn_f32_tiled_supported(int T, int hs, const void* a, const void* b);
+int attn_f32_tiled_forward(const float* qkv, float* out, float* lse, float* probs, int B, int T, int H, int hs,
+                           float scale, cudaStream_t stream);
+int attn_f32_tiled_backward(const float* qkv, const float* d_o, const float* lse, const float* delta, float* dqkv, int B,
+                            int T, int H, int hs, float scale, cudaStream_t stream);
 int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B, int T, int H, int hs,
                cudaStream_t stream);
 int attn_f32_forward(const float* qkv, float* out, float* lse, int B, int T, int H, int hs, float scale,
