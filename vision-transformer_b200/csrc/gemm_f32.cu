@@ -85,7 +85,7 @@ __device__ __forceinline__ void store_tile(float (*S)[FBM + 4], const float (&v)
 template <bool A_KMAJOR, bool B_KMAJOR>
 __global__ void __launch_bounds__(FTHREADS)
 gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restrict__ B, int64_t ldb, int M, int N,
-                int K, int k_per_split, const GemmEpilogue ep, int vec_a, int vec_b) {
+                int K, int k_per_split, const GemmEpilogue ep, int vec_a, int vec_b, int vec_c) {
   __shared__ __align__(16) float As[2][FBK][FBM + 4];
   __shared__ __align__(16) float Bs[2][FBK][FBN + 4];
   const int tid = threadIdx.x;
@@ -138,14 +138,42 @@ gemm_f32_kernel(const float* __restrict__ A, int64_t lda, const float* __restric
   float cs[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) cs[j] = 0.f;
+  const bool first = blockIdx.z == 0;
+  if (vec_c) {
+    // 8 consecutive columns per row through the shared vector epilogue (16-byte loads / stores, one Philox call per
+    // 8 elements); additive terms only on the first K-split.
+    const int n = n0 + tx * 8;
+    if (n < N) {
+      GemmEpilogue e = ep;
+      if (!first) { e.residual = nullptr; e.row_add = nullptr; }
+      float bias8[8];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int m = m0 + ty * 8 + i;
-    if (m >= M) continue;
+      for (int j = 0; j < 8; ++j) bias8[j] = (e.bias != nullptr && first) ? __ldg(e.bias + n + j) : 0.f;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int n = n0 + tx * 8 + j;
-      if (n < N) cs[j] += epilogue_store1_f32(ep, m, n, N, acc[i][j], blockIdx.z == 0);
+      for (int i = 0; i < 8; ++i) {
+        const int m = m0 + ty * 8 + i;
+        if (m >= M) continue;
+        const int64_t off = epi_out_row(e, m) * e.ldc + n;
+        EpiPre pre;
+        epilogue_fetch8<float, kEpiGeneric>(e, off, m, n, pre);
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = acc[i][j];
+        epilogue_finish8<float, kEpiGeneric>(e, m, n, N, off, v, pre, bias8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) cs[j] += v[j];
+      }
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int m = m0 + ty * 8 + i;
+      if (m >= M) continue;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int n = n0 + tx * 8 + j;
+        if (n < N) cs[j] += epilogue_store1_f32(ep, m, n, N, acc[i][j], first);
+      }
     }
   }
   if (ep.col_sum != nullptr) {
@@ -218,16 +246,18 @@ int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int6
   // 16-byte operand loads need 16-byte aligned rows; K-major tiles additionally start at multiples of 4 in k
   const int vec_a = aligned16(A) && lda % 4 == 0 && (a_major == 1 || k_per_split % 4 == 0);
   const int vec_b = aligned16(B) && ldb % 4 == 0 && (b_major == 1 || k_per_split % 4 == 0);
+  const int vec_c = N % 8 == 0 && ep.ldc % 8 == 0 && aligned16(ep.C) && aligned16(ep.residual) && aligned16(ep.mask_aux) &&
+                    aligned16(ep.row_add) && aligned16(ep.bias);
   ProfScope prof(kProfGemmF32, 2.0 * M * N * K, 1, stream);
   VB_REQUIRE(grid.y <= 65535 && grid.z <= 65535, "gemm_f32: grid too large");
   if (a_major == 0 && b_major == 0)
-    gemm_f32_kernel<true, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b);
+    gemm_f32_kernel<true, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b, vec_c);
   else if (a_major == 0 && b_major == 1)
-    gemm_f32_kernel<true, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b);
+    gemm_f32_kernel<true, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b, vec_c);
   else if (a_major == 1 && b_major == 1)
-    gemm_f32_kernel<false, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b);
+    gemm_f32_kernel<false, false><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b, vec_c);
   else if (a_major == 1 && b_major == 0)
-    gemm_f32_kernel<false, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b);
+    gemm_f32_kernel<false, true><<<grid, FTHREADS, 0, stream>>>(A, lda, B, ldb, M, N, K, k_per_split, ep, vec_a, vec_b, vec_c);
   else {
     set_error("gemm_f32: bad operand majors a=%d b=%d", a_major, b_major);
     return kErrInvalid;
