@@ -161,7 +161,7 @@ def test_layernorm_fwd_bwd(lib, M, E):
 
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("M,E,add", [(197 * 7, 768, 1), (1000, 384, 1), (333, 1024, 0), (64, 8, 1), (4099, 192, 0),
-                                     (50, 3072, 1), (9, 100, 1)])
+                                     (50, 3072, 1), (9, 100, 1), (577 * 3, 1280, 1), (200, 1536, 0)])
 def test_layernorm_bwd_masked_operand_and_bias_grad(lib, dt, M, E, add):
     """The fused outputs of the LayerNorm backward: g (+)= dx, dyn = cast(g_new * dropout factors) and
     dyn_colsum += column sums of dyn — bulk-copy ring kernel (E % 8 == 0, E <= 1024) and the generic one."""

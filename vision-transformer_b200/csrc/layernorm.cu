@@ -232,7 +232,9 @@ ln_bwd_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, const flo
 constexpr int LNB_WARPS = 8;
 constexpr int LNB_MAX_STAGES = 4;
 
-template <typename DyT, int CH>
+// KEEP: xhat / dy of the row stay in registers between the two passes (CH <= 8); otherwise they are re-read from
+// the shared-memory slot in the second pass so that wide rows (E up to 1536, CH = 10 / 12) do not spill.
+template <typename DyT, int CH, bool KEEP>
 __global__ void __launch_bounds__(LNB_WARPS * 32, 1)
 ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
                    const float* __restrict__ rstd_in, const float* __restrict__ gamma, float* __restrict__ g,
@@ -246,6 +248,7 @@ ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, cons
   const uint32_t row_x = E * 4u, row_g = add_to_g ? E * 4u : 0u, row_dy = E * static_cast<uint32_t>(sizeof(DyT));
   const uint32_t stage_bytes = row_x + row_g + row_dy;
   uint64_t* bar = bars + warp * LNB_MAX_STAGES;
+  const int nwarps = blockDim.x >> 5;   // 8, or 4 for wide rows (slot size)
   const uint32_t ring = smem_u32(bars + LNB_WARPS * LNB_MAX_STAGES) + warp * nst * stage_bytes;
   const uint32_t sgam = smem_u32(s_gamma);
 
@@ -260,7 +263,7 @@ ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, cons
   __syncthreads();
 
   const int E4 = E >> 2;
-  const int w0 = blockIdx.x * LNB_WARPS + warp, stride = gridDim.x * LNB_WARPS;
+  const int w0 = blockIdx.x * nwarps + warp, stride = gridDim.x * nwarps;
   const int nrows = w0 < M ? (M - w0 + stride - 1) / stride : 0;
   auto issue = [&](int it) {  // lane 0
     const int st = it % nst;
@@ -305,34 +308,41 @@ ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, cons
     mbar_wait(bar + st, (it / nst) & 1);
     const uint32_t sx = ring + st * stage_bytes, sg = sx + row_x, sdy = sg + row_g;
 
-    float h[CH][4], d[CH][4];
+    constexpr int NK = KEEP ? CH : 1;
+    float h[NK][4], d[NK][4];
     float s1 = 0.f, s2 = 0.f;
+    // xhat and dy of chunk i of the current row, from the shared-memory slot
+    auto row_chunk = [&](int i, float (&hh)[4], float (&dd)[4]) {
+      const float4 xv = lds128(sx + 16 * i);
+      if constexpr (sizeof(DyT) == 2) {
+        const uint2 raw = lds64(sdy + 8 * i);
+        dd[0] = __uint_as_float(raw.x << 16); dd[1] = __uint_as_float(raw.x & 0xffff0000u);
+        dd[2] = __uint_as_float(raw.y << 16); dd[3] = __uint_as_float(raw.y & 0xffff0000u);
+      } else {
+        const float4 dv = lds128(sdy + 16 * i);
+        dd[0] = dv.x; dd[1] = dv.y; dd[2] = dv.z; dd[3] = dv.w;
+      }
+      hh[0] = (xv.x - mean) * rstd; hh[1] = (xv.y - mean) * rstd;
+      hh[2] = (xv.z - mean) * rstd; hh[3] = (xv.w - mean) * rstd;
+    };
 #pragma unroll
     for (int k = 0; k < CH; ++k) {
       const int i = lane + 32 * k;
+      float hh[4] = {0.f, 0.f, 0.f, 0.f}, dd[4] = {0.f, 0.f, 0.f, 0.f};
       if (i < E4) {
-        const float4 xv = lds128(sx + 16 * i);
+        row_chunk(i, hh, dd);
         const float4 gm = lds128(sgam + 16 * i);
-        if constexpr (sizeof(DyT) == 2) {
-          const uint2 raw = lds64(sdy + 8 * i);
-          d[k][0] = __uint_as_float(raw.x << 16); d[k][1] = __uint_as_float(raw.x & 0xffff0000u);
-          d[k][2] = __uint_as_float(raw.y << 16); d[k][3] = __uint_as_float(raw.y & 0xffff0000u);
-        } else {
-          const float4 dv = lds128(sdy + 16 * i);
-          d[k][0] = dv.x; d[k][1] = dv.y; d[k][2] = dv.z; d[k][3] = dv.w;
-        }
-        h[k][0] = (xv.x - mean) * rstd; h[k][1] = (xv.y - mean) * rstd;
-        h[k][2] = (xv.z - mean) * rstd; h[k][3] = (xv.w - mean) * rstd;
         const float gg[4] = {gm.x, gm.y, gm.z, gm.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float t = d[k][j] * gg[j];
+          const float t = dd[j] * gg[j];
           s1 += t;
-          s2 = fmaf(t, h[k][j], s2);
+          s2 = fmaf(t, hh[j], s2);
         }
-      } else {
+      }
+      if constexpr (KEEP) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) { h[k][j] = 0.f; d[k][j] = 0.f; }
+        for (int j = 0; j < 4; ++j) { h[k][j] = hh[j]; d[k][j] = dd[j]; }
       }
     }
 #pragma unroll
@@ -351,12 +361,19 @@ ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, cons
       if (i < E4) {
         const float4 gm = lds128(sgam + 16 * i);
         const float gg[4] = {gm.x, gm.y, gm.z, gm.w};
+        float hh[4], dd[4];
+        if constexpr (KEEP) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) { hh[j] = h[k][j]; dd[j] = d[k][j]; }
+        } else {
+          row_chunk(i, hh, dd);
+        }
         float o[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          o[j] = rstd * (d[k][j] * gg[j] - s1 - h[k][j] * s2);
-          rg[k][j] = fmaf(d[k][j], h[k][j], rg[k][j]);
-          rb[k][j] += d[k][j];
+          o[j] = rstd * (dd[j] * gg[j] - s1 - hh[j] * s2);
+          rg[k][j] = fmaf(dd[j], hh[j], rg[k][j]);
+          rb[k][j] += dd[j];
         }
         if (add_to_g) {
           const float4 old = lds128(sg + 16 * i);
@@ -446,27 +463,29 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
   ProfScope prof(kProfLnBwd, static_cast<double>(M) * E * (4 + es + 4 + (add_to_g ? 4 : 0) + (dyn ? es : 0)) + 8.0 * M,
                  1, stream);
   // ---- ring kernel
-  if ((E & 7) == 0 && E <= 1024 && M >= 4 * LNB_WARPS) {
+  if ((E & 7) == 0 && E <= 1536 && M >= 4 * LNB_WARPS) {
+    const int nwarps = E <= 1024 ? LNB_WARPS : 4;   // wide rows: fewer, deeper rings
     const size_t stage = static_cast<size_t>(E) * (4 + (add_to_g ? 4 : 0) + (dy_bf16 ? 2 : 4));
     const size_t fixed = static_cast<size_t>(E) * 16 + LNB_WARPS * LNB_MAX_STAGES * 8;
-    int nst = static_cast<int>((216 * 1024 - fixed) / (LNB_WARPS * stage));
+    int nst = static_cast<int>((216 * 1024 - fixed) / (nwarps * stage));
     if (nst > LNB_MAX_STAGES) nst = LNB_MAX_STAGES;
     if (nst >= 2) {
-      const size_t smem = fixed + static_cast<size_t>(nst) * LNB_WARPS * stage;
+      const size_t smem = fixed + static_cast<size_t>(nst) * nwarps * stage;
       const int ch = ceil_div(E, 128);
-      const int grid = std::min(num_sms(), ceil_div(M, LNB_WARPS));
+      const int grid = std::min(num_sms(), ceil_div(M, nwarps));
 #define VB_LN_RING(T, C)                                                                                          \
   do {                                                                                                            \
-    VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
+    VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C, (C <= 8)>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                        static_cast<int>(smem)));                                                  \
-    VB_CHECK_CUDA(launch_pdl(ln_bwd_ring_kernel<T, C>, dim3(grid), dim3(LNB_WARPS * 32), smem, stream, 1,         \
+    VB_CHECK_CUDA(launch_pdl(ln_bwd_ring_kernel<T, C, (C <= 8)>, dim3(grid), dim3(nwarps * 32), smem, stream, 1,    \
                              static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta,         \
                              static_cast<T*>(dyn), dyn_colsum, drop, M, E, nst));                                 \
   } while (0)
 #define VB_LN_RING_CH(T)                                                                                          \
   do {                                                                                                            \
     if (ch <= 1) VB_LN_RING(T, 1); else if (ch <= 2) VB_LN_RING(T, 2); else if (ch <= 3) VB_LN_RING(T, 3);        \
-    else if (ch <= 4) VB_LN_RING(T, 4); else if (ch <= 6) VB_LN_RING(T, 6); else VB_LN_RING(T, 8);                \
+    else if (ch <= 4) VB_LN_RING(T, 4); else if (ch <= 6) VB_LN_RING(T, 6); else if (ch <= 8) VB_LN_RING(T, 8);   \
+    else if (ch <= 10) VB_LN_RING(T, 10); else VB_LN_RING(T, 12);                                                 \
   } while (0)
       if (dy_bf16) VB_LN_RING_CH(bf16); else VB_LN_RING_CH(float);
 #undef VB_LN_RING_CH
