@@ -25,12 +25,15 @@ constexpr int kThreads = 64 + kEpiWarps * 32;
 
 // CG = 1: one CTA owns a 128 x BN tile.  CG = 2: a CTA PAIR (cluster of 2, tcgen05 cta_group::2) owns a 256 x BN tile;
 // each CTA stages its own 128 rows of A and HALF of the B tile, the leader issues M = 256 MMAs that read both halves,
-// so every SM pulls a third less operand traffic through L2 and shared memory per output element.
+// so every SM pulls a third less operand traffic through L2 and shared memory per output element.  CG = 4: a cluster
+// of TWO pairs works on two vertically adjacent 256 x BN tiles; they need the same B tile, so each CTA fetches only a
+// QUARTER of it and TMA-multicasts that quarter to its counterpart in the other pair (24 KB instead of 32 KB per CTA
+// and k-block: the K-major call sites are bound by the ~43 B/clk/SM L2->SM feed, not by the tensor pipe).
 template <int BN, int CG>
 struct TileCfg {
-  static constexpr int STAGES = CG == 2 ? 6 : 4;
+  static constexpr int STAGES = CG >= 2 ? 6 : 4;
   static constexpr int A_BYTES = BM * BK * 2;            // 16 KB
-  static constexpr int B_BYTES = BN * BK * 2 / CG;       // 32 KB @ BN=256 (16 KB per CTA of a pair)
+  static constexpr int B_BYTES = BN * BK * 2 / (CG >= 2 ? 2 : 1);   // 32 KB @ BN=256 (16 KB per CTA of a pair)
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_BYTES = 256;
   static constexpr int STG_BYTES = kEpiWarps * 32 * 128;   // per epilogue warp: 32 rows x 32 fp32 transpose buffer
@@ -51,9 +54,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
   using Cfg = TileCfg<BN, CG>;
   constexpr int kStages = Cfg::STAGES;
   // pair rank / work-unit walk: a unit is one (tile, split); CTAs of a pair walk the same units
-  const uint32_t rank = CG == 2 ? ptx::cluster_ctarank() : 0u;
-  const int walker = CG == 2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
-  const int nwalkers = CG == 2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  const uint32_t rank = CG >= 2 ? ptx::cluster_ctarank() : 0u;   // rank in the cluster: pair = rank >> 1, half = rank & 1
+  const uint32_t pair = rank >> 1, half_id = rank & 1u;
+  const int walker = static_cast<int>(blockIdx.x) / CG;
+  const int nwalkers = static_cast<int>(gridDim.x) / CG;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::STAGE_BYTES);
@@ -72,16 +76,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     ptx::tma_prefetch_desc(&tma_b);
     for (int s = 0; s < kStages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], CG == 4 ? 2 : 1);   // CG 4: both pairs read what lands in this slot
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tmem_full[s], 1);
-      ptx::mbar_init(&tmem_empty[s], kEpiWarps * CG);   // pair: the leader's barrier collects both CTAs' epilogue warps
+      ptx::mbar_init(&tmem_empty[s], kEpiWarps * (CG >= 2 ? 2 : 1));   // pair: the leader collects both CTAs' epilogue warps
     }
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
-    if constexpr (CG == 2) {
+    if constexpr (CG >= 2) {
       ptx::tmem_alloc_pair(tmem_ptr, Cfg::TMEM_COLS);
       ptx::tmem_relinquish_pair();
     } else {
@@ -90,7 +94,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     }
   }
   ptx::tc_fence_before();
-  if constexpr (CG == 2) ptx::cluster_sync(); else __syncthreads();
+  if constexpr (CG >= 2) ptx::cluster_sync(); else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   pdl_wait();      // everything above overlapped the previous kernel's tail; global memory is touched only below
@@ -109,16 +113,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         const int kb0 = split * p.kb_per_split;
         const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
         const int m_row = (m_blk * CG + static_cast<int>(rank)) * BM;          // my 128 rows of A
-        const int n_row = n_blk * BN + static_cast<int>(rank) * (BN / CG);     // my share of the B tile
+        // my share of the B tile: the whole tile, my half, or (CG 4) the quarter I fetch for both pairs
+        const int n_row = n_blk * BN + (CG >= 2 ? static_cast<int>(half_id) * (BN / 2) : 0) +
+                          (CG == 4 ? static_cast<int>(pair) * (BN / 4) : 0);
+        const uint16_t mc_mask = static_cast<uint16_t>((1u << half_id) | (1u << (2u + half_id)));
         for (int kb = kb0; kb < kb1; ++kb) {
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1u);
           // pair: the leader's barrier expects the bytes of BOTH CTAs; the peer's copies are credited to it
-          if (CG == 1 || rank == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], CG * Cfg::STAGE_BYTES);
+          if (CG == 1 || half_id == 0) ptx::mbar_arrive_expect_tx(&full_bar[stage], (CG >= 2 ? 2 : 1) * Cfg::STAGE_BYTES);
           uint8_t* sA = smem + stage * Cfg::STAGE_BYTES;
           uint8_t* sB = sA + Cfg::A_BYTES;
           auto load = [&](uint8_t* dst, const CUtensorMap* tm, int c0, int c1) {
-            if constexpr (CG == 2) ptx::tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
+            if constexpr (CG >= 2) ptx::tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
             else ptx::tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
+          };
+          auto load_b = [&](uint8_t* dst, int c0, int c1) {
+            if constexpr (CG == 4) ptx::tma_load_2d_pair_mc(dst, &tma_b, &full_bar[stage], c0, c1, mc_mask);
+            else load(dst, &tma_b, c0, c1);
           };
           if constexpr (AMAJ == 0) {
             load(sA, &tma_a, kb * BK, m_row);
@@ -126,11 +137,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) load(sA + j * (BK * 128), &tma_a, m_row + j * 64, kb * BK);
           }
+          // CG 4: my quarter goes to offset pair * 8 KB of the half tile (64 K-major rows, or one 64-wide MN slab)
+          uint8_t* sBq = sB + (CG == 4 ? pair * (Cfg::B_BYTES / 2) : 0u);
           if constexpr (BMAJ == 0) {
-            load(sB, &tma_b, kb * BK, n_row);
+            load_b(sBq, kb * BK, n_row);
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / CG / 64; ++j) load(sB + j * (BK * 128), &tma_b, n_row + j * 64, kb * BK);
+            for (int j = 0; j < BN / CG / 64; ++j) load_b(sBq + j * (BK * 128), n_row + j * 64, kb * BK);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
@@ -138,8 +151,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (one thread)
-    if (lane == 0 && rank == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(BM * CG, BN, AMAJ, BMAJ);
+    if (lane == 0 && half_id == 0) {
+      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(BM * (CG >= 2 ? 2 : 1), BN, AMAJ, BMAJ);
+      const uint16_t pair_mask = static_cast<uint16_t>(3u << (2u * pair));   // both CTAs of my pair
+      const uint16_t slot_mask = CG == 4 ? uint16_t(0xF) : pair_mask;          // everyone whose loads land in the slot
       // K-major: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.
       // MN-major: 64-wide MN slabs BK*128 B apart (LBO), 8 k-rows = 1024 B (SBO), k-step = 16 rows * 128 B.
       constexpr uint32_t a_lbo = AMAJ == 0 ? 16 : BK * 128, a_sbo = 1024, a_kstep = AMAJ == 0 ? 32 : 2048;
@@ -164,15 +179,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t da = ptx::make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, a_sbo);
             const uint64_t db = ptx::make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, b_sbo);
-            if constexpr (CG == 2) ptx::umma_f16_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if constexpr (CG >= 2) ptx::umma_f16_pair(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
             else ptx::umma_f16(d_tmem, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           // smem slot reusable once these MMAs retire (pair: in both CTAs)
-          if constexpr (CG == 2) ptx::umma_commit_pair(&empty_bar[stage], 3); else ptx::umma_commit(&empty_bar[stage]);
+          if constexpr (CG >= 2) ptx::umma_commit_pair(&empty_bar[stage], slot_mask); else ptx::umma_commit(&empty_bar[stage]);
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
         // accumulator complete -> epilogue (pair: each CTA drains its own 128 lanes)
-        if constexpr (CG == 2) ptx::umma_commit_pair(&tmem_full[acc], 3); else ptx::umma_commit(&tmem_full[acc]);
+        if constexpr (CG >= 2) ptx::umma_commit_pair(&tmem_full[acc], pair_mask); else ptx::umma_commit(&tmem_full[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
@@ -315,17 +330,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) {
-        if constexpr (CG == 2) ptx::mbar_arrive_cluster(&tmem_empty[acc], 0); else ptx::mbar_arrive(&tmem_empty[acc]);
+        if constexpr (CG >= 2) ptx::mbar_arrive_cluster(&tmem_empty[acc], 2u * pair); else ptx::mbar_arrive(&tmem_empty[acc]);
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   }
 
   ptx::tc_fence_before();
-  if constexpr (CG == 2) ptx::cluster_sync(); else __syncthreads();
+  if constexpr (CG >= 2) ptx::cluster_sync(); else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
-    if constexpr (CG == 2) ptx::tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS); else ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    if constexpr (CG >= 2) ptx::tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS); else ptx::tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
   }
 }
 
@@ -399,19 +414,44 @@ int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
     const int grid = total < num_sms() ? total : num_sms();
     VB_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), Cfg::SMEM_BYTES, stream, 1, ta, tb, p, ep));
   } else {
-    const int pairs = num_sms() / 2;
-    const int grid = 2 * (total < pairs ? total : pairs);
-    VB_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), Cfg::SMEM_BYTES, stream, 2, ta, tb, p, ep));
+    // persistent walk: only as many clusters as can be co-resident (clusters of 4 do not tile all 148 SMs)
+    static int max_clusters = 0;
+    static std::once_flag occ_once;
+    std::call_once(occ_once, [&] {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(num_sms() / CG * CG);
+      cfg.blockDim = dim3(kThreads);
+      cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = CG;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) n = num_sms() / CG;
+      max_clusters = n;
+    });
+    const int clusters = total < max_clusters ? total : max_clusters;
+    VB_CHECK_CUDA(launch_pdl(kern, dim3(CG * clusters), dim3(kThreads), Cfg::SMEM_BYTES, stream, CG, ta, tb, p, ep));
   }
   VB_CHECK_LAUNCH();
   return kOk;
 }
 
-// pairs = true: operands / TcParams were prepared for 256-row tiles and half-width B boxes
+// cg: CTAs per cluster the operands / TcParams were prepared for (128*cg-row tiles, BN/cg-row B boxes).  The cluster
+// of 4 is instantiated for the forward-type call sites only (K-major x K-major and K-major x MN-major operands).
 template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI>
-int launch_tc(bool pairs, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
+int launch_tc(int cg, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
               cudaStream_t stream) {
-  if (pairs) return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 2>(ta, tb, p, ep, stream);
+#ifdef VITB200_CG4   // measured 4-8 % SLOWER than pairs on B200 (only 33 clusters of 4 fit the 148 SMs): off by default
+  if constexpr (AMAJ == 0) {
+    if (cg == 4) return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 4>(ta, tb, p, ep, stream);
+  }
+#endif
+  if (cg == 4) cg = 2;
+  if (cg == 2) return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 2>(ta, tb, p, ep, stream);
   return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 1>(ta, tb, p, ep, stream);
 }
 
@@ -432,9 +472,12 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   constexpr int BN = 256;
 
   // CTA pairs (256-row tiles) whenever there is more than one 128-row tile of output; VITB200_GEMM_CG=1|2 forces.
-  static const int force_cg = getenv("VITB200_GEMM_CG") ? atoi(getenv("VITB200_GEMM_CG")) : 0;
-  const int cg = force_cg == 1 || force_cg == 2 ? force_cg : (M > BM ? 2 : 1);
-  const bool pairs = cg == 2;
+  static const int force_cg = getenv("VITB200_GEMM_CG") ? atoi(getenv("VITB200_GEMM_CG")) : 0;   // 1 | 2 | 4 forces
+  int cg = M > BM ? 2 : 1;
+#ifdef VITB200_CG4
+  if (force_cg == 4 && a_major == 0 && !ep.accumulate) cg = 4;   // experiment only, see launch_tc
+#endif
+  if (force_cg == 1 || force_cg == 2) cg = force_cg;
 
   CUtensorMap ta, tb;
   if (a_major == 0) VB_PROPAGATE(make_tmap_bf16(&ta, A, M, K, lda, BK, BM));
@@ -462,31 +505,31 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   // Hot call sites of the training step get a compile-time-specialised epilogue; anything else runs the generic one.
   const uint32_t f = epi_flags(ep);
 #define VB_TC(AM, BM_, T, FL) \
-  if (f == (FL)) return launch_tc<AM, BM_, BN, T, (FL)>(pairs, ta, tb, p, ep, stream)
+  if (f == (FL)) return launch_tc<AM, BM_, BN, T, (FL)>(cg, ta, tb, p, ep, stream)
   if (a_major == 0 && b_major == 0) {
     if (out_f32) {
       VB_TC(0, 0, float, 0u);
       VB_TC(0, 0, float, kEpiBias | kEpiResidual);
       VB_TC(0, 0, float, kEpiBias | kEpiDrop | kEpiResidual);
       VB_TC(0, 0, float, kEpiBias | kEpiRowMap);
-      return launch_tc<0, 0, BN, float, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
+      return launch_tc<0, 0, BN, float, kEpiGeneric>(cg, ta, tb, p, ep, stream);
     }
     VB_TC(0, 0, bf16, 0u);
     VB_TC(0, 0, bf16, kEpiBias | kEpiRelu);
     VB_TC(0, 0, bf16, kEpiBias | kEpiRelu | kEpiBitsOut);
-    return launch_tc<0, 0, BN, bf16, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
+    return launch_tc<0, 0, BN, bf16, kEpiGeneric>(cg, ta, tb, p, ep, stream);
   } else if (a_major == 0 && b_major == 1) {
-    if (out_f32) return launch_tc<0, 1, BN, float, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
+    if (out_f32) return launch_tc<0, 1, BN, float, kEpiGeneric>(cg, ta, tb, p, ep, stream);
     VB_TC(0, 1, bf16, 0u);
     VB_TC(0, 1, bf16, kEpiMask | kEpiColSum);
     VB_TC(0, 1, bf16, kEpiBitMask | kEpiColSum);
-    return launch_tc<0, 1, BN, bf16, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
+    return launch_tc<0, 1, BN, bf16, kEpiGeneric>(cg, ta, tb, p, ep, stream);
   } else if (a_major == 1 && b_major == 1) {
     if (out_f32) {
       VB_TC(1, 1, float, kEpiAccum);
-      return launch_tc<1, 1, BN, float, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
+      return launch_tc<1, 1, BN, float, kEpiGeneric>(cg, ta, tb, p, ep, stream);
     }
-    return launch_tc<1, 1, BN, bf16, kEpiGeneric>(pairs, ta, tb, p, ep, stream);
+    return launch_tc<1, 1, BN, bf16, kEpiGeneric>(cg, ta, tb, p, ep, stream);
   }
 #undef VB_TC
   set_error("gemm_tc: operand major combination a=%d b=%d not instantiated", a_major, b_major);
