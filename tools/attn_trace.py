@@ -32,15 +32,15 @@ names = {1: "mma: wait slot_free", 2: "mma: slot free", 3: "mma: sd issued", 4: 
 for mode in (1, 0):
     base = mode * 2048
     evs = []
-    for role in range(3):
+    for role in range(4):
         for v in tr[base + role * 512: base + (role + 1) * 512]:
             if v:
                 evs.append((v >> 8, role, v & 255))
     evs.sort()
     t0 = evs[0][0]
     print(f"==== MODE {mode}: {len(evs)} events; first 120 (clk since start, role, event)")
-    last = {0: t0, 1: t0, 2: t0}
-    for clk, role, tag in evs[:120]:
+    last = {0: t0, 1: t0, 2: t0, 3: t0}
+    for clk, role, tag in evs[:int(os.environ.get('NEV', 120))]:
         print(f"{clk - t0:8d}  +{clk - last[role]:6d}  r{role}  {names.get(tag, tag)}")
         last[role] = clk
     # per-item period for the MMA thread: time between consecutive 'kv full'

@@ -36,17 +36,20 @@ out_e, out_f, out_3e = torch.empty(M, E, device=dev, dtype=bf), torch.empty(M, F
 b_e, b_f = rnd(E, dt=torch.float32), rnd(F, dt=torch.float32)
 dw_qkv, dw_proj, dw_fc1, dw_fc2 = (torch.zeros(s, device=dev) for s in ((3 * E, E), (E, E), (F, E), (E, F)))
 K0, K1 = _C.MAJOR_K, _C.MAJOR_MN
+hbits = torch.zeros((F // 32) * M, device=dev, dtype=torch.int32)  # ReLU sign bits, word (n/32)*M + m
 sites = [
     # name, flops, ours, torch
     ("fwd qkv   NT bf16", 2 * M * 3 * E * E, lambda: _C.gemm(x_e, w_qkv, out_3e, M=M, N=3 * E, K=E), lambda: x_e @ w_qkv.t()),
     ("fwd proj  NT f32 bias+res", 2 * M * E * E, lambda: _C.gemm(x_e, w_proj, out_e32, M=M, N=E, K=E, bias=b_e, residual=res), lambda: x_e @ w_proj.t()),
     ("fwd proj  NT f32 bias+drop+res", 2 * M * E * E, lambda: _C.gemm(x_e, w_proj, out_e32, M=M, N=E, K=E, bias=b_e, residual=res, dropout=(0.2, 1, 2)), lambda: x_e @ w_proj.t()),
     ("fwd fc1   NT bf16 bias+relu", 2 * M * F * E, lambda: _C.gemm(x_e, w_fc1, out_f, M=M, N=F, K=E, bias=b_f, relu=True), lambda: x_e @ w_fc1.t()),
+    ("fwd fc1   NT bf16 bias+relu+bits", 2 * M * F * E, lambda: _C.gemm(x_e, w_fc1, out_f, M=M, N=F, K=E, bias=b_f, relu=True, bits_out=hbits, bits_rows=M), lambda: x_e @ w_fc1.t()),
     ("fwd fc2   NT f32 bias+res", 2 * M * F * E, lambda: _C.gemm(x_f, w_fc2, out_e32, M=M, N=E, K=F, bias=b_e, residual=res), lambda: x_f @ w_fc2.t()),
     ("fwd fc2   NT f32 bias+drop+res", 2 * M * F * E, lambda: _C.gemm(x_f, w_fc2, out_e32, M=M, N=E, K=F, bias=b_e, residual=res, dropout=(0.2, 1, 3)), lambda: x_f @ w_fc2.t()),
     ("bwd dW2   TN acc", 2 * M * F * E, lambda: _C.gemm(x_e, x_f, dw_fc2, a_major=K1, b_major=K1, M=E, N=F, K=M, accumulate=True), lambda: x_e.t() @ x_f),
     ("bwd dh    NN bf16 mask", 2 * M * F * E, lambda: _C.gemm(x_e, w_fc2, out_f, b_major=K1, M=M, N=F, K=E, mask_aux=x_f), lambda: x_e @ w_fc2),
     ("bwd dh    NN bf16 mask+colsum", 2 * M * F * E, lambda: _C.gemm(x_e, w_fc2, out_f, b_major=K1, M=M, N=F, K=E, mask_aux=x_f, col_sum=b_f), lambda: x_e @ w_fc2),
+    ("bwd dh    NN bf16 bits+colsum", 2 * M * F * E, lambda: _C.gemm(x_e, w_fc2, out_f, b_major=K1, M=M, N=F, K=E, mask_bits=hbits, bits_rows=M, col_sum=b_f), lambda: x_e @ w_fc2),
     ("bwd dh    NN bf16 plain", 2 * M * F * E, lambda: _C.gemm(x_e, w_fc2, out_f, b_major=K1, M=M, N=F, K=E), lambda: x_e @ w_fc2),
     ("bwd dW1   TN acc", 2 * M * F * E, lambda: _C.gemm(x_f, x_e, dw_fc1, a_major=K1, b_major=K1, M=F, N=E, K=M, accumulate=True), lambda: x_f.t() @ x_e),
     ("bwd dln2  NN bf16", 2 * M * F * E, lambda: _C.gemm(x_f, w_fc1, out_e, b_major=K1, M=M, N=E, K=F), lambda: x_f @ w_fc1),
@@ -65,7 +68,7 @@ for name, fl, ours, ref in sites:
     if "drop" not in name or True:
         pass
     print(f"{name:<34} ours {to*1e3:7.1f} us {fl/to/1e9:7.0f} TF/s | cuBLAS {tt*1e3:7.1f} us {fl/tt/1e9:7.0f} TF/s | ratio {to/tt:4.2f}")
-    if ("bias+res" in name and "drop" not in name) or "plain" in name or name.endswith("mask"):
+    if ("bias+res" in name and "drop" not in name) or "plain" in name or "mask" in name or name.endswith("relu"):
         continue  # the dropout variant is the one the training step uses
     tot_o += to; tot_t += tt
 print(f"per-block GEMM total: ours {tot_o:.3f} ms, cuBLAS (no epilogues) {tot_t:.3f} ms; x12 blocks = {12*tot_o:.1f} / {12*tot_t:.1f} ms")

@@ -38,6 +38,7 @@ constexpr float kLn2 = 0.6931471805599453f;
 struct FwdParams {
   int T, TP, H, items;   // TP = T rounded up to a multiple of 16 (UMMA N and PV K extent)
   float scale_log2;      // scale * log2(e)
+  int st256;             // output rows are 32-byte aligned: store whole sectors per thread
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -236,14 +237,19 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
         ptx::tmem_ld_32x32(t_row + 128u + static_cast<uint32_t>(c * 32), r);
         ptx::tmem_ld_wait();
         if (live) {
+          uint32_t w[16];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 o;
-            o.x = pack_bf16x2(__uint_as_float(r[8 * j + 0]) * inv, __uint_as_float(r[8 * j + 1]) * inv);
-            o.y = pack_bf16x2(__uint_as_float(r[8 * j + 2]) * inv, __uint_as_float(r[8 * j + 3]) * inv);
-            o.z = pack_bf16x2(__uint_as_float(r[8 * j + 4]) * inv, __uint_as_float(r[8 * j + 5]) * inv);
-            o.w = pack_bf16x2(__uint_as_float(r[8 * j + 6]) * inv, __uint_as_float(r[8 * j + 7]) * inv);
-            *reinterpret_cast<uint4*>(orow + c * 32 + j * 8) = o;
+          for (int j = 0; j < 16; ++j)
+            w[j] = pack_bf16x2(__uint_as_float(r[2 * j]) * inv, __uint_as_float(r[2 * j + 1]) * inv);
+          if (p.st256) {                            // whole 32-byte sectors per thread (rows are 32-byte aligned)
+            const uint32_t lo[8] = {w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]};
+            const uint32_t hi[8] = {w[8], w[9], w[10], w[11], w[12], w[13], w[14], w[15]};
+            ptx::stg256(orow + c * 32, lo);
+            ptx::stg256(orow + c * 32 + 16, hi);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<uint4*>(orow + c * 32 + j * 8) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
           }
         }
       }
@@ -279,7 +285,8 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
 //   output MMAs   : TS form, A = the bf16 chunk straight from tensor memory, accumulate over the unit's chunks into
 //                   two accumulators at columns 384..447 | 448..511 (MODE 0: dQ split by k-step parity, MODE 1: dV | dK)
 // Both groups drain half of each accumulator (32 columns) once a unit's last chunk is committed.
-constexpr int kBwdThreads = 64 + 8 * 32;
+constexpr int kBwdThreads = 64 + 8 * 32 + 32;   // producer, S/dP issuer, 8 element-wise warps, output-MMA issuer
+constexpr int kOutWarp = 10;
 constexpr int kStatBytes = 2048;            // lse*log2e [256] | delta*scale [256] per stage
 
 struct BwdParams {
@@ -287,6 +294,7 @@ struct BwdParams {
   int W, nchk;                              // chunk width (multiple of 16) and chunks per unit
   int tile_bytes, stage_bytes;              // TP*128, 4*tile_bytes + kStatBytes
   float scale, scale_log2;
+  int st256;                                // dqkv rows are 32-byte aligned: drain with 32-byte stores
   int dbg;                                  // timing experiments only (VITB200_ATTN_DBG), 0 in production
   long long* trace;                         // optional event trace of CTA 0 (tools/attn_trace.py), else nullptr
 };
@@ -305,10 +313,13 @@ __device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[N]
   if constexpr (N == 16) ptx::tmem_st_32x16(taddr, r); else ptx::tmem_st_32x8(taddr, r);
 }
 
+// Column split of a chunk of wc columns (a multiple of 16) between the two element-wise groups, in whole k-steps.
+__device__ __forceinline__ int bwd_split(int wc) { return ((wc >> 4) + 1) >> 1 << 4; }
+
 // N columns [c0, c0+N) of one chunk (global column index gcol0 .. gcol0+N-1) for this thread's row.
 template <int MODE, int N>
-__device__ __forceinline__ void bwd_piece(uint32_t tS, uint32_t tP, int c0, int gcol0, int T, float sl2, float scale,
-                                          float lse2r, float dscr, const float* __restrict__ stat) {
+__device__ __forceinline__ void bwd_piece(uint32_t tS, uint32_t tP, int c0, int d0, int gcol0, int T, float sl2,
+                                          float scale, float lse2r, float dscr, uint32_t stat_s) {
   uint32_t rs[N], rp[N];
   tmem_ld_n<N>(tS + static_cast<uint32_t>(c0), rs);
   tmem_ld_n<N>(tP + static_cast<uint32_t>(c0), rp);
@@ -336,11 +347,10 @@ __device__ __forceinline__ void bwd_piece(uint32_t tS, uint32_t tP, int c0, int 
       }
     }
   } else {
-    const float4* l4 = reinterpret_cast<const float4*>(stat + gcol0);
-    const float4* d4 = reinterpret_cast<const float4*>(stat + 256 + gcol0);
+    const uint32_t l4 = stat_s + static_cast<uint32_t>(gcol0) * 4u, d4 = l4 + 1024u;
 #pragma unroll
     for (int j4 = 0; j4 < N / 4; ++j4) {
-      const float4 lv = l4[j4], dv = d4[j4];
+      const float4 lv = ptx::lds128(l4 + 16u * j4), dv = ptx::lds128(d4 + 16u * j4);
       const float lj[4] = {lv.x, lv.y, lv.z, lv.w}, dj[4] = {dv.x, dv.y, dv.z, dv.w};
       float pe[4], de[4];
 #pragma unroll
@@ -352,8 +362,8 @@ __device__ __forceinline__ void bwd_piece(uint32_t tS, uint32_t tP, int c0, int 
       pk1[2 * j4] = pack_bf16x2(de[0], de[1]); pk1[2 * j4 + 1] = pack_bf16x2(de[2], de[3]);
     }
   }
-  tmem_st_n<N / 2>(tS + static_cast<uint32_t>(c0 >> 1), pk0);
-  if (MODE == 1) tmem_st_n<N / 2>(tP + static_cast<uint32_t>(c0 >> 1), pk1);
+  tmem_st_n<N / 2>(tS + static_cast<uint32_t>(d0), pk0);
+  if (MODE == 1) tmem_st_n<N / 2>(tP + static_cast<uint32_t>(d0), pk1);
 }
 
 template <int MODE>
@@ -369,11 +379,11 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   uint64_t* st_full = bars + 2;      // [2] row statistics staged (32 producer lanes)
   uint64_t* kv_empty = bars + 4;     // [2]
   uint64_t* sd_full = bars + 6;      // [2] S and dP of the chunk in slot s are ready
-  uint64_t* ew_done = bars + 8;      // [2] bf16 operands of slot s written (4 warps)
-  uint64_t* slot_free = bars + 10;   // [2] output MMAs that read slot s have completed
-  uint64_t* acc_full = bars + 12;    // unit's accumulators complete
-  uint64_t* acc_free = bars + 13;    // accumulators drained (8 warps)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* ew_done = bars + 8;      // [2][2] bf16 operands of slot s, column half h written (4 warps each)
+  uint64_t* slot_free = bars + 12;   // [2] output MMAs that read slot s have completed
+  uint64_t* acc_full = bars + 14;    // unit's accumulators complete
+  uint64_t* acc_free = bars + 15;    // accumulators drained (8 warps)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int E = p.H * HS;
@@ -391,7 +401,8 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       ptx::mbar_init(&st_full[s], 32);
       ptx::mbar_init(&kv_empty[s], 1);
       ptx::mbar_init(&sd_full[s], 1);
-      ptx::mbar_init(&ew_done[s], 4);
+      ptx::mbar_init(&ew_done[2 * s], 4);
+      ptx::mbar_init(&ew_done[2 * s + 1], 4);
       ptx::mbar_init(&slot_free[s], 1);
     }
     ptx::mbar_init(acc_full, 1);
@@ -436,94 +447,125 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       ptx::mbar_arrive(&st_full[st]);
     }
   } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (one thread)
+    // ------------------------------------------------------------------ MMA issuer 1 (one thread): S / dP of every chunk
+    // Two issuing threads in two warps (this one and warp kOutWarp below).  A single thread that alternates between
+    // the S/dP batch of chunk g+1 and the output batch of chunk g spends more clocks on its own waits, fences and
+    // bookkeeping than the tensor pipe needs for the MMAs (2.9K clk per chunk against ~1.1K of MMA time, measured
+    // with the clock64 trace); as two independent state machines the two streams overlap.  The issue path itself is
+    // kept lean: descriptor low words are computed once per item / chunk and advanced with one 32-bit add per MMA.
     if (lane == 0) {
       long long* trbuf = (p.trace != nullptr && blockIdx.x == 0) ? p.trace + MODE * 2048 : nullptr;
       int trn = 0;
-      const uint32_t idesc_o = ptx::make_idesc_bf16_f32(QT, HS, 0, 1);
-      struct Pending { uint32_t sq, sk, sdo; int slot, st, col0, wc, u; uint32_t gph; bool first, last, last_item; };
-      Pending pd{};
-      bool have = false;
-      auto issue_out = [&](const Pending& c) {
-        VB_TR(4);
-        ptx::mbar_wait(&ew_done[c.slot], c.gph);
-        VB_TR(5);
-        if (c.first) ptx::mbar_wait(acc_free, (static_cast<uint32_t>(c.u) & 1u) ^ 1u);
-        ptx::tc_fence_after();
-        const uint32_t tS = tmem_base + static_cast<uint32_t>(c.slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
-        const int k0 = c.col0 / 16, nk = c.wc / 16;
-        // Back-to-back MMAs into ONE accumulator serialise on its latency (~114 clk each, measured); two independent
-        // accumulators interleaved run at ~55 clk each.  MODE 0 therefore splits dQ over two accumulators by k-step
-        // parity (summed in the drain); MODE 1 alternates dV and dK.
-        if (MODE == 0) {
-          for (int k = 0; k < nk; ++k)            // dQ(k parity) += dS K
-            ptx::umma_f16_ts(tmem_base + ((dual && (k & 1)) ? kAcc1 : kAcc0), tS + static_cast<uint32_t>(k * 8),
-                             ptx::make_smem_desc_sw128(c.sk + (k0 + k) * 2048, 64 * 128, 1024), idesc_o,
-                             (c.first && k < (dual ? 2 : 1)) ? 0u : 1u);
-        } else {
-          for (int k = 0; k < nk; ++k) {
-            ptx::umma_f16_ts(tmem_base + kAcc0, tS + static_cast<uint32_t>(k * 8),            // dV += P^T dO
-                             ptx::make_smem_desc_sw128(c.sdo + (k0 + k) * 2048, 64 * 128, 1024), idesc_o,
-                             (c.first && k == 0) ? 0u : 1u);
-            ptx::umma_f16_ts(tmem_base + kAcc1, tP + static_cast<uint32_t>(k * 8),            // dK += dS^T Q
-                             ptx::make_smem_desc_sw128(c.sq + (k0 + k) * 2048, 64 * 128, 1024), idesc_o,
-                             (c.first && k == 0) ? 0u : 1u);
-          }
-        }
-        ptx::umma_commit(&slot_free[c.slot]);
-        VB_TR(6);
-        if (c.last) ptx::umma_commit(acc_full);
-        if (c.last_item) ptx::umma_commit(&kv_empty[c.st]);
-      };
-      int it = 0, u = 0, g = 0;
+      constexpr uint32_t kHi = ptx::smem_desc_hi_sw128(1024);
+      constexpr uint32_t kIdescS0 = ptx::make_idesc_bf16_f32(QT, 0, 0, 0);
+      int it = 0, g = 0;
       for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
         const int st = p.stages == 2 ? (it & 1) : 0;
         const uint32_t ph = p.stages == 2 ? ((it >> 1) & 1) : (it & 1);
         const uint32_t sq = ptx::smem_u32(smem + st * p.stage_bytes);
         const uint32_t sk = sq + p.tile_bytes, sv = sk + p.tile_bytes, sdo = sv + p.tile_bytes;
         // MODE 0: rows from Q / dO, columns from K / V.   MODE 1: rows from K / V, columns from Q / dO.
-        const uint32_t a1 = MODE == 0 ? sq : sk, b1 = MODE == 0 ? sk : sq;
-        const uint32_t a2 = MODE == 0 ? sdo : sv, b2 = MODE == 0 ? sv : sdo;
+        const uint32_t a1 = ptx::smem_desc_lo(MODE == 0 ? sq : sk, 16), b1 = ptx::smem_desc_lo(MODE == 0 ? sk : sq, 16);
+        const uint32_t a2 = ptx::smem_desc_lo(MODE == 0 ? sdo : sv, 16), b2 = ptx::smem_desc_lo(MODE == 0 ? sv : sdo, 16);
         VB_TR(7);
         ptx::mbar_wait(&kv_full[st], ph);
         ptx::tc_fence_after();
         VB_TR(8);
-        for (int t = 0; t < ntile; ++t, ++u) {
+        for (int t = 0; t < ntile; ++t) {
+          const uint32_t a1t = a1 + static_cast<uint32_t>(t * (QT * 128 / 16)), a2t = a2 + static_cast<uint32_t>(t * (QT * 128 / 16));
           for (int j = 0; j < nchk; ++j, ++g) {
             const int slot = g & 1;
             const uint32_t gph = (static_cast<uint32_t>(g) >> 1) & 1u;
             const int col0 = j * W, wc = min(W, p.TP - col0);
-            const uint32_t idesc_s = ptx::make_idesc_bf16_f32(QT, wc, 0, 0);
+            const uint32_t idesc_s = kIdescS0 | (static_cast<uint32_t>(wc >> 3) << 17);
             const uint32_t tS = tmem_base + static_cast<uint32_t>(slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
+            const uint32_t b1c = b1 + static_cast<uint32_t>(col0 * 8), b2c = b2 + static_cast<uint32_t>(col0 * 8);
             VB_TR(1);
             ptx::mbar_wait(&slot_free[slot], gph ^ 1u);
             ptx::tc_fence_after();
             VB_TR(2);
 #pragma unroll
             for (int k = 0; k < HS / 16; ++k) {   // S and dP interleaved: two independent accumulator chains
-              ptx::umma_f16(tS, ptx::make_smem_desc_sw128(a1 + t * (QT * 128) + k * 32, 16, 1024),
-                            ptx::make_smem_desc_sw128(b1 + col0 * 128 + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
-              ptx::umma_f16(tP, ptx::make_smem_desc_sw128(a2 + t * (QT * 128) + k * 32, 16, 1024),
-                            ptx::make_smem_desc_sw128(b2 + col0 * 128 + k * 32, 16, 1024), idesc_s, k > 0 ? 1u : 0u);
+              ptx::umma_f16_lh(tS, a1t + 2u * k, b1c + 2u * k, kHi, idesc_s, k > 0 ? 1u : 0u);
+              ptx::umma_f16_lh(tP, a2t + 2u * k, b2c + 2u * k, kHi, idesc_s, k > 0 ? 1u : 0u);
             }
             ptx::umma_commit(&sd_full[slot]);
             VB_TR(3);
-            if (have) issue_out(pd);
-            pd.sq = sq; pd.sk = sk; pd.sdo = sdo; pd.slot = slot; pd.st = st; pd.col0 = col0; pd.wc = wc; pd.u = u;
-            pd.gph = gph; pd.first = j == 0; pd.last = j == nchk - 1;
-            pd.last_item = pd.last && t == ntile - 1;
-            have = true;
           }
         }
       }
-      if (have) issue_out(pd);
+    }
+  } else if (warp == kOutWarp) {
+    // ------------------------------------------------------------------ MMA issuer 2 (one thread): output MMAs
+    if (lane == 0) {
+      long long* trbuf = (p.trace != nullptr && blockIdx.x == 0) ? p.trace + MODE * 2048 + 1536 : nullptr;
+      int trn = 0;
+      constexpr uint32_t kHi = ptx::smem_desc_hi_sw128(1024);
+      const uint32_t idesc_o = ptx::make_idesc_bf16_f32(QT, HS, 0, 1);
+      const uint32_t acc_odd = tmem_base + (dual ? kAcc1 : kAcc0);
+      int it = 0, u = 0, g = 0;
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
+        const int st = p.stages == 2 ? (it & 1) : 0;
+        const uint32_t sq = ptx::smem_u32(smem + st * p.stage_bytes);
+        const uint32_t sk = sq + p.tile_bytes, sdo = sk + 2 * p.tile_bytes;
+        // B operands (MN-major, 16 rows = 2048 B per k-step): MODE 0 K | MODE 1 dO and Q
+        const uint32_t o0 = ptx::smem_desc_lo(MODE == 0 ? sk : sdo, 64 * 128), o1 = ptx::smem_desc_lo(sq, 64 * 128);
+        for (int t = 0; t < ntile; ++t, ++u) {
+          for (int j = 0; j < nchk; ++j, ++g) {
+            const int slot = g & 1;
+            const uint32_t gph = (static_cast<uint32_t>(g) >> 1) & 1u;
+            const int col0 = j * W, nk = min(W, p.TP - col0) >> 4;
+            const uint32_t tS = tmem_base + static_cast<uint32_t>(slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
+            const uint32_t b0 = o0 + static_cast<uint32_t>(col0 * 8), b1 = o1 + static_cast<uint32_t>(col0 * 8);
+            const uint32_t keep = j == 0 ? 0u : 1u;                    // first chunk of a unit overwrites the accumulators
+            // bf16 operand of k-step k: columns 8k.. of the region for the first group's k-steps, shifted by hc/2 for
+            // the second group's (it packs in place from column hc on)
+            const int kh = bwd_split(nk << 4) >> 4;
+            const uint32_t sh = static_cast<uint32_t>(kh * 8);
+            VB_TR(4);
+            ptx::mbar_wait(&ew_done[2 * slot], gph);
+            VB_TR(5);
+            if (j == 0) ptx::mbar_wait(acc_free, (static_cast<uint32_t>(u) & 1u) ^ 1u);
+            ptx::tc_fence_after();
+            // Back-to-back MMAs into ONE accumulator serialise on its latency (~114 clk each, measured); two
+            // independent accumulators interleaved run at ~55 clk each.  MODE 0 therefore splits dQ over two
+            // accumulators by k-step parity (summed in the drain); MODE 1 alternates dV and dK.
+            const uint32_t keep1 = dual ? keep : 1u;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+              if (k < nk) {
+                if (k == kh) {
+                  ptx::mbar_wait(&ew_done[2 * slot + 1], gph);
+                  ptx::tc_fence_after();
+                }
+                const uint32_t ao = static_cast<uint32_t>(k * 8) + (k >= kh ? sh : 0u);
+                if (MODE == 0) {
+                  ptx::umma_f16_ts_lh((k & 1) ? acc_odd : tmem_base + kAcc0, tS + ao,               // dQ(k parity) += dS K
+                                      b0 + static_cast<uint32_t>(k * 128), kHi, idesc_o, k == 0 ? keep : (k == 1 ? keep1 : 1u));
+                } else {
+                  ptx::umma_f16_ts_lh(tmem_base + kAcc0, tS + ao, b0 + static_cast<uint32_t>(k * 128), kHi, idesc_o,
+                                      k == 0 ? keep : 1u);                                         // dV += P^T dO
+                  ptx::umma_f16_ts_lh(tmem_base + kAcc1, tP + ao, b1 + static_cast<uint32_t>(k * 128), kHi, idesc_o,
+                                      k == 0 ? keep : 1u);                                         // dK += dS^T Q
+                }
+              }
+            }
+            if (nk <= kh) ptx::mbar_wait(&ew_done[2 * slot + 1], gph);   // one-k-step chunk: keep the barrier's phase in step
+            ptx::umma_commit(&slot_free[slot]);
+            VB_TR(6);
+            if (j == nchk - 1) {
+              ptx::umma_commit(acc_full);
+              if (t == ntile - 1) ptx::umma_commit(&kv_empty[st]);
+            }
+          }
+        }
+      }
     }
   } else {
     // ------------------------------------------------------------------ element-wise warps: one thread per row
     const int q = warp & 3;                      // tensor-memory lane quarter
     const int grp = (warp - 2) >> 2;             // slot / chunk parity owned by this warp; half of the drain columns
     const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    const uint32_t tS = lane_base + static_cast<uint32_t>(grp * 2 * W), tP = tS + static_cast<uint32_t>(W);
     const float sl2 = p.scale_log2, scale = p.scale;
     const int my_items = blockIdx.x < p.items ? (p.items - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
     const int total_units = my_items * ntile;
@@ -555,27 +597,23 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         bf16* grow = dqkv + (static_cast<int64_t>(b) * p.T + row) * (3 * static_cast<int64_t>(E)) + h * HS + grp * 32;
         // MODE 0: dQ -> section 0.  MODE 1: accumulator 0 = dV -> section 2, accumulator 1 = dK -> section 1.
         bf16* d0 = grow + (MODE == 0 ? 0 : 2) * static_cast<int64_t>(E);
+        auto put = [&](bf16* dst, const uint32_t (&r)[32]) {     // my 32 columns = 64 contiguous bytes of the row
+          uint32_t w[16];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          uint4 v;
-          v.x = pack_bf16x2(__uint_as_float(r0[8 * j + 0]), __uint_as_float(r0[8 * j + 1]));
-          v.y = pack_bf16x2(__uint_as_float(r0[8 * j + 2]), __uint_as_float(r0[8 * j + 3]));
-          v.z = pack_bf16x2(__uint_as_float(r0[8 * j + 4]), __uint_as_float(r0[8 * j + 5]));
-          v.w = pack_bf16x2(__uint_as_float(r0[8 * j + 6]), __uint_as_float(r0[8 * j + 7]));
-          *reinterpret_cast<uint4*>(d0 + j * 8) = v;
-        }
-        if (MODE == 1) {
-          bf16* d1 = grow + static_cast<int64_t>(E);
+          for (int j = 0; j < 16; ++j) w[j] = pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+          if (p.st256) {
+            const uint32_t lo[8] = {w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]};
+            const uint32_t hi[8] = {w[8], w[9], w[10], w[11], w[12], w[13], w[14], w[15]};
+            ptx::stg256(dst, lo);
+            ptx::stg256(dst + 16, hi);
+          } else {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 v;
-            v.x = pack_bf16x2(__uint_as_float(r1[8 * j + 0]), __uint_as_float(r1[8 * j + 1]));
-            v.y = pack_bf16x2(__uint_as_float(r1[8 * j + 2]), __uint_as_float(r1[8 * j + 3]));
-            v.z = pack_bf16x2(__uint_as_float(r1[8 * j + 4]), __uint_as_float(r1[8 * j + 5]));
-            v.w = pack_bf16x2(__uint_as_float(r1[8 * j + 6]), __uint_as_float(r1[8 * j + 7]));
-            *reinterpret_cast<uint4*>(d1 + j * 8) = v;
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<uint4*>(dst + j * 8) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
           }
-        }
+        };
+        put(d0, r0);
+        if (MODE == 1) put(grow + static_cast<int64_t>(E), r1);
       }
     };
 
@@ -584,30 +622,40 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       const int st = p.stages == 2 ? (it & 1) : 0;
       const uint32_t ph = p.stages == 2 ? ((it >> 1) & 1) : (it & 1);
       const float* stat = reinterpret_cast<const float*>(smem + st * p.stage_bytes + 4 * p.tile_bytes);
+      const uint32_t stat_s = ptx::smem_u32(stat);
       ptx::mbar_wait(&st_full[st], ph);
       for (int t = 0; t < ntile; ++t, ++u) {
         const int row = t * QT + q * 32 + lane;  // query (MODE 0) or key (MODE 1) index of this thread
         float lse2r = 0.f, dscr = 0.f;
         if (MODE == 0) { lse2r = stat[row]; dscr = stat[256 + row]; }
         for (int j = 0; j < nchk; ++j, ++g) {
-          if ((g & 1) != grp) continue;
+          // BOTH groups work on every chunk: group 0 takes columns [0, hc), group 1 [hc, wc).  That halves the
+          // S/dP -> operand latency of a chunk, which is what bounds the slot cycle (S/dP MMAs -> element-wise ->
+          // output MMAs -> slot free).  Each group packs its bf16 results in place at the start of ITS OWN column
+          // range (ascending, so it only overwrites what it has already read); the output-MMA issuer knows the layout.
+          const int slot = g & 1;
           const int col0 = j * W, wc = min(W, p.TP - col0);
+          const int hc = bwd_split(wc);
+          const int cbeg = grp == 0 ? 0 : hc, cend = grp == 0 ? hc : wc;
+          const uint32_t tS = lane_base + static_cast<uint32_t>(slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
           VB_TR(10);
-          ptx::mbar_wait(&sd_full[grp], (static_cast<uint32_t>(g) >> 1) & 1u);
+          ptx::mbar_wait(&sd_full[slot], (static_cast<uint32_t>(g) >> 1) & 1u);
           ptx::tc_fence_after();
           VB_TR(11);
-          int c0 = 0;
-          if (p.dbg & 1) c0 = wc;                 // experiment: no element-wise work
-          for (; c0 + 32 <= wc; c0 += 32)
-            bwd_piece<MODE, 32>(tS, tP, c0, col0 + c0, p.T, sl2, scale, lse2r, dscr, stat);
-          if (c0 < wc) bwd_piece<MODE, 16>(tS, tP, c0, col0 + c0, p.T, sl2, scale, lse2r, dscr, stat);
+          int c0 = cbeg;
+          if (p.dbg & 1) c0 = cend;               // experiment: no element-wise work
+          for (; c0 + 32 <= cend; c0 += 32)
+            bwd_piece<MODE, 32>(tS, tP, c0, cbeg + ((c0 - cbeg) >> 1), col0 + c0, p.T, sl2, scale, lse2r, dscr, stat_s);
+          if (c0 < cend)
+            bwd_piece<MODE, 16>(tS, tP, c0, cbeg + ((c0 - cbeg) >> 1), col0 + c0, p.T, sl2, scale, lse2r, dscr, stat_s);
           ptx::tmem_st_wait();
           ptx::tc_fence_before();
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(&ew_done[grp]);
+          if (lane == 0) ptx::mbar_arrive(&ew_done[2 * slot + grp]);
           VB_TR(12);
-          // accumulators of every unit whose last chunk is <= g are (about to be) complete: take my half
-          while (next_drain < total_units && (next_drain + 1) * nchk - 1 <= g) drain(next_drain++);
+          // Drain a unit's accumulators one chunk LATE (after the first chunk of the next unit): right after the unit's
+          // own last chunk its output MMAs have only just been issued and both groups would sit on acc_full.
+          while (next_drain < total_units && (next_drain + 1) * nchk - 1 < g) drain(next_drain++);
         }
       }
     }
@@ -647,6 +695,7 @@ int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H,
   FwdParams p;
   p.T = T; p.TP = (T + 15) / 16 * 16; p.H = H; p.items = B * H;
   p.scale_log2 = scale * kLog2e;
+  p.st256 = (reinterpret_cast<uintptr_t>(out) & 31u) == 0 && (E * 2) % 32 == 0;
   ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * static_cast<double>(T) * hs, 1, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
   VB_CHECK_CUDA(launch_pdl(attn_tc_fwd_kernel, dim3(grid), dim3(kThreads), SMEM_BYTES, stream, 1, tm, out, lse, p));
@@ -672,6 +721,7 @@ int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const f
   const int pad = 32768 - p.tile_bytes;      // an A tile of rows [128,256) may over-read past a TP-row operand
   p.stages = (2 * p.stage_bytes + pad + 256 + 1024 <= 227 * 1024) ? 2 : 1;
   p.scale = scale; p.scale_log2 = scale * kLog2e;
+  p.st256 = (reinterpret_cast<uintptr_t>(dqkv) & 31u) == 0 && (3 * E * 2) % 32 == 0;
   static const int dbg = getenv("VITB200_ATTN_DBG") ? atoi(getenv("VITB200_ATTN_DBG")) : 0;
   p.dbg = dbg;
   p.trace = getenv("VITB200_ATTN_TRACE") ? reinterpret_cast<long long*>(strtoull(getenv("VITB200_ATTN_TRACE"), nullptr, 0)) : nullptr;
