@@ -122,6 +122,32 @@ def cpu_sample(args, batch, steps, warmup):
     return batch / sec, sec, host, torch.get_num_threads()
 
 
+def vit_c_sample(E, H, P, img):
+    """The reference's C prototype (csrc/vit.c, built by oracle/Makefile into oracle/_ref/): seconds per vit_forward
+    = patch embedding + 2 attention blocks, FORWARD ONLY, different math from the PyTorch path -> reported beside
+    the images/s figure, never converted into one."""
+    import subprocess
+    out = {}
+    for tag, exe in (("serial", "vit_c_time"), ("omp", "vit_c_time_omp")):
+        path = os.path.join(ROOT, "oracle", "_ref", exe)
+        if not os.path.exists(path):
+            out[tag] = None
+            continue
+        for dims in ((4, 4), (E, H)):
+            if tag == "serial" and dims[0] > 64:
+                continue  # the serial build needs ~10x longer at D=768; the OMP build is timed there
+            try:
+                r = subprocess.run([path, str(img), "3", str(P), str(dims[1]), str(dims[0]), "2"],
+                                   capture_output=True, text=True, timeout=120)
+                j = json.loads(r.stderr.strip().splitlines()[-1])
+                out[f"{tag}_D{dims[0]}_H{dims[1]}"] = {"seconds_per_forward": j["seconds_per_forward_best"],
+                                                         "threads": j["threads"]}
+            except Exception as e:  # a baseline curiosity must never fail the bench
+                out[f"{tag}_D{dims[0]}_H{dims[1]}"] = {"error": str(e)[:120]}
+    out["what"] = "csrc/vit.c vit_forward: patch embed + 2 attention blocks, forward only, one image; not the training step"
+    return out
+
+
 def run_reference(args):
     """`--impl reference`: the reference's own CPU implementation of the step (its PyTorch path restated in
     oracle/, since /root/reference is a Python tree that does not travel to the GPU box), all host threads."""
@@ -275,12 +301,13 @@ def run_b200(args):
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         torch.cuda.synchronize()
-        b = 4
-        ips, sec, host, threads = cpu_sample(args, b, 2, 1)
+        b, ksteps = 16, 8
+        ips, sec, host, threads = cpu_sample(args, b, ksteps, 1)
         cpu = {"value": ips, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": f"2 steps x {b} images after 1 warm-up ({sec:.2f} s/step), oracle/cpu_step.py (restated "
-                         f"reference PyTorch path, fwd+CE+bwd+AdamW, dropout on), {host['cpu_model']}, "
-                         f"os.cpu_count={host['os_cpu_count']}"}
+               "sample": f"{ksteps} steps x {b} images after 1 warm-up ({sec:.2f} s/step), oracle/cpu_step.py "
+                         f"(restated reference PyTorch path, fwd+CE+bwd+AdamW, dropout on), {host['cpu_model']}, "
+                         f"os.cpu_count={host['os_cpu_count']}",
+               "vit_c": vit_c_sample(*[MODELS[args.model][i] for i in (0, 1, 3, 4)])}
 
     E, H, L, P, img = MODELS[args.model]
     line = {

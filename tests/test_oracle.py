@@ -70,3 +70,21 @@ def test_oracle_adamw_matches_torch():
         opt.step()
         ref_vit.adamw_step(q, gr, m, v, step)
         assert torch.allclose(q, p.detach(), rtol=1e-6, atol=1e-7)
+
+
+def test_vit_c_baseline_known_answer():
+    """The C prototype timed as a CPU baseline (oracle/_ref/vit_c_time, built from the reference's csrc/vit.c where
+    it lies) reproduces the reference's own known-answer notebook (tests/multihead-attention-test.ipynb cell 0:
+    seed 69, 4x4x1 image of ones, P=2, D=4, 2 heads -> CLS+patch embeddings 5x4)."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "vit_c_time")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/vit_c_time not built (reference sources absent)")
+    out = subprocess.run([exe, "kat"], capture_output=True, text=True, timeout=60).stdout.splitlines()
+    i = next(k for k, ln in enumerate(out) if ln.startswith("Matrix: CLS+Patch Embeddings"))
+    got = torch.tensor([[float(v) for v in out[i + 1 + r].split()] for r in range(5)])
+    want = torch.tensor([[0.7825, 1.0174, 1.6778, 1.2251], [3.3223, 2.8748, 3.0050, 3.2986],
+                         [3.3452, 2.4302, 3.0276, 2.3968], [3.0843, 3.1493, 2.6917, 3.3506],
+                         [3.5323, 3.3369, 2.9087, 2.9229]])
+    assert torch.allclose(got, want, atol=1.5e-4)
