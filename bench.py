@@ -265,6 +265,16 @@ def run_b200(args):
                "api": "train_dp.DPTrainer.step_host(pinned images fp32, labels): H2D on a copy stream "
                       "(double-buffered) + loss D2H every step"}
 
+        # the same step fed with raw uint8 pixels (device-side input pipeline): 1 byte per pixel H2D
+        x8 = [(x * 255).to(torch.uint8).pin_memory() for x in xh]
+        idx8 = []
+        u8_ms, _ = timed(lambda i: idx8.append(tr.step_host_u8(x8[i % n_host], yh[i % n_host])), args.steps, 2)
+        e2e["u8_input"] = {"value": gb / (u8_ms / args.steps * 1e-3), "unit": UNIT, "ms_per_step": u8_ms / args.steps,
+                           "h2d_bytes_per_step": x8[0].numel() + args.batch * 8, "last_loss": tr.read_loss(idx8[-1]),
+                           "api": "DPTrainer.step_host_u8(pinned uint8 NCHW pixels, labels): /255 fused into the "
+                                  "patch gather"}
+        del x8
+
     # ---- live per-kernel-class timing (CUDA events on the launching stream) over 2 more steps: `roofline`
     pk = peaks()
     barrier()

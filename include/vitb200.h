@@ -125,6 +125,12 @@ int vitb200_attn_probs(const float* qkv, float* probs, int B, int T, int H, int 
  * row b*N + gy*(Wi/P) + gx, column c*P*P + ph*P + pw. */
 int vitb200_im2col(const float* x, void* A, int out_dtype, int B, int C, int Hi, int Wi, int P, int Kpad,
                    void* stream);
+/* The same gather from uint8 pixels with the ToTensor scaling (uint8 / 255 in fp32, train.py:151-155) fused in, so
+ * the host ships 1 byte per pixel instead of 4.  layout 0: x u8 [B,C,Hi,Wi]; layout 1: x u8 [B,Hi,Wi,C]. */
+#define VITB200_U8_NCHW 0
+#define VITB200_U8_NHWC 1
+int vitb200_im2col_u8(const uint8_t* x, int layout, void* A, int out_dtype, int B, int C, int Hi, int Wi, int P,
+                      int Kpad, void* stream);
 /* out[n] += sum_m in[m,n] (bias gradients). */
 int vitb200_colsum(const void* in, int in_dtype, int64_t ld, float* out, int M, int N, void* stream);
 /* nn.CrossEntropyLoss() mean + gradient (train.py:81,93): dlogits = grad_scale * d(mean loss)/dlogits, may be NULL. */
@@ -177,6 +183,10 @@ typedef struct { float *w, *bias, *cls, *pos; } vitb200_embed_grads;
 int64_t vitb200_embed_act_bytes(const vitb200_dims* d);
 int vitb200_embed_fwd(const vitb200_dims* d, const vitb200_embed_params* p, const float* images, float* x_out,
                       void* acts, void* stream);
+/* Same stage fed with uint8 pixels (the input pipeline of train.py:91,151-162 moved onto the device):
+ * identical results to vitb200_embed_fwd on images_u8 / 255. */
+int vitb200_embed_fwd_u8(const vitb200_dims* d, const vitb200_embed_params* p, const uint8_t* images_u8, int layout,
+                         float* x_out, void* acts, void* stream);
 /* g: fp32 [B,T,E] gradient of the embedding output; scratch >= vitb200_embed_act_bytes. Grads are ACCUMULATED. */
 int vitb200_embed_bwd(const vitb200_dims* d, const vitb200_embed_grads* gr, const float* g, const void* acts,
                       void* scratch, void* stream);

@@ -270,6 +270,28 @@ def test_im2col_bit_exact_layout(lib, B, Cc, Hi, Wi, P):
         assert torch.equal(Ab.cpu(), ref.bfloat16())
 
 
+@pytest.mark.parametrize("B,Cc,Hi,Wi,P", [(2, 3, 32, 48, 16), (1, 1, 40, 40, 10), (2, 3, 30, 30, 14), (3, 3, 224, 224, 16)])
+@pytest.mark.parametrize("layout", [0, 1])
+def test_im2col_u8_bit_exact(lib, B, Cc, Hi, Wi, P, layout):
+    """uint8 pixels with the ToTensor /255 fused in == the fp32 gather of x.float()/255, bit for bit,
+    from (B,C,H,W) and (B,H,W,C) pixel orders; includes 0 and 255."""
+    C = _C()
+    gen = torch.Generator().manual_seed(11)
+    x8 = torch.randint(0, 256, (B, Cc, Hi, Wi), dtype=torch.uint8, generator=gen)
+    x8[0, 0, 0, 0], x8[0, 0, 0, 1] = 0, 255
+    N, K = (Hi // P) * (Wi // P), Cc * P * P
+    ref = ref_vit.im2col(x8.float() / 255.0, P).reshape(B * N, K)
+    src = (x8.permute(0, 2, 3, 1).contiguous() if layout == 1 else x8).to(DEV)
+    A = torch.empty(B * N, K, device=DEV)
+    C.check(lib.vitb200_im2col_u8(src.data_ptr(), layout, A.data_ptr(), C.F32, B, Cc, Hi, Wi, P, K, C.stream_ptr()))
+    assert torch.equal(A.cpu(), ref)
+    if K % 8 == 0:
+        Ab = torch.empty(B * N, K, device=DEV, dtype=torch.bfloat16)
+        C.check(lib.vitb200_im2col_u8(src.data_ptr(), layout, Ab.data_ptr(), C.BF16, B, Cc, Hi, Wi, P, K, C.stream_ptr()))
+        assert torch.equal(Ab.cpu(), ref.bfloat16())
+    assert lib.vitb200_im2col_u8(src.data_ptr(), 2, A.data_ptr(), C.F32, B, Cc, Hi, Wi, P, K, C.stream_ptr()) != 0
+
+
 # ------------------------------------------------------------------------------------------------ misc bandwidth kernels
 def test_colsum_cross_entropy_cast(lib):
     C = _C()

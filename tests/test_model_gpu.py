@@ -56,6 +56,25 @@ def test_fp32_model_matches_reference_fixture(lib, name):
         assert rel_err(mine[k], ref) < 1e-4, k
 
 
+@pytest.mark.parametrize("name", ["tiny", "c1"])
+def test_uint8_images_equal_scaled_float_images(lib, name):
+    """Raw uint8 pixels (B,C,H,W) fed to the module give exactly the logits and gradients of images_u8.float()/255
+    (the device-side input pipeline of SURVEY 8f-1), and those match the reference fixture."""
+    g = load_golden(name)
+    out = []
+    for as_u8 in (True, False):
+        m = _build(g["config"]).eval()
+        m.load_state_dict(g["state_dict"])
+        x = g["images_u8"].to(DEV) if as_u8 else (g["images_u8"].float() / 255.0).to(DEV)
+        logits = m(x)
+        torch.nn.CrossEntropyLoss()(logits, g["labels"].to(DEV)).backward()
+        out.append((logits.detach(), m.emdeddings.sequence[0].weight.grad.clone(), m.emdeddings.pos_embd.grad.clone()))
+    assert torch.equal(out[0][0], out[1][0])
+    assert rel_err(out[0][0], g["logits"]) < 1e-4
+    assert rel_err(out[0][1], out[1][1]) < 1e-5  # split-K atomics: order-dependent rounding only
+    assert rel_err(out[0][2], out[1][2]) < 1e-5
+
+
 def _synthetic_case(E, H, L, B, P, img, classes, C=3, seed=0):
     N = (img // P) ** 2
     cfg = ref_vit.Cfg(C, classes, N, E, P, H, L, B)

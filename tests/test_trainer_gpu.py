@@ -94,6 +94,26 @@ def test_trainer_step_host_matches_step(lib):
         tr_a.step(x[:2].cuda(), y[:2].cuda())
 
 
+@pytest.mark.parametrize("layout", [0, 1])
+def test_trainer_step_host_u8_matches_float_step(lib, layout):
+    """step_host_u8 (1 byte per pixel over PCIe, /255 fused into the patch gather) follows the same trajectory as
+    step() on images_u8.float()/255."""
+    tr_a, cfg, sd, x, y = _make(torch.float32)
+    tr_b, *_ = _make(torch.float32)
+    x8 = (x * 255).round().clamp(0, 255).to(torch.uint8)
+    xf = (x8.float() / 255.0).cuda()
+    xh = (x8.permute(0, 2, 3, 1).contiguous() if layout == 1 else x8).pin_memory()
+    yh = y.pin_memory()
+    for _ in range(3):
+        tr_a.step(xf, y.cuda())
+        li = tr_b.step_host_u8(xh, yh, layout=layout)
+    assert abs(tr_b.read_loss(li) - tr_a.loss.item()) < 1e-5
+    diff = (tr_a.p - tr_b.p).abs()
+    assert (diff > 1e-6).float().mean().item() < 1e-3
+    with pytest.raises(RuntimeError, match="uint8 pixels"):
+        tr_b.step_host_u8(xh[:1], yh)
+
+
 # ---------------------------------------------------------------------------------------------- data parallel
 def _dp_worker(rank, world, port, out):
     """One rank of a 2-process data-parallel step.  Both ranks share cuda:0 (gloo moves the buckets), so the real

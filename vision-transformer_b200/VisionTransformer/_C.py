@@ -132,6 +132,8 @@ def _declare(L):
         "vitb200_adamw_flat": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, AdamWHyper, c_void_p],
         "vitb200_adamw_multi": [c_void_p] * 8 + [c_int, AdamWHyper, c_void_p],
         "vitb200_embed_fwd": [P(Dims), P(EmbedParams), c_void_p, c_void_p, c_void_p, c_void_p],
+        "vitb200_embed_fwd_u8": [P(Dims), P(EmbedParams), c_void_p, c_int, c_void_p, c_void_p, c_void_p],
+        "vitb200_im2col_u8": [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
         "vitb200_embed_bwd": [P(Dims), P(EmbedGrads), c_void_p, c_void_p, c_void_p, c_void_p],
         "vitb200_block_fwd": [P(Dims), c_int, P(BlockParams), c_void_p, c_void_p, c_void_p, c_void_p],
         "vitb200_block_bwd": [P(Dims), c_int, P(BlockParams), P(BlockGrads), c_void_p, c_void_p, c_void_p, c_void_p,
@@ -156,7 +158,7 @@ EXPORTS = (
     "vitb200_prof_begin", "vitb200_prof_end", "vitb200_abi_sizeof", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
     "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
     "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
-    "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_bwd",
+    "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_fwd_u8", "vitb200_im2col_u8", "vitb200_embed_bwd",
     "vitb200_block_act_bytes", "vitb200_block_scratch_bytes", "vitb200_block_fwd", "vitb200_block_bwd",
     "vitb200_head_act_bytes", "vitb200_head_fwd", "vitb200_head_bwd",
 )

@@ -44,8 +44,14 @@ class Plan:
             setattr(s, f, None if t is None else t.data_ptr())
         return s
 
-    def embed_fwd(self, d, params, images, x_out, acts):
+    def embed_fwd(self, d, params, images, x_out, acts, u8_layout=0):
         p = self._fill(_C.EmbedParams, _C.EMBED_FIELDS_P, params)
+        if images.dtype == torch.uint8:  # raw pixels, layout 0 = (B,C,H,W), 1 = (B,H,W,C); /255 fused on the device
+            _C.check(_C.lib().vitb200_embed_fwd_u8(ctypes.byref(d), ctypes.byref(p), images.data_ptr(), int(u8_layout),
+                                                   x_out.data_ptr(), acts.data_ptr(), _C.stream_ptr()))
+            return
+        if images.dtype != torch.float32:
+            raise RuntimeError(f"images must be float32 or uint8, got {images.dtype}")
         _C.check(_C.lib().vitb200_embed_fwd(ctypes.byref(d), ctypes.byref(p), images.data_ptr(), x_out.data_ptr(),
                                             acts.data_ptr(), _C.stream_ptr()))
 

@@ -45,6 +45,9 @@ def _check_images(x, C, batch_size):
         raise RuntimeError(f"Sizes of tensors must match except in dimension 1. Expected size {x.shape[0]} but got "
                            f"size {batch_size} for tensor number 1 in the list (cls_tkn_embd is per batch slot: "
                            f"the input batch must equal config.batch_size)")
+    if x.dtype == torch.uint8:
+        # raw pixels (B,C,H,W): the ToTensor /255 (train.py:151-155) is fused into the patch gather on the device
+        return x.contiguous()
     return x.contiguous().float()
 
 

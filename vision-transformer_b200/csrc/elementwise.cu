@@ -48,6 +48,53 @@ __global__ void im2col_kernel(const float* __restrict__ x, OutT* __restrict__ A,
   }
 }
 
+// uint8 pixels -> A with the ToTensor scaling fused in (reference train.py:151-155: ToTensor = uint8 / 255 in fp32,
+// IEEE division).  NHWC = 0: x u8 [B,C,Hi,Wi] (what ToTensor's permute yields); NHWC = 1: x u8 [B,Hi,Wi,C] (decoder
+// order).  VEC4 (NCHW only) moves 4 pixels of one patch row per thread.
+template <typename OutT, bool NHWC, bool VEC4>
+__global__ void im2col_u8_kernel(const uint8_t* __restrict__ x, OutT* __restrict__ A, int B, int C, int Hi, int Wi,
+                                 int P, int gh, int gw, int K, int Kpad) {
+  const int kq = VEC4 ? Kpad / 4 : Kpad;
+  const int64_t total = static_cast<int64_t>(B) * gh * gw * kq;
+  for (int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int kk = static_cast<int>(idx % kq);
+    const int64_t row = idx / kq;
+    const int gx = static_cast<int>(row % gw);
+    const int gy = static_cast<int>((row / gw) % gh);
+    const int b = static_cast<int>(row / (static_cast<int64_t>(gw) * gh));
+    if (VEC4) {
+      const int k = kk * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (k < K) {
+        const int c = k / (P * P), rem = k - c * P * P, ph = rem / P, pw = rem - ph * P;
+        const uchar4 u = __ldg(reinterpret_cast<const uchar4*>(
+            x + ((static_cast<int64_t>(b) * C + c) * Hi + gy * P + ph) * Wi + gx * P + pw));
+        v = make_float4(__fdiv_rn(static_cast<float>(u.x), 255.f), __fdiv_rn(static_cast<float>(u.y), 255.f),
+                        __fdiv_rn(static_cast<float>(u.z), 255.f), __fdiv_rn(static_cast<float>(u.w), 255.f));
+      }
+      if constexpr (sizeof(OutT) == 2) {
+        uint2 o;
+        o.x = pack_bf16x2(v.x, v.y);
+        o.y = pack_bf16x2(v.z, v.w);
+        *reinterpret_cast<uint2*>(A + row * Kpad + k) = o;
+      } else {
+        *reinterpret_cast<float4*>(A + row * Kpad + k) = v;
+      }
+    } else {
+      float v = 0.f;
+      if (kk < K) {
+        const int c = kk / (P * P), rem = kk - c * P * P, ph = rem / P, pw = rem - ph * P;
+        const int64_t y = gy * P + ph, xx = gx * P + pw;
+        const int64_t off = NHWC ? ((static_cast<int64_t>(b) * Hi + y) * Wi + xx) * C + c
+                                 : ((static_cast<int64_t>(b) * C + c) * Hi + y) * Wi + xx;
+        v = __fdiv_rn(static_cast<float>(__ldg(x + off)), 255.f);
+      }
+      A[row * Kpad + kk] = from_f32<OutT>(v);
+    }
+  }
+}
+
 // out[b, N, :] = cls[b, :] + pos[N, :]   (CLS appended LAST: reference vit.py:41-42)
 __global__ void cls_rows_kernel(const float* __restrict__ cls, const float* __restrict__ pos, float* __restrict__ out,
                                 int B, int T, int E) {
@@ -328,6 +375,32 @@ int im2col(const float* x, void* A, bool out_bf16, int B, int C, int Hi, int Wi,
     if (vec) im2col_kernel<float, true><<<grid, 256, 0, s>>>(x, static_cast<float*>(A), B, C, Hi, Wi, P, gh, gw, K, Kpad);
     else im2col_kernel<float, false><<<grid, 256, 0, s>>>(x, static_cast<float*>(A), B, C, Hi, Wi, P, gh, gw, K, Kpad);
   }
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int im2col_u8(const uint8_t* x, int nhwc, void* A, bool out_bf16, int B, int C, int Hi, int Wi, int P, int Kpad,
+              cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
+  const int gh = Hi / P, gw = Wi / P, K = C * P * P;
+  VB_REQUIRE(gh > 0 && gw > 0 && Kpad >= K, "im2col_u8: bad geometry");
+  VB_REQUIRE(nhwc == 0 || nhwc == 1, "im2col_u8: layout must be 0 (NCHW) or 1 (NHWC)");
+  const bool vec = !nhwc && (P % 4 == 0) && (Wi % 4 == 0) && (Kpad % 4 == 0) &&
+                   (reinterpret_cast<uintptr_t>(x) % 4 == 0) && aligned16(A);
+  const int64_t items = static_cast<int64_t>(B) * gh * gw * (vec ? Kpad / 4 : Kpad);
+  const int grid = grid_for(items, 256);
+#define VB_U8_LAUNCH(OUT, NHWC, VEC) \
+  im2col_u8_kernel<OUT, NHWC, VEC><<<grid, 256, 0, s>>>(x, static_cast<OUT*>(A), B, C, Hi, Wi, P, gh, gw, K, Kpad)
+  if (out_bf16) {
+    if (vec) VB_U8_LAUNCH(bf16, false, true);
+    else if (nhwc) VB_U8_LAUNCH(bf16, true, false);
+    else VB_U8_LAUNCH(bf16, false, false);
+  } else {
+    if (vec) VB_U8_LAUNCH(float, false, true);
+    else if (nhwc) VB_U8_LAUNCH(float, true, false);
+    else VB_U8_LAUNCH(float, false, false);
+  }
+#undef VB_U8_LAUNCH
   VB_CHECK_LAUNCH();
   return kOk;
 }

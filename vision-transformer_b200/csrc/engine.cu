@@ -168,8 +168,9 @@ int64_t vitb200_embed_act_bytes(const vitb200_dims* d) {
   return static_cast<int64_t>(align256(rows * g.Kpad * (g.lp ? 2 : 4)) + align256(rows * d->E * (g.lp ? 2 : 4)));
 }
 
-int vitb200_embed_fwd(const vitb200_dims* d, const vitb200_embed_params* p, const float* images, float* x_out,
-                      void* acts, void* stream) {
+// images_f32 XOR images_u8 (u8_layout: 0 NCHW, 1 NHWC; the ToTensor /255 is fused into the gather)
+static int embed_forward(const vitb200_dims* d, const vitb200_embed_params* p, const float* images,
+                         const uint8_t* images_u8, int u8_layout, float* x_out, void* acts, void* stream) {
   VB_PROPAGATE(check_dims(d));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const EmbedGeom g = embed_geom(d);
@@ -178,7 +179,8 @@ int vitb200_embed_fwd(const vitb200_dims* d, const vitb200_embed_params* p, cons
   VB_REQUIRE(!g.lp || p->w_lp != nullptr, "embed: bf16 weight copy missing");
   Carver c(acts);
   void* A = c.take(static_cast<size_t>(d->B) * g.N * g.Kpad * (g.lp ? 2 : 4));
-  VB_PROPAGATE(im2col(images, A, g.lp, d->B, d->C, d->Hi, d->Wi, d->P, g.Kpad, s));
+  if (images_u8) VB_PROPAGATE(im2col_u8(images_u8, u8_layout, A, g.lp, d->B, d->C, d->Hi, d->Wi, d->P, g.Kpad, s));
+  else VB_PROPAGATE(im2col(images, A, g.lp, d->B, d->C, d->Hi, d->Wi, d->P, g.Kpad, s));
   Lin l;
   l.M = d->B * g.N; l.N = d->E; l.K = g.K;
   l.A = A; l.lda = g.Kpad;
@@ -191,6 +193,18 @@ int vitb200_embed_fwd(const vitb200_dims* d, const vitb200_embed_params* p, cons
   l.out_f32 = true;
   VB_PROPAGATE(run_lin(g.lp, l, s));
   return cls_rows(p->cls, p->pos, x_out, d->B, d->T, d->E, s);
+}
+
+int vitb200_embed_fwd(const vitb200_dims* d, const vitb200_embed_params* p, const float* images, float* x_out,
+                      void* acts, void* stream) {
+  VB_REQUIRE(images != nullptr, "embed_fwd: images is NULL");
+  return embed_forward(d, p, images, nullptr, 0, x_out, acts, stream);
+}
+
+int vitb200_embed_fwd_u8(const vitb200_dims* d, const vitb200_embed_params* p, const uint8_t* images_u8, int layout,
+                         float* x_out, void* acts, void* stream) {
+  VB_REQUIRE(images_u8 != nullptr, "embed_fwd_u8: images is NULL");
+  return embed_forward(d, p, nullptr, images_u8, layout, x_out, acts, stream);
 }
 
 int vitb200_embed_bwd(const vitb200_dims* d, const vitb200_embed_grads* gr, const float* g_in, const void* acts,
@@ -443,6 +457,10 @@ int vitb200_attn_probs(const float* qkv, float* probs, int B, int T, int H, int 
 int vitb200_im2col(const float* x, void* A, int out_dtype, int B, int C, int Hi, int Wi, int P, int Kpad,
                    void* stream) {
   return im2col(x, A, out_dtype == VITB200_BF16, B, C, Hi, Wi, P, Kpad, static_cast<cudaStream_t>(stream));
+}
+int vitb200_im2col_u8(const uint8_t* x, int layout, void* A, int out_dtype, int B, int C, int Hi, int Wi, int P,
+                      int Kpad, void* stream) {
+  return im2col_u8(x, layout, A, out_dtype == VITB200_BF16, B, C, Hi, Wi, P, Kpad, static_cast<cudaStream_t>(stream));
 }
 int vitb200_colsum(const void* in, int in_dtype, int64_t ld, float* out, int M, int N, void* stream) {
   return colsum(in, in_dtype == VITB200_BF16, ld, out, M, N, static_cast<cudaStream_t>(stream));

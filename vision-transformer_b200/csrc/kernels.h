@@ -57,6 +57,8 @@ int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const f
 
 // bandwidth kernels
 int im2col(const float* x, void* A, bool out_bf16, int B, int C, int Hi, int Wi, int P, int Kpad, cudaStream_t s);
+int im2col_u8(const uint8_t* x, int nhwc, void* A, bool out_bf16, int B, int C, int Hi, int Wi, int P, int Kpad,
+              cudaStream_t s);
 int cls_rows(const float* cls, const float* pos, float* out, int B, int T, int E, cudaStream_t s);
 int embed_bwd_reduce(const float* g, float* dpos, float* dcls, void* dY, bool dy_bf16, int B, int T, int E,
                      cudaStream_t s);

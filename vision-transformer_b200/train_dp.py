@@ -187,6 +187,7 @@ class DPTrainer:
         self.reducer = BucketReducer(self.g, self.buckets, self.pg, self.world)
         self._in = [(torch.empty(self.B, self.C, self.img, self.img, dtype=torch.float32, device=dev),
                      torch.empty(self.B, dtype=torch.int64, device=dev)) for _ in range(2)]
+        self._in_u8 = None  # uint8 staging buffers, allocated on the first step_host_u8
         self._in_ready = [torch.cuda.Event() for _ in range(2)]
         self._in_free = [torch.cuda.Event() for _ in range(2)]
         self._slot = 0
@@ -285,9 +286,9 @@ class DPTrainer:
         seed = (self.seed * 0x9E3779B97F4A7C15 + self.step_no * 0xD1B54A32D192ED03) & 0xFFFFFFFFFFFFFFFF
         return self.plan.dims(self.dropout_p if train else 0.0, seed)
 
-    def forward(self, images, d):
+    def forward(self, images, d, u8_layout=0):
         pl = self.plan
-        pl.embed_fwd(d, self.embed_p, images, self.xs[0], self.emb_acts)
+        pl.embed_fwd(d, self.embed_p, images, self.xs[0], self.emb_acts, u8_layout)
         for i in range(self.L):
             pl.block_fwd(d, i, self.block_p[i], self.xs[i], self.xs[i + 1], self.blk_acts[i])
         pl.head_fwd(d, self.head_p, self.xs[self.L], self.logits, self.head_acts)
@@ -349,6 +350,35 @@ class DPTrainer:
         self.forward(x, d)
         self.backward(y, d)
         self._in_free[k].record(cur)  # the labels are read by the loss kernel at the top of backward
+        self.optimizer_step()
+        li = (self.step_no - 1) % self.loss_host.numel()
+        self.loss_host[li:li + 1].copy_(self.loss, non_blocking=True)
+        self._loss_ev[li].record(cur)
+        return li
+
+    def step_host_u8(self, images_host_u8, labels_host, layout=0):
+        """step_host fed with raw uint8 pixels: pinned (B,C,H,W) [layout 0] or (B,H,W,C) [layout 1]
+        uint8 -> one H2D of 1 byte per pixel, the ToTensor /255 (train.py:151-155) fused into the patch gather."""
+        if self._in_u8 is None:
+            self._in_u8 = [torch.empty(self.B * self.C * self.img * self.img, dtype=torch.uint8, device=self.dev)
+                           for _ in range(2)]
+        if images_host_u8.dtype != torch.uint8 or images_host_u8.numel() != self._in_u8[0].numel():
+            raise RuntimeError(f"expected {self._in_u8[0].numel()} uint8 pixels, got {images_host_u8.dtype} x "
+                               f"{images_host_u8.numel()}")
+        k = self._slot
+        self._slot ^= 1
+        x, y = self._in_u8[k], self._in[k][1]
+        cur = torch.cuda.current_stream(self.dev)
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self._in_free[k])
+            x.copy_(images_host_u8.reshape(-1), non_blocking=True)
+            y.copy_(labels_host, non_blocking=True)
+            self._in_ready[k].record(self.copy_stream)
+        cur.wait_event(self._in_ready[k])
+        d = self._dims(True)
+        self.forward(x, d, u8_layout=layout)
+        self.backward(y, d)
+        self._in_free[k].record(cur)
         self.optimizer_step()
         li = (self.step_no - 1) % self.loss_host.numel()
         self.loss_host[li:li + 1].copy_(self.loss, non_blocking=True)
