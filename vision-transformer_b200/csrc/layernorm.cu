@@ -74,6 +74,86 @@ ln_fwd_kernel(const float* __restrict__ x, const float* __restrict__ gamma, cons
   }
 }
 
+// Register-resident forward for E % 4 == 0, E <= 128 * VPL: each lane owns float4 chunks lane + 32k of its warp's
+// row, and the NEXT row's chunks are requested before the current row's statistics are reduced, so every warp keeps
+// two rows of loads in flight and shared memory is not touched.  Same two-pass arithmetic as ln_fwd_kernel.
+template <typename OutT, int VPL>
+__global__ void __launch_bounds__(LN_THREADS)
+ln_fwd_reg_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                  OutT* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int E,
+                  float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  const int nq = E >> 2;
+  const int stride = gridDim.x * nw;
+  pdl_wait();
+  pdl_trigger();
+  float4 gm[VPL], bt[VPL];
+#pragma unroll
+  for (int k = 0; k < VPL; ++k) {
+    const int i = lane + 32 * k;
+    gm[k] = i < nq ? __ldg(reinterpret_cast<const float4*>(gamma) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    bt[k] = i < nq ? __ldg(reinterpret_cast<const float4*>(beta) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  int m = blockIdx.x * nw + warp;
+  float4 cur[VPL], nxt[VPL];
+  if (m < M) {
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const int i = lane + 32 * k;
+      cur[k] = i < nq ? __ldcs(reinterpret_cast<const float4*>(x + static_cast<int64_t>(m) * E) + i)
+                      : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  const float inv_e = 1.f / static_cast<float>(E);
+  for (; m < M; m += stride) {
+    const int mn = m + stride;
+    if (mn < M) {
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) {
+        const int i = lane + 32 * k;
+        nxt[k] = i < nq ? __ldcs(reinterpret_cast<const float4*>(x + static_cast<int64_t>(mn) * E) + i)
+                        : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) s += (cur[k].x + cur[k].y) + (cur[k].z + cur[k].w);
+    const float mean = warp_sum(s) / static_cast<float>(E);
+    float sq = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      if (lane + 32 * k < nq) {
+        const float d0 = cur[k].x - mean, d1 = cur[k].y - mean, d2 = cur[k].z - mean, d3 = cur[k].w - mean;
+        sq = fmaf(d0, d0, sq); sq = fmaf(d1, d1, sq); sq = fmaf(d2, d2, sq); sq = fmaf(d3, d3, sq);
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(sq) * inv_e + eps);
+    if (lane == 0) {
+      if (mean_out) mean_out[m] = mean;
+      if (rstd_out) rstd_out[m] = rstd;
+    }
+    OutT* yr = y + static_cast<int64_t>(m) * E;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const int i = lane + 32 * k;
+      if (i < nq) {
+        const float o0 = (cur[k].x - mean) * rstd * gm[k].x + bt[k].x, o1 = (cur[k].y - mean) * rstd * gm[k].y + bt[k].y;
+        const float o2 = (cur[k].z - mean) * rstd * gm[k].z + bt[k].z, o3 = (cur[k].w - mean) * rstd * gm[k].w + bt[k].w;
+        if constexpr (sizeof(OutT) == 2) {
+          uint2 o;
+          o.x = pack_bf16x2(o0, o1);
+          o.y = pack_bf16x2(o2, o3);
+          reinterpret_cast<uint2*>(yr)[i] = o;
+        } else {
+          reinterpret_cast<float4*>(yr)[i] = make_float4(o0, o1, o2, o3);
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) cur[k] = nxt[k];
+  }
+}
+
 // dy: gradient w.r.t. the LN output (DyT).  g: fp32 residual-stream gradient, updated in place (g += dx) when
 // add_to_g != 0, overwritten (g = dx) otherwise.  dyn: optional down-cast copy of the new g multiplied by the
 // dropout factors of the layer that produced this LN's input.
@@ -438,6 +518,27 @@ int ln_grid(int M, int nw, int per_sm) {
 int ln_forward(const float* x, const float* gamma, const float* beta, void* y, bool y_bf16, float* mean,
                float* rstd, int M, int E, float eps, cudaStream_t stream) {
   VB_REQUIRE(M > 0 && E > 0, "ln_forward: empty input");
+  if ((E & 3) == 0 && E <= 128 * 12 && aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta) &&
+      M >= 4 * num_sms()) {
+    // register-resident rows, next row prefetched (the block LayerNorms; the [B, 4E] head LayerNorm stays below)
+    ProfScope prof(kProfLnFwd, static_cast<double>(M) * E * (4 + (y_bf16 ? 2 : 4)) + 8.0 * M, 1, stream);
+    const int vpl = ceil_div(E, 128);
+    const int per_sm = vpl <= 3 ? 4 : vpl <= 6 ? 2 : 1;  // CTAs resident per SM by register count
+    const int grid = ln_grid(M, LN_WARPS, per_sm);
+#define VB_LN_REG(V)                                                                                              \
+  case V:                                                                                                         \
+    if (y_bf16) VB_CHECK_CUDA(launch_pdl(ln_fwd_reg_kernel<bf16, V>, dim3(grid), dim3(LN_THREADS), 0, stream, 1, x, \
+                                         gamma, beta, static_cast<bf16*>(y), mean, rstd, M, E, eps));             \
+    else VB_CHECK_CUDA(launch_pdl(ln_fwd_reg_kernel<float, V>, dim3(grid), dim3(LN_THREADS), 0, stream, 1, x, gamma, \
+                                  beta, static_cast<float*>(y), mean, rstd, M, E, eps));                          \
+    break;
+    switch (vpl <= 3 ? 3 : vpl <= 6 ? 6 : vpl <= 8 ? 8 : 12) {
+      VB_LN_REG(3) VB_LN_REG(6) VB_LN_REG(8) VB_LN_REG(12)
+    }
+#undef VB_LN_REG
+    VB_CHECK_LAUNCH();
+    return kOk;
+  }
   const int nw = ln_warps(E, 1, 0);
   const size_t smem = static_cast<size_t>(nw) * E * sizeof(float);
   VB_REQUIRE(smem <= 200 * 1024, "ln_forward: row too long (E=%d)", E);
