@@ -95,3 +95,105 @@ def test_dropout_is_hard_coded_like_the_reference():
     assert m._drop() == pytest.approx(0.2)
     m.eval()
     assert m._drop() == 0.0
+
+
+# ---------------------------------------------------------------------------------------- checkpoint compatibility
+def test_checkpoint_parameter_lists_match_reference_and_package():
+    """reference_param_keys == the real reference's parameter order (its state_dict holds parameters only; fixture
+    written by the reference itself); packed_param_keys == this package's named_parameters()."""
+    from VisionTransformer import checkpoint
+    for name in ("tiny", "odd", "c1"):
+        g = load_golden(name)
+        c = g["config"]
+        assert checkpoint.reference_param_keys(c["num_blocks"], c["num_heads"]) == list(g["state_dict"].keys())
+        m = _model(g)
+        assert checkpoint.packed_param_keys(c["num_blocks"]) == [n for n, _ in m.named_parameters()]
+
+
+def test_optimizer_state_translation_follows_real_adamw():
+    """Run torch.optim.AdamW over the reference parameter list (per-head q/k/v) and over the packed list with the
+    same gradients; the translated state equals the other optimizer's state, resumes identically, and the
+    round trip is lossless (reference src/train.py:66,73,110)."""
+    from VisionTransformer import checkpoint
+    g = load_golden("tiny")
+    c = g["config"]
+    L, H, E = c["num_blocks"], c["num_heads"], c["embedding_size"]
+    hs = E // H
+    m = _model(g)
+    m.load_state_dict(g["state_dict"])
+    packed = [p.detach().clone().requires_grad_(True) for p in m.parameters()]
+    ref_keys = checkpoint.reference_param_keys(L, H)
+    ref = [g["state_dict"][k].detach().clone().requires_grad_(True) for k in ref_keys]
+    opt_p = torch.optim.AdamW(packed, lr=1e-2, weight_decay=1e-4)
+    opt_r = torch.optim.AdamW(ref, lr=1e-2, weight_decay=1e-4)
+    pk_keys = checkpoint.packed_param_keys(L)
+    gen = torch.Generator().manual_seed(3)
+
+    def set_grads():
+        for k, p in zip(pk_keys, packed):
+            p.grad = torch.randn(p.shape, generator=gen)
+        by_key = dict(zip(pk_keys, packed))
+        for k, r in zip(ref_keys, ref):
+            if "multi_head.heads." in k:
+                pk, r0 = checkpoint._head_rows(k, H, hs)
+                r.grad = by_key[pk].grad[r0:r0 + hs].clone()
+            else:
+                r.grad = by_key[k].grad.clone()
+
+    for _ in range(3):
+        set_grads()
+        opt_p.step()
+        opt_r.step()
+    to_packed = checkpoint.optimizer_state_to_packed(opt_r.state_dict(), H)
+    want = opt_p.state_dict()
+    assert to_packed["param_groups"][0]["params"] == want["param_groups"][0]["params"]
+    for j, st in want["state"].items():
+        assert float(to_packed["state"][j]["step"]) == float(st["step"]) == 3.0
+        assert torch.equal(to_packed["state"][j]["exp_avg"], st["exp_avg"]), pk_keys[j]
+        assert torch.equal(to_packed["state"][j]["exp_avg_sq"], st["exp_avg_sq"]), pk_keys[j]
+    back = checkpoint.optimizer_state_to_reference(to_packed, H)
+    rs = opt_r.state_dict()
+    assert set(back["state"]) == set(rs["state"])
+    for i, st in rs["state"].items():
+        assert torch.equal(back["state"][i]["exp_avg"], st["exp_avg"]), ref_keys[i]
+        assert torch.equal(back["state"][i]["exp_avg_sq"], st["exp_avg_sq"]), ref_keys[i]
+    # resume: a fresh packed optimizer loaded from the translated reference state takes the same next step
+    fresh = [p.detach().clone().requires_grad_(True) for p in packed]
+    opt_f = torch.optim.AdamW(fresh, lr=1e-2, weight_decay=1e-4)
+    opt_f.load_state_dict(to_packed)
+    set_grads()
+    for f, p in zip(fresh, packed):
+        f.grad = p.grad.clone()
+    opt_p.step()
+    opt_f.step()
+    for f, p in zip(fresh, packed):
+        assert torch.equal(f, p)
+    # and the reference's own optimizer accepts the state translated back from the packed one
+    opt_r2 = torch.optim.AdamW([r.detach().clone().requires_grad_(True) for r in ref], lr=1e-2, weight_decay=1e-4)
+    opt_r2.load_state_dict(checkpoint.optimizer_state_to_reference(want, H))
+    with pytest.raises(ValueError, match="not a reference ViT parameter list"):
+        checkpoint.optimizer_state_to_packed({"state": {}, "param_groups": [{"params": list(range(13))}]}, H)
+
+
+def test_convert_checkpoint_cli_roundtrip(tmp_path):
+    from VisionTransformer import checkpoint
+    g = load_golden("tiny")
+    c = g["config"]
+    H = c["num_heads"]
+    keys = checkpoint.reference_param_keys(c["num_blocks"], H)
+    params = [g["state_dict"][k].clone().requires_grad_(True) for k in keys]
+    opt = torch.optim.AdamW(params, lr=1e-4, weight_decay=1e-4)
+    for p in params:
+        p.grad = torch.ones_like(p)
+    opt.step()
+    src, mid, dst = tmp_path / "ref.pt", tmp_path / "ours.pt", tmp_path / "back.pt"
+    torch.save({"epoch": 3, "model_state_dict": g["state_dict"], "optimizer_state_dict": opt.state_dict(),
+                "loss": 1.5, "step": 7}, src)
+    checkpoint.main(["to-packed", str(src), str(mid), "--heads", str(H)])
+    checkpoint.main(["to-reference", str(mid), str(dst), "--heads", str(H)])
+    a, b = torch.load(src, weights_only=False), torch.load(dst, weights_only=False)
+    assert a["epoch"] == b["epoch"] and a["step"] == b["step"]
+    assert len(torch.load(mid, weights_only=False)["optimizer_state_dict"]["param_groups"][0]["params"]) == \
+        4 + 11 * c["num_blocks"] + 6
+    for i, st in a["optimizer_state_dict"]["state"].items():
+        assert torch.equal(b["optimizer_state_dict"]["state"][i]["exp_avg"], st["exp_avg"])

@@ -114,6 +114,44 @@ def test_trainer_step_host_u8_matches_float_step(lib, layout):
         tr_b.step_host_u8(xh[:1], yh)
 
 
+def test_trainer_optimizer_state_in_reference_format(lib):
+    """DPTrainer.optimizer_state_dict() is a torch.optim.AdamW state_dict over the REFERENCE's parameter list
+    (train.py:66,73,110): a real AdamW over per-head parameters loads it and, fed the trainer's gradients, takes the
+    same next step; load_optimizer_state_dict resumes a second trainer on the same trajectory."""
+    from VisionTransformer import checkpoint
+    tr, cfg, sd, x, y = _make(torch.float32)
+    xd, yd = x.cuda(), y.cuda()
+    for _ in range(2):
+        tr.step(xd, yd)
+    osd, msd = tr.optimizer_state_dict(), tr.state_dict()
+    keys = checkpoint.reference_param_keys(cfg.num_blocks, cfg.num_heads)
+    assert osd["param_groups"][0]["params"] == list(range(len(keys))) and len(osd["state"]) == len(keys)
+    ref_params = [msd[k].clone().cpu().requires_grad_(True) for k in keys]
+    opt = torch.optim.AdamW(ref_params, lr=1e-3, weight_decay=1e-4)
+    opt.load_state_dict(osd)                       # what the reference does at src/train.py:73
+    d = tr._dims(True)
+    tr.forward(xd, d)
+    tr.backward(yd, d)
+    grads = {k: v.clone().cpu() for k, v in tr.grads_by_ref_key().items()}
+    tr.optimizer_step()
+    for k, p in zip(keys, ref_params):
+        p.grad = grads[k]
+    opt.step()
+    new = tr.state_dict()
+    for k, p in zip(keys, ref_params):
+        assert torch.allclose(new[k].cpu(), p.detach(), rtol=1e-4, atol=2e-6), k
+    # resume in a second trainer from (model, optimizer) state
+    tr2, *_ = _make(torch.float32)
+    tr2.load_state_dict(msd)
+    tr2.load_optimizer_state_dict(osd)
+    assert tr2.step_no == 2
+    tr2.step(xd, yd)
+    diff = (tr.p - tr2.p).abs()
+    assert (diff > 1e-6).float().mean().item() < 1e-3
+    with pytest.raises(ValueError, match="doesn't match the size"):
+        tr2.load_optimizer_state_dict({"state": {}, "param_groups": [{"params": [0, 1]}]})
+
+
 # ---------------------------------------------------------------------------------------------- data parallel
 def _dp_worker(rank, world, port, out):
     """One rank of a 2-process data-parallel step.  Both ranks share cuda:0 (gloo moves the buckets), so the real

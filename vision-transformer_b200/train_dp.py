@@ -272,6 +272,68 @@ class DPTrainer:
                             t[s * E + h * hs: s * E + (h + 1) * hs]
         return out
 
+    # ---- optimizer state in the reference's torch.optim.AdamW format (train.py:66,73,110) ----------
+    def _moment_views(self, arena):
+        """reference key -> view of `arena` (per-head slices of the packed q/k/v rows), same mapping as grads."""
+        E, H = self.E, self.H
+        hs = E // H
+        out = {}
+        for stage, field, key, _ in self.layout:
+            t = self.view(stage, field, arena)
+            if key is not None:
+                out[key] = t
+            else:
+                for h in range(H):
+                    for s_, sec in enumerate(_SECTIONS):
+                        out[f"transformer_encoder.blocks.{stage}.multi_head.heads.{h}.{sec}.weight"] = \
+                            t[s_ * E + h * hs: s_ * E + (h + 1) * hs]
+        return out
+
+    def optimizer_state_dict(self):
+        """What `torch.optim.AdamW(reference_model.parameters()).state_dict()` would hold after the same steps:
+        state indexed by position in the REFERENCE's parameter list, so a checkpoint written here resumes in the
+        unmodified reference (src/train.py:73) and vice versa."""
+        from VisionTransformer.checkpoint import reference_param_keys
+        keys = reference_param_keys(self.L, self.H)
+        m, v = self._moment_views(self.m), self._moment_views(self.v)
+        state = {}
+        if self.step_no > 0:
+            for i, k in enumerate(keys):
+                state[i] = {"step": torch.tensor(float(self.step_no)), "exp_avg": m[k].detach().clone(),
+                            "exp_avg_sq": v[k].detach().clone()}
+        group = {"lr": self.lr, "betas": tuple(self.betas), "eps": self.eps, "weight_decay": self.wd, "amsgrad": False,
+                 "foreach": None, "maximize": False, "capturable": False, "differentiable": False, "fused": None,
+                 "decoupled_weight_decay": True, "params": list(range(len(keys)))}
+        return {"state": state, "param_groups": [group]}
+
+    def load_optimizer_state_dict(self, sd):
+        """Inverse of optimizer_state_dict(); accepts the reference's own checkpoint['optimizer_state_dict']."""
+        from VisionTransformer.checkpoint import reference_param_keys
+        keys = reference_param_keys(self.L, self.H)
+        if len(sd["param_groups"]) != 1 or len(sd["param_groups"][0]["params"]) != len(keys):
+            raise ValueError(f"loaded state dict contains a parameter group that doesn't match the size of "
+                             f"optimizer's group ({len(keys)} parameters in the reference list)")
+        g = sd["param_groups"][0]
+        self.lr, self.betas, self.eps, self.wd = g["lr"], tuple(g["betas"]), g["eps"], g["weight_decay"]
+        m, v = self._moment_views(self.m), self._moment_views(self.v)
+        steps = set()
+        with torch.no_grad():
+            self.m.zero_()
+            self.v.zero_()
+            for i, k in enumerate(keys):
+                st = sd["state"].get(i)
+                if st is None:
+                    continue
+                if tuple(st["exp_avg"].shape) != tuple(m[k].shape):
+                    raise ValueError(f"size mismatch for optimizer state of {k}: {tuple(st['exp_avg'].shape)} vs "
+                                     f"{tuple(m[k].shape)}")
+                m[k].copy_(st["exp_avg"].to(self.dev, torch.float32))
+                v[k].copy_(st["exp_avg_sq"].to(self.dev, torch.float32))
+                steps.add(int(float(st["step"])))
+        if len(steps) > 1:
+            raise ValueError(f"per-parameter step counters differ ({sorted(steps)}); the flat AdamW kernel keeps one")
+        self.step_no = steps.pop() if steps else 0
+
     def sync_shadow(self):
         if self.shadow is not None:
             eng.cast_bf16(self.p, self.shadow)
