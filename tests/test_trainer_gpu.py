@@ -128,7 +128,9 @@ def test_trainer_optimizer_state_in_reference_format(lib):
     assert osd["param_groups"][0]["params"] == list(range(len(keys))) and len(osd["state"]) == len(keys)
     ref_params = [msd[k].clone().cpu().requires_grad_(True) for k in keys]
     opt = torch.optim.AdamW(ref_params, lr=1e-3, weight_decay=1e-4)
-    opt.load_state_dict(osd)                       # what the reference does at src/train.py:73
+    import copy
+    opt.load_state_dict(copy.deepcopy(osd))        # what the reference does at src/train.py:73 (torch keeps the
+    #                                                'step' tensors of the dict it is given, hence the copy)
     d = tr._dims(True)
     tr.forward(xd, d)
     tr.backward(yd, d)

@@ -20,8 +20,18 @@ namespace {
 constexpr int BM = 128;          // UMMA M (cta_group::1)
 constexpr int BK = 64;           // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kEpiWarps = 8;         // 2 per TMEM lane quarter: each pair splits the accumulator columns
-constexpr int kThreads = 64 + kEpiWarps * 32;
+// Epilogue warps per CTA: EW / 4 per TMEM lane quarter, each draining BN * 4 / EW accumulator columns.  8 everywhere.
+// 16 warps for the 2-byte-output CTA-pair call sites (64 columns each, <= 96 registers per thread, one ring stage
+// traded for the extra transpose buffers) was built and measured on B200: fc1+bits 200 -> 194 us, but qkv / dh / dln2
+// 3-6 us slower each (5-stage ring), per-block total unchanged (1.703 vs 1.706 ms) — kept behind
+// -DVITB200_EPI_WARPS_LP=16.
+#ifndef VITB200_EPI_WARPS_LP
+#define VITB200_EPI_WARPS_LP 8
+#endif
+template <typename OutT, int CG>
+constexpr int epi_warps() { return (sizeof(OutT) == 2 && CG == 2) ? VITB200_EPI_WARPS_LP : 8; }
+template <typename OutT, int CG>
+constexpr int gemm_threads() { return 64 + epi_warps<OutT, CG>() * 32; }
 
 // CG = 1: one CTA owns a 128 x BN tile.  CG = 2: a CTA PAIR (cluster of 2, tcgen05 cta_group::2) owns a 256 x BN tile;
 // each CTA stages its own 128 rows of A and HALF of the B tile, the leader issues M = 256 MMAs that read both halves,
@@ -29,14 +39,14 @@ constexpr int kThreads = 64 + kEpiWarps * 32;
 // of TWO pairs works on two vertically adjacent 256 x BN tiles; they need the same B tile, so each CTA fetches only a
 // QUARTER of it and TMA-multicasts that quarter to its counterpart in the other pair (24 KB instead of 32 KB per CTA
 // and k-block: the K-major call sites are bound by the ~43 B/clk/SM L2->SM feed, not by the tensor pipe).
-template <int BN, int CG>
+template <int BN, int CG, int EW>
 struct TileCfg {
-  static constexpr int STAGES = CG >= 2 ? 6 : 4;
+  static constexpr int STAGES = CG >= 2 ? (EW > 8 ? 5 : 6) : 4;   // 16 transpose buffers cost one ring stage
   static constexpr int A_BYTES = BM * BK * 2;            // 16 KB
   static constexpr int B_BYTES = BN * BK * 2 / (CG >= 2 ? 2 : 1);   // 32 KB @ BN=256 (16 KB per CTA of a pair)
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int BAR_BYTES = 256;
-  static constexpr int STG_BYTES = kEpiWarps * 32 * 128;   // per epilogue warp: 32 rows x 32 fp32 transpose buffer
+  static constexpr int STG_BYTES = EW * 32 * 128;   // per epilogue warp: 32 rows x 32 fp32 transpose buffer
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES + 1024;  // +1024 alignment slack
   static constexpr int TMEM_COLS = 2 * BN;
 };
@@ -48,10 +58,12 @@ struct TcParams {
 };
 
 template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__((gemm_threads<OutT, CG>()), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                const TcParams p, const GemmEpilogue ep) {
-  using Cfg = TileCfg<BN, CG>;
+  constexpr int EW = epi_warps<OutT, CG>();
+  constexpr int CW = BN * 4 / EW;          // accumulator columns drained by one epilogue warp
+  using Cfg = TileCfg<BN, CG, EW>;
   constexpr int kStages = Cfg::STAGES;
   // pair rank / work-unit walk: a unit is one (tile, split); CTAs of a pair walk the same units
   const uint32_t rank = CG >= 2 ? ptx::cluster_ctarank() : 0u;   // rank in the cluster: pair = rank >> 1, half = rank & 1
@@ -80,7 +92,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&tmem_full[s], 1);
-      ptx::mbar_init(&tmem_empty[s], kEpiWarps * (CG >= 2 ? 2 : 1));   // pair: the leader collects both CTAs' epilogue warps
+      ptx::mbar_init(&tmem_empty[s], EW * (CG >= 2 ? 2 : 1));   // pair: the leader collects both CTAs' epilogue warps
     }
     ptx::fence_barrier_init();
   }
@@ -192,8 +204,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (8 warps)
-    // Warp (q, half) drains TMEM lanes [32q, 32q+32) x accumulator columns [half*BN/2, (half+1)*BN/2) in chunks of
+    // ------------------------------------------------------------------ epilogue (EW warps)
+    // Warp (q, half) drains TMEM lanes [32q, 32q+32) x accumulator columns [half*CW, (half+1)*CW) in chunks of
     // 32 columns: tcgen05.ld gives each thread ONE row, a swizzled warp-private shared-memory transpose turns that
     // into "4 lanes cover 32 consecutive columns of a row", so residual / mask loads and the C stores are coalesced.
     const int ew = warp - 2;
@@ -214,9 +226,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       // dReLU mask rows) of my 32 x (BN/2) sub-tile into L2, one row segment per lane.
       if (VB_EPI(kEpiResidual | kEpiMask, ep.residual != nullptr || ep.mask_aux != nullptr)) {
         const int m = m0 + lane;
-        const int nb = n_blk * BN + half * (BN / 2);
+        const int nb = n_blk * BN + half * CW;
         if (m < p.M && nb < p.N) {
-          const int ncols = min(BN / 2, p.N - nb);
+          const int ncols = min(CW, p.N - nb);
           const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
           const int64_t off = orow * ep.ldc + nb;
           if (VB_EPI(kEpiResidual, ep.residual != nullptr))
@@ -229,10 +241,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
       const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BN);
-      const int nb = n_blk * BN + half * (BN / 2);     // first column of my half
-      constexpr int NCH = BN / 2 / 32;
+      const int nb = n_blk * BN + half * CW;     // first column of my share
+      constexpr int NCH = CW / 32;
       uint32_t r[32];
-      if (nb < p.N) ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * (BN / 2)), r);
+      if (nb < p.N) ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * CW), r);
       // Read-side operands (residual / dReLU mask) are fetched ONE CHUNK AHEAD into registers: their L2 latency is
       // covered by the previous chunk's transpose + stores instead of stalling every chunk.
       EpiPre pre_nx[4];
@@ -282,7 +294,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         __syncwarp();
         // (3) next chunk's TMEM load flies while this chunk is finished
         if (c + 1 < NCH && n0 + 32 < p.N)
-          ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * (BN / 2) + (c + 1) * 32), r);
+          ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * CW + (c + 1) * 32), r);
         float cs[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) cs[i] = 0.f;
@@ -400,7 +412,8 @@ namespace {
 template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG>
 int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
                  cudaStream_t stream) {
-  using Cfg = TileCfg<BN, CG>;
+  using Cfg = TileCfg<BN, CG, epi_warps<OutT, CG>()>;
+  constexpr int kThreads = gemm_threads<OutT, CG>();
   auto kern = gemm_tc_kernel<AMAJ, BMAJ, BN, OutT, EPI, CG>;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
