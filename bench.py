@@ -174,7 +174,7 @@ def run_reference(args):
         "e2e": {"value": ips, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------- our arm
@@ -336,13 +336,35 @@ def run_b200(args):
                 "of_measured_burst": step_tflops / pk["tflops_burst"], "of_datasheet_2250": step_tflops / 2250.0},
         "kernels": kern, "loss_after": loss_after,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def _claim_stdout():
+    """Libraries print to stdout behind our back (NCCL writes its version banner there): keep the real stdout for the
+    ONE JSON line the driver parses and point fd 1 at stderr for everything else."""
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
     args = parse()
+    _claim_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
