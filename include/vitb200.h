@@ -216,6 +216,20 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
                       const float* x_in, const void* acts, float* g, const void* dy_in, void* dy_out, void* scratch,
                       void* stream);
 
+/* Last-block variants: the classifier reads ONLY token 0 of the encoder output (vit.py:80 `x[:, 0, :]`), so in the LAST
+ * block the output projection, LayerNorm-2 and the MLP (transformer.py:46-47,56-59,78) are needed for the B token-0
+ * rows only; LayerNorm-1, q/k/v and attention still run over all tokens.  Logits and every gradient equal those of
+ * vitb200_block_fwd / vitb200_block_bwd (the other rows are dead values with exactly zero gradient).
+ *   fwd_row0: x0_out fp32 [B, E] = token 0 of each image.
+ *   bwd_row0: on entry g fp32 [B, E] and dy0_in `dtype` [B, E] are the compact token-0 rows (as written by
+ *             vitb200_head_bwd_row0); on exit g is the full [B*T, E] gradient w.r.t. x_in, dy_out as in block_bwd.
+ * g must be the usual [B*T, E] buffer in both cases. */
+int vitb200_block_fwd_row0(const vitb200_dims* d, int layer, const vitb200_block_params* p, const float* x_in,
+                           float* x0_out, void* acts, void* stream);
+int vitb200_block_bwd_row0(const vitb200_dims* d, int layer, const vitb200_block_params* p,
+                           const vitb200_block_grads* gr, const float* x_in, const void* acts, float* g,
+                           const void* dy0_in, void* dy_out, void* scratch, void* stream);
+
 /* Classifier head on token 0 (vit.py:69-74,80): Linear(E,4E) -> GELU(erf) -> LayerNorm(4E) -> Linear(4E,cls); fp32. */
 /* w1_lp (optional, bf16 copy of w1): in bf16 mode the two large head products (x0 W1^T and its backward pair) run
  * on the tensor-core path, as they do under the reference's autocast; NULL keeps the whole head in fp32. */
@@ -227,6 +241,13 @@ int vitb200_head_fwd(const vitb200_dims* d, const vitb200_head_params* p, const 
 /* Produces g (fp32 [B*T,E], zero except token 0) and dy_out = cast(g * fc2-dropout mask of layer n_layers-1). */
 int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_params* p, const vitb200_head_grads* gr,
                      const void* acts, const float* dlogits, float* g, void* dy_out, void* scratch, void* stream);
+/* Head fed by / feeding vitb200_block_{fwd,bwd}_row0: x0 fp32 [B, E] compact; g0 fp32 [B, E] and dy0 `dtype` [B, E]
+ * compact (dy0 masked with the fc2 dropout of layer n_layers-1 at compact element indices, as block_fwd_row0 drew it). */
+int vitb200_head_fwd_row0(const vitb200_dims* d, const vitb200_head_params* p, const float* x0, float* logits,
+                          void* acts, void* stream);
+int vitb200_head_bwd_row0(const vitb200_dims* d, int n_layers, const vitb200_head_params* p,
+                          const vitb200_head_grads* gr, const void* acts, const float* dlogits, float* g0, void* dy0,
+                          void* scratch, void* stream);
 
 /* sizeof() of the ABI structs as this library was compiled, for binding self-checks.
  * which: 0 dims, 1 dropout, 2 gemm_args, 3 adamw_hyper, 4 block_params, 5 block_grads, 6 head_params, 7 prof_entry;

@@ -9,10 +9,10 @@ from oracle import ref_vit
 pytestmark = pytest.mark.gpu
 
 
-def _make(dtype, E=64, H=2, L=2, B=4, P=8, img=32, classes=3, dropout_p=0.0):
+def _make(dtype, E=64, H=2, L=2, B=4, P=8, img=32, classes=3, dropout_p=0.0, **kw):
     import train_dp
     tr = train_dp.DPTrainer(input_channels=3, num_classes=classes, image_size=img, patch_size=P, embedding_size=E,
-                            num_heads=H, num_blocks=L, batch_size=B, dtype=dtype, dropout_p=dropout_p, lr=1e-3)
+                            num_heads=H, num_blocks=L, batch_size=B, dtype=dtype, dropout_p=dropout_p, lr=1e-3, **kw)
     cfg = ref_vit.Cfg(3, classes, (img // P) ** 2, E, P, H, L, B)
     sd = ref_vit.random_state_dict(cfg, seed=21)
     tr.load_state_dict(sd)
@@ -152,6 +152,40 @@ def test_trainer_optimizer_state_in_reference_format(lib):
     assert (diff > 1e-6).float().mean().item() < 1e-3
     with pytest.raises(ValueError, match="doesn't match the size"):
         tr2.load_optimizer_state_dict({"state": {}, "param_groups": [{"params": [0, 1]}]})
+
+
+@pytest.mark.parametrize("dtype,shape", [(torch.float32, dict()), (torch.float32, dict(L=1)),
+                                         (torch.bfloat16, dict(E=128, H=2, L=3, B=32, P=16, img=224)),
+                                         (torch.float32, dict(E=96, H=3, L=2, B=5, P=8, img=40))])
+def test_last_block_row0_mode_is_exact(lib, dtype, shape):
+    """last_block_row0=True (only token 0 of the last block is computed past attention, reference vit.py:80) gives the
+    logits and EVERY gradient of the full computation, and still matches the oracle in fp32."""
+    tr_f, cfg, sd, x, y = _make(dtype, **shape)
+    tr_r, *_ = _make(dtype, last_block_row0=True, **shape)
+    xd, yd = x.cuda(), y.cuda()
+    out = []
+    for tr in (tr_f, tr_r):
+        d = tr._dims(False)
+        tr.forward(xd, d)
+        tr.backward(yd, d)
+        torch.cuda.synchronize()
+        out.append((tr.logits.clone(), tr.loss.item(), {k: v.clone() for k, v in tr.grads_by_ref_key().items()}))
+    assert rel_err(out[1][0], out[0][0]) < 1e-6
+    assert abs(out[1][1] - out[0][1]) < 1e-6
+    for k, g in out[0][2].items():
+        assert rel_err(out[1][2][k], g) < 2e-5, k      # same per-row arithmetic; fp32 summation order differs
+    if dtype == torch.float32:
+        ref_logits, ref_loss, ref_grads = ref_vit.loss_and_grads(sd, x, y, cfg)
+        assert rel_err(out[1][0], ref_logits) < 1e-4
+        for k, g in ref_grads.items():
+            assert rel_err(out[1][2][k], g) < 1e-4, k
+    # with dropout the two modes draw different (equally valid) masks; training still descends
+    tr_d, *_ = _make(dtype, dropout_p=0.2, last_block_row0=True, **shape)
+    first = None
+    for _ in range(30):
+        tr_d.step(xd, yd)
+        first = tr_d.loss.item() if first is None else first
+    assert tr_d.loss.item() < first
 
 
 # ---------------------------------------------------------------------------------------------- data parallel

@@ -138,6 +138,12 @@ def _declare(L):
         "vitb200_block_fwd": [P(Dims), c_int, P(BlockParams), c_void_p, c_void_p, c_void_p, c_void_p],
         "vitb200_block_bwd": [P(Dims), c_int, P(BlockParams), P(BlockGrads), c_void_p, c_void_p, c_void_p, c_void_p,
                               c_void_p, c_void_p, c_void_p],
+        "vitb200_block_fwd_row0": [P(Dims), c_int, P(BlockParams), c_void_p, c_void_p, c_void_p, c_void_p],
+        "vitb200_block_bwd_row0": [P(Dims), c_int, P(BlockParams), P(BlockGrads), c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_void_p, c_void_p, c_void_p],
+        "vitb200_head_fwd_row0": [P(Dims), P(HeadParams), c_void_p, c_void_p, c_void_p, c_void_p],
+        "vitb200_head_bwd_row0": [P(Dims), c_int, P(HeadParams), P(HeadGrads), c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p, c_void_p],
         "vitb200_head_fwd": [P(Dims), P(HeadParams), c_void_p, c_void_p, c_void_p, c_void_p],
         "vitb200_head_bwd": [P(Dims), c_int, P(HeadParams), P(HeadGrads), c_void_p, c_void_p, c_void_p, c_void_p,
                              c_void_p, c_void_p],
@@ -160,7 +166,8 @@ EXPORTS = (
     "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
     "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_fwd_u8", "vitb200_im2col_u8", "vitb200_embed_bwd",
     "vitb200_block_act_bytes", "vitb200_block_scratch_bytes", "vitb200_block_fwd", "vitb200_block_bwd",
-    "vitb200_head_act_bytes", "vitb200_head_fwd", "vitb200_head_bwd",
+    "vitb200_head_act_bytes", "vitb200_head_fwd", "vitb200_head_bwd", "vitb200_block_fwd_row0",
+    "vitb200_block_bwd_row0", "vitb200_head_fwd_row0", "vitb200_head_bwd_row0",
 )
 
 

@@ -60,28 +60,32 @@ class Plan:
         _C.check(_C.lib().vitb200_embed_bwd(ctypes.byref(d), ctypes.byref(gr), g.data_ptr(), acts.data_ptr(),
                                             acts.data_ptr(), _C.stream_ptr()))
 
-    def block_fwd(self, d, layer, params, x_in, x_out, acts):
+    def block_fwd(self, d, layer, params, x_in, x_out, acts, row0=False):
         p = self._fill(_C.BlockParams, _C.BLOCK_FIELDS_P, params)
-        _C.check(_C.lib().vitb200_block_fwd(ctypes.byref(d), layer, ctypes.byref(p), x_in.data_ptr(), x_out.data_ptr(),
+        fn = _C.lib().vitb200_block_fwd_row0 if row0 else _C.lib().vitb200_block_fwd
+        _C.check(fn(ctypes.byref(d), layer, ctypes.byref(p), x_in.data_ptr(), x_out.data_ptr(),
                                             acts.data_ptr(), _C.stream_ptr()))
 
-    def block_bwd(self, d, layer, params, grads, x_in, acts, g, dy_in, dy_out, scratch):
+    def block_bwd(self, d, layer, params, grads, x_in, acts, g, dy_in, dy_out, scratch, row0=False):
         p = self._fill(_C.BlockParams, _C.BLOCK_FIELDS_P, params)
         gr = self._fill(_C.BlockGrads, _C.BLOCK_GRADS_STRUCT, grads)
-        _C.check(_C.lib().vitb200_block_bwd(ctypes.byref(d), layer, ctypes.byref(p), ctypes.byref(gr), x_in.data_ptr(),
+        fn = _C.lib().vitb200_block_bwd_row0 if row0 else _C.lib().vitb200_block_bwd
+        _C.check(fn(ctypes.byref(d), layer, ctypes.byref(p), ctypes.byref(gr), x_in.data_ptr(),
                                             acts.data_ptr(), g.data_ptr(), dy_in.data_ptr(),
                                             None if dy_out is None else dy_out.data_ptr(), scratch.data_ptr(),
                                             _C.stream_ptr()))
 
-    def head_fwd(self, d, params, x_last, logits, acts):
+    def head_fwd(self, d, params, x_last, logits, acts, row0=False):
         p = self._fill(_C.HeadParams, _C.HEAD_PARAMS_STRUCT, params)
-        _C.check(_C.lib().vitb200_head_fwd(ctypes.byref(d), ctypes.byref(p), x_last.data_ptr(), logits.data_ptr(),
+        fn = _C.lib().vitb200_head_fwd_row0 if row0 else _C.lib().vitb200_head_fwd
+        _C.check(fn(ctypes.byref(d), ctypes.byref(p), x_last.data_ptr(), logits.data_ptr(),
                                            acts.data_ptr(), _C.stream_ptr()))
 
-    def head_bwd(self, d, params, grads, acts, dlogits, g, dy_out, scratch):
+    def head_bwd(self, d, params, grads, acts, dlogits, g, dy_out, scratch, row0=False):
         p = self._fill(_C.HeadParams, _C.HEAD_PARAMS_STRUCT, params)
         gr = self._fill(_C.HeadGrads, _C.HEAD_FIELDS, grads)
-        _C.check(_C.lib().vitb200_head_bwd(ctypes.byref(d), self.L, ctypes.byref(p), ctypes.byref(gr), acts.data_ptr(),
+        fn = _C.lib().vitb200_head_bwd_row0 if row0 else _C.lib().vitb200_head_bwd
+        _C.check(fn(ctypes.byref(d), self.L, ctypes.byref(p), ctypes.byref(gr), acts.data_ptr(),
                                            dlogits.data_ptr(), g.data_ptr(), dy_out.data_ptr(), scratch.data_ptr(),
                                            _C.stream_ptr()))
 

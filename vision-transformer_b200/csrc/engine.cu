@@ -239,13 +239,15 @@ int64_t vitb200_head_act_bytes(const vitb200_dims* d) {
   return static_cast<int64_t>(total);
 }
 
-int vitb200_head_fwd(const vitb200_dims* d, const vitb200_head_params* p, const float* x_last, float* logits,
-                     void* acts, void* stream) {
+// Tx: tokens per image in x_last / g (d->T for the full residual stream, 1 when the last block ran in row-0 mode and
+// handed over only token 0 of every image)
+static int head_forward(const vitb200_dims* d, const vitb200_head_params* p, const float* x_last, float* logits,
+                        void* acts, void* stream, int Tx) {
   VB_PROPAGATE(check_dims(d));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const HeadActs a = carve_head(d, acts);
   const int B = d->B, E = d->E, F = 4 * d->E;
-  VB_PROPAGATE(gather_row0(x_last, a.x0, B, d->T, E, s));
+  VB_PROPAGATE(gather_row0(x_last, a.x0, B, Tx, E, s));
   GemmEpilogue ep = make_ep(a.h1, F);
   ep.bias = p->b1;
   if (head_lp(d, p)) {
@@ -261,8 +263,18 @@ int vitb200_head_fwd(const vitb200_dims* d, const vitb200_head_params* p, const 
   return gemm_f32(B, d->classes, F, 0, 0, a.n, F, p->w3, F, 1, ep3, s);
 }
 
-int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_params* p, const vitb200_head_grads* gr,
-                     const void* acts, const float* dlogits, float* g, void* dy_out, void* scratch, void* stream) {
+int vitb200_head_fwd(const vitb200_dims* d, const vitb200_head_params* p, const float* x_last, float* logits,
+                     void* acts, void* stream) {
+  return head_forward(d, p, x_last, logits, acts, stream, d ? d->T : 0);
+}
+int vitb200_head_fwd_row0(const vitb200_dims* d, const vitb200_head_params* p, const float* x0, float* logits,
+                          void* acts, void* stream) {
+  return head_forward(d, p, x0, logits, acts, stream, 1);
+}
+
+static int head_backward(const vitb200_dims* d, int n_layers, const vitb200_head_params* p, const vitb200_head_grads* gr,
+                         const void* acts, const float* dlogits, float* g, void* dy_out, void* scratch, void* stream,
+                         int Tx) {
   VB_PROPAGATE(check_dims(d));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const HeadActs a = carve_head(d, const_cast<void*>(acts));
@@ -300,7 +312,17 @@ int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_par
   }
   // scatter into the residual-stream gradient (token 0 only) + masked low-precision copy for the last fc2
   const Dropout dr = make_dropout(d->dropout_p, d->seed, drop_stream(n_layers - 1, 1));
-  return head_scatter(dx0, g, dy_out, is_bf16(d), dr, B, d->T, E, s);
+  return head_scatter(dx0, g, dy_out, is_bf16(d), dr, B, Tx, E, s);
+}
+
+int vitb200_head_bwd(const vitb200_dims* d, int n_layers, const vitb200_head_params* p, const vitb200_head_grads* gr,
+                     const void* acts, const float* dlogits, float* g, void* dy_out, void* scratch, void* stream) {
+  return head_backward(d, n_layers, p, gr, acts, dlogits, g, dy_out, scratch, stream, d ? d->T : 0);
+}
+int vitb200_head_bwd_row0(const vitb200_dims* d, int n_layers, const vitb200_head_params* p,
+                          const vitb200_head_grads* gr, const void* acts, const float* dlogits, float* g0, void* dy0,
+                          void* scratch, void* stream) {
+  return head_backward(d, n_layers, p, gr, acts, dlogits, g0, dy0, scratch, stream, 1);
 }
 
 }  // extern "C"
@@ -319,13 +341,22 @@ int64_t vitb200_block_scratch_bytes(const vitb200_dims* d) {
   return static_cast<int64_t>(total);
 }
 
-int vitb200_block_fwd(const vitb200_dims* d, int layer, const vitb200_block_params* p, const float* x_in,
-                      float* x_out, void* acts, void* stream) {
+}  // extern "C"
+
+// row0: ONLY token 0 of every image leaves this block (the classifier reads x[:, 0, :] of the LAST block, reference
+// vit.py:80).  LayerNorm-1, the q/k/v projection and attention still run on all B*T rows (token 0 attends to every
+// key), but the output projection, LayerNorm-2 and the MLP run on the B token-0 rows only; every stored tensor after
+// attention is then a compact [B, ...] matrix at the front of its usual buffer.  Logits and all gradients are those
+// of the full computation (the other rows are dead: nothing reads them, their gradient is exactly zero).
+static int block_forward(const vitb200_dims* d, int layer, const vitb200_block_params* p, const float* x_in,
+                         float* x_out, void* acts, void* stream, bool row0) {
   VB_PROPAGATE(check_dims(d));
   VB_REQUIRE(x_in != x_out, "block_fwd: x_in and x_out may not alias");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const bool bf = is_bf16(d);
   const int M = d->B * d->T, E = d->E, hs = E / d->H;
+  const int Mt = row0 ? d->B : M;                        // rows of the block tail (proj .. fc2)
+  const int64_t attn_ld = row0 ? static_cast<int64_t>(d->T) * E : E;   // token-0 rows of attn, strided view
   const BlockActs a = carve_block(d, acts);
   const float scale = sqrtf(static_cast<float>(hs));  // reference MULTIPLIES by sqrt(head_size): transformer.py:24
 
@@ -337,35 +368,60 @@ int vitb200_block_fwd(const vitb200_dims* d, int layer, const vitb200_block_para
   VB_PROPAGATE(run_lin(bf, l, s));
   if (bf) VB_PROPAGATE(attn_bf16_forward(static_cast<const bf16*>(a.qkv), static_cast<bf16*>(a.attn), a.lse, d->B, d->T, d->H, hs, scale, s));
   else VB_PROPAGATE(attn_f32_forward(static_cast<const float*>(a.qkv), static_cast<float*>(a.attn), a.lse, d->B, d->T, d->H, hs, scale, s));
+  const float* res_in = x_in;
+  if (row0) {   // compact copy of the token-0 rows of x_in behind x_mid's own B rows (the residual operand shares ldc)
+    float* x_in0 = a.x_mid + static_cast<size_t>(d->B) * E;
+    VB_CHECK_CUDA(cudaMemcpy2DAsync(x_in0, static_cast<size_t>(E) * 4, x_in, static_cast<size_t>(d->T) * E * 4,
+                                    static_cast<size_t>(E) * 4, d->B, cudaMemcpyDeviceToDevice, s));
+    res_in = x_in0;
+  }
   l = Lin();
-  l.M = M; l.N = E; l.K = E; l.A = a.attn; l.lda = E; l.B = p->w_proj; l.ldb = E;
-  l.ep = make_ep(a.x_mid, E); l.ep.bias = p->b_proj; l.ep.residual = x_in;
+  l.M = Mt; l.N = E; l.K = E; l.A = a.attn; l.lda = attn_ld; l.B = p->w_proj; l.ldb = E;
+  l.ep = make_ep(a.x_mid, E); l.ep.bias = p->b_proj; l.ep.residual = res_in;
   l.ep.drop = make_dropout(d->dropout_p, d->seed, drop_stream(layer, 0));
   l.out_f32 = true;
   VB_PROPAGATE(run_lin(bf, l, s));
 
   // x_out = x_mid + dropout(fc2(relu(fc1(LN2 x_mid))))
-  VB_PROPAGATE(ln_forward(a.x_mid, p->ln2_w, p->ln2_b, a.ln2, bf, a.mean2, a.rstd2, M, E, d->ln_eps, s));
+  VB_PROPAGATE(ln_forward(a.x_mid, p->ln2_w, p->ln2_b, a.ln2, bf, a.mean2, a.rstd2, Mt, E, d->ln_eps, s));
   l = Lin();
-  l.M = M; l.N = 4 * E; l.K = E; l.A = a.ln2; l.lda = E; l.B = p->w_fc1; l.ldb = E;
+  l.M = Mt; l.N = 4 * E; l.K = E; l.A = a.ln2; l.lda = E; l.B = p->w_fc1; l.ldb = E;
   l.ep = make_ep(a.h, 4 * E); l.ep.bias = p->b_fc1; l.ep.relu = 1; l.out_f32 = !bf;
-  if (a.hbits) { l.ep.bits_out = a.hbits; l.ep.bits_rows = M; }
+  if (a.hbits) { l.ep.bits_out = a.hbits; l.ep.bits_rows = Mt; }
   VB_PROPAGATE(run_lin(bf, l, s));
   l = Lin();
-  l.M = M; l.N = E; l.K = 4 * E; l.A = a.h; l.lda = 4 * E; l.B = p->w_fc2; l.ldb = 4 * E;
+  l.M = Mt; l.N = E; l.K = 4 * E; l.A = a.h; l.lda = 4 * E; l.B = p->w_fc2; l.ldb = 4 * E;
   l.ep = make_ep(x_out, E); l.ep.bias = p->b_fc2; l.ep.residual = a.x_mid;
   l.ep.drop = make_dropout(d->dropout_p, d->seed, drop_stream(layer, 1));
   l.out_f32 = true;
   return run_lin(bf, l, s);
 }
 
-int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_params* p, const vitb200_block_grads* gr,
+extern "C" {
+
+int vitb200_block_fwd(const vitb200_dims* d, int layer, const vitb200_block_params* p, const float* x_in,
+                      float* x_out, void* acts, void* stream) {
+  return block_forward(d, layer, p, x_in, x_out, acts, stream, false);
+}
+int vitb200_block_fwd_row0(const vitb200_dims* d, int layer, const vitb200_block_params* p, const float* x_in,
+                           float* x0_out, void* acts, void* stream) {
+  return block_forward(d, layer, p, x_in, x0_out, acts, stream, true);
+}
+
+}  // extern "C"
+
+static int block_backward(const vitb200_dims* d, int layer, const vitb200_block_params* p, const vitb200_block_grads* gr,
                       const float* x_in, const void* acts, float* g, const void* dy_in, void* dy_out, void* scratch,
-                      void* stream) {
+                      void* stream, bool row0) {
   VB_PROPAGATE(check_dims(d));
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const bool bf = is_bf16(d);
-  const int M = d->B * d->T, E = d->E, F = 4 * d->E, hs = E / d->H;
+  const int M_all = d->B * d->T, E = d->E, F = 4 * d->E, hs = E / d->H;
+  // row0 (see block_forward): on entry g and dy_in hold the B token-0 rows only, compact; the MLP / LayerNorm-2 /
+  // projection backward runs on those B rows, then the gradient is spread back over the full [B*T, E] layout (zero
+  // in every other row) for the attention / q-k-v / LayerNorm-1 backward, which see all tokens.
+  int M = row0 ? d->B : M_all;
+  const int64_t attn_ld = row0 ? static_cast<int64_t>(d->T) * E : E;
   const BlockActs a = carve_block(d, const_cast<void*>(acts));
   const BlockScratch sc = carve_scratch(d, scratch);
   const float scale = sqrtf(static_cast<float>(hs));
@@ -397,13 +453,24 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
 
   // ---- attention branch
   // dWproj[E,E] += s3^T attn  (dbproj += colsum(s3) came out of the LN2 backward above)
-  l = Lin(); l.M = E; l.N = E; l.K = M; l.a_major = 1; l.b_major = 1; l.A = sc.s3; l.lda = E; l.B = a.attn; l.ldb = E;
+  l = Lin(); l.M = E; l.N = E; l.K = M; l.a_major = 1; l.b_major = 1; l.A = sc.s3; l.lda = E; l.B = a.attn; l.ldb = attn_ld;
   l.ep = make_ep(gr->w_proj, E); l.ep.accumulate = 1; l.out_f32 = true;
   VB_PROPAGATE(run_lin(bf, l, s));
+  if (row0) {
+    // dO is zero except in the token-0 rows (written by the GEMM below through ldc = T*E); the residual-stream
+    // gradient g goes from compact [B,E] to full [B*T,E] with zeros elsewhere (staged through the free s1 buffer)
+    const size_t esz = bf ? 2 : 4;
+    VB_CHECK_CUDA(cudaMemsetAsync(sc.s2, 0, static_cast<size_t>(M_all) * E * esz, s));
+    VB_CHECK_CUDA(cudaMemcpyAsync(sc.s1, g, static_cast<size_t>(d->B) * E * 4, cudaMemcpyDeviceToDevice, s));
+    VB_CHECK_CUDA(cudaMemsetAsync(g, 0, static_cast<size_t>(M_all) * E * 4, s));
+    VB_CHECK_CUDA(cudaMemcpy2DAsync(g, static_cast<size_t>(d->T) * E * 4, sc.s1, static_cast<size_t>(E) * 4,
+                                    static_cast<size_t>(E) * 4, d->B, cudaMemcpyDeviceToDevice, s));
+  }
   // dO[M,E] = s3 Wproj
   l = Lin(); l.M = M; l.N = E; l.K = E; l.b_major = 1; l.A = sc.s3; l.lda = E; l.B = p->w_proj; l.ldb = E;
-  l.ep = make_ep(sc.s2, E); l.out_f32 = !bf;
+  l.ep = make_ep(sc.s2, attn_ld); l.out_f32 = !bf;
   VB_PROPAGATE(run_lin(bf, l, s));
+  M = M_all;   // from here on every token takes part
   // dqkv[M,3E] (into s1)
   if (bf) VB_PROPAGATE(attn_bf16_backward(static_cast<const bf16*>(a.qkv), static_cast<const bf16*>(a.attn), static_cast<const bf16*>(sc.s2), a.lse, sc.delta, static_cast<bf16*>(sc.s1), d->B, d->T, d->H, hs, scale, s));
   else VB_PROPAGATE(attn_f32_backward(static_cast<const float*>(a.qkv), static_cast<const float*>(a.attn), static_cast<const float*>(sc.s2), a.lse, sc.delta, static_cast<float*>(sc.s1), d->B, d->T, d->H, hs, scale, s));
@@ -419,6 +486,19 @@ int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_para
   const Dropout prev = make_dropout(layer > 0 ? d->dropout_p : 0.f, d->seed, drop_stream(layer - 1, 1));
   return ln_backward(sc.s2, bf, x_in, a.mean1, a.rstd1, p->ln1_w, g, 1, gr->ln1_w, gr->ln1_b,
                      layer > 0 ? dy_out : nullptr, layer > 0 ? gr->b_fc2_prev : nullptr, prev, M, E, s);
+}
+
+extern "C" {
+
+int vitb200_block_bwd(const vitb200_dims* d, int layer, const vitb200_block_params* p, const vitb200_block_grads* gr,
+                      const float* x_in, const void* acts, float* g, const void* dy_in, void* dy_out, void* scratch,
+                      void* stream) {
+  return block_backward(d, layer, p, gr, x_in, acts, g, dy_in, dy_out, scratch, stream, false);
+}
+int vitb200_block_bwd_row0(const vitb200_dims* d, int layer, const vitb200_block_params* p,
+                           const vitb200_block_grads* gr, const float* x_in, const void* acts, float* g,
+                           const void* dy0_in, void* dy_out, void* scratch, void* stream) {
+  return block_backward(d, layer, p, gr, x_in, acts, g, dy0_in, dy_out, scratch, stream, true);
 }
 
 // ================================================================================================ single ops

@@ -4,6 +4,8 @@
 //   backward: dx fused with the residual-gradient accumulate (g += dx), dgamma/dbeta reduced per CTA in
 //             shared memory then atomically into fp32 grads, and optionally emits the dropout-masked,
 //             down-cast gradient the next GEMM consumes (so no separate cast/mask pass exists).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "ptx.cuh"
@@ -518,8 +520,9 @@ int ln_grid(int M, int nw, int per_sm) {
 int ln_forward(const float* x, const float* gamma, const float* beta, void* y, bool y_bf16, float* mean,
                float* rstd, int M, int E, float eps, cudaStream_t stream) {
   VB_REQUIRE(M > 0 && E > 0, "ln_forward: empty input");
-  if ((E & 3) == 0 && E <= 128 * 12 && aligned16(x) && aligned16(y) && aligned16(gamma) && aligned16(beta) &&
-      M >= 4 * num_sms()) {
+  static const bool reg_path = !(getenv("VITB200_LN_REG") && atoi(getenv("VITB200_LN_REG")) == 0);
+  if (reg_path && (E & 3) == 0 && E <= 128 * 12 && aligned16(x) && aligned16(y) && aligned16(gamma) &&
+      aligned16(beta) && M >= 4 * num_sms()) {
     // register-resident rows, next row prefetched (the block LayerNorms; the [B, 4E] head LayerNorm stays below)
     ProfScope prof(kProfLnFwd, static_cast<double>(M) * E * (4 + (y_bf16 ? 2 : 4)) + 8.0 * M, 1, stream);
     const int vpl = ceil_div(E, 128);

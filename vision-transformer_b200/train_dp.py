@@ -118,7 +118,7 @@ class DPTrainer:
     def __init__(self, *, input_channels=3, num_classes=2, image_size=224, patch_size=16, embedding_size=768,
                  num_heads=12, num_blocks=12, batch_size=256, dtype=torch.bfloat16, device=None, lr=1e-4,
                  weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8, dropout_p=eng.DROPOUT_P, process_group=None,
-                 world_size=1, bucket_mb=48, seed=0):
+                 world_size=1, bucket_mb=48, seed=0, last_block_row0=False):
         dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         eng.require_cuda(torch.empty(0, device=dev), "trainer device")
         if _C.lib().vitb200_device_ok() != 1:
@@ -132,6 +132,10 @@ class DPTrainer:
         self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
         self.dropout_p, self.seed, self.step_no = float(dropout_p), int(seed), 0
         self.pg, self.world = process_group, int(world_size)
+        # opt-in dead-row elimination: only token 0 of the LAST block feeds the classifier (reference vit.py:80), so
+        # that block's proj / LayerNorm-2 / MLP and their backward run on B rows instead of B*T.  Same logits, same
+        # gradients; fewer executed FLOPs than the algorithmic count, hence off unless asked for.
+        self.row0 = bool(last_block_row0) and num_blocks >= 1
 
         self.layout = param_layout(C=self.C, P=self.P, E=self.E, H=self.H, L=self.L, T=self.T, B=self.B,
                                    classes=self.classes)
@@ -352,8 +356,9 @@ class DPTrainer:
         pl = self.plan
         pl.embed_fwd(d, self.embed_p, images, self.xs[0], self.emb_acts, u8_layout)
         for i in range(self.L):
-            pl.block_fwd(d, i, self.block_p[i], self.xs[i], self.xs[i + 1], self.blk_acts[i])
-        pl.head_fwd(d, self.head_p, self.xs[self.L], self.logits, self.head_acts)
+            pl.block_fwd(d, i, self.block_p[i], self.xs[i], self.xs[i + 1], self.blk_acts[i],
+                         row0=self.row0 and i == self.L - 1)
+        pl.head_fwd(d, self.head_p, self.xs[self.L], self.logits, self.head_acts, row0=self.row0)
         return self.logits
 
     def _bucket_ready(self, stage, handles):
@@ -365,11 +370,12 @@ class DPTrainer:
                                          self.dlogits.data_ptr(), self.B, self.classes, 1.0, _C.stream_ptr()))
         handles = []
         dy_a, dy_b = self.dy
-        pl.head_bwd(d, self.head_p, self.head_g, self.head_acts, self.dlogits, self.gstream, dy_a, self.scratch)
+        pl.head_bwd(d, self.head_p, self.head_g, self.head_acts, self.dlogits, self.gstream, dy_a, self.scratch,
+                    row0=self.row0)
         self._bucket_ready("head", handles)
         for i in range(self.L - 1, -1, -1):
             pl.block_bwd(d, i, self.block_p[i], self.block_g[i], self.xs[i], self.blk_acts[i], self.gstream, dy_a,
-                         dy_b, self.scratch)
+                         dy_b, self.scratch, row0=self.row0 and i == self.L - 1)
             dy_a, dy_b = dy_b, dy_a
             self._bucket_ready(i, handles)
         pl.embed_bwd(d, self.embed_g, self.gstream, self.emb_acts)
