@@ -128,7 +128,10 @@ def test_gemm_rejects_bad_arguments(lib):
 
 
 # ------------------------------------------------------------------------------------------------ LayerNorm
-@pytest.mark.parametrize("M,E", [(197 * 3, 768), (50, 384), (7, 4), (33, 1280), (5, 3072), (3, 100)])
+# M >= 4 x 148 rows take the register-resident forward kernel (one case per register-tile width: E <= 384, 768, 1024,
+# 1536), fewer rows the shared-memory one
+@pytest.mark.parametrize("M,E", [(197 * 3, 768), (50, 384), (7, 4), (33, 1280), (5, 3072), (3, 100), (1576, 384),
+                                 (197 * 4, 768), (601, 1024), (1000, 1280), (597, 200)])
 def test_layernorm_fwd_bwd(lib, M, E):
     C = _C()
     torch.manual_seed(4)
