@@ -8,7 +8,7 @@ from VisionTransformer import _C
 
 mode = sys.argv[1] if len(sys.argv) > 1 else "both"
 B, T, H = (int(v) for v in sys.argv[2:5]) if len(sys.argv) >= 5 else (256, 197, 12)
-hs = 64
+hs = int(os.environ.get("HS", 64))
 E = H * hs
 L = _C.lib()
 torch.manual_seed(0)
