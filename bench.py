@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-module-path", action="store_true", help="skip the drop-in nn.Module side number")
     ap.add_argument("--no-row0", action="store_true", help="skip the last-block dead-row-elimination side number")
     ap.add_argument("--bucket-mb", type=float, default=48)
     return ap.parse_args()
@@ -324,6 +325,40 @@ def run_b200(args):
                         "reported beside the headline, which executes every row"}
         del tr0
 
+    # ---- side number: the reference's OWN step lines (src/train.py:66,81,91-98) on the drop-in nn.Module package —
+    # what a user gets by only changing PYTHONPATH: model(x) / CrossEntropyLoss / zero_grad / backward / torch AdamW,
+    # host batch copied with .to(device) every step, loss.item() every step
+    module_path = None
+    if not args.no_module_path and world == 1:
+        from VisionTransformer import config as vcfg, vit as vvit
+        del tr.gstream
+        torch.cuda.empty_cache()
+        E_, H_, L_, P_, img_ = MODELS[args.model]
+        cfg = vcfg.ViTConfig(3, args.classes, (img_ // P_) ** 2, E_, P_, H_, L_, "cuda", args.batch, precision=dtype)
+        torch.manual_seed(0)
+        model = vvit.VisionTransformer(cfg).to(dev)
+        model.train()
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-4, weight_decay=1e-4)
+        crit = torch.nn.CrossEntropyLoss()
+        last = [0.0]
+
+        def ref_step(i):
+            tensors, labels = xh[i % n_host].to(dev), yh[i % n_host].to(dev)
+            logits = model(tensors)
+            loss = crit(logits.float(), labels)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+            last[0] = loss.item()
+
+        m_ms, _ = timed(ref_step, max(args.steps // 2, 3), 3)
+        n_m = max(args.steps // 2, 3)
+        module_path = {"value": gb / (m_ms / n_m * 1e-3), "unit": UNIT, "ms_per_step": m_ms / n_m, "last_loss": last[0],
+                       "what": "reference train loop lines (src/train.py:91-98) unchanged on the drop-in "
+                               "VisionTransformer package: synchronous .to(device) of a pinned fp32 batch, "
+                               "model(x), CrossEntropyLoss, backward, torch.optim.AdamW, loss.item() every step"}
+        del model, opt
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -356,6 +391,7 @@ def run_b200(args):
         "mfu": {"algorithmic_tflops_per_gpu": step_tflops, "of_measured_sustained": step_tflops / pk["tflops_sustained"],
                 "of_measured_burst": step_tflops / pk["tflops_burst"], "of_datasheet_2250": step_tflops / 2250.0},
         "kernels": kern, "loss_after": loss_after, "last_block_row0": row0,
+        "module_path": module_path,
     }
     emit(line)
     if world > 1:
