@@ -447,17 +447,27 @@ int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B
                cudaStream_t stream);
 
 // VITB200_ATTN=legacy forces the mma.sync kernels everywhere (A/B comparison and tests of the generic path).
-static bool use_tc_attention(int T, int hs) {
+static bool legacy_attention() {
   static const bool legacy = [] {
     const char* e = getenv("VITB200_ATTN");
     return e != nullptr && e[0] == 'l';
   }();
-  return !legacy && attn_tc_supported(T, hs);
+  return legacy;
+}
+static bool use_tc_attention(int T, int hs) { return !legacy_attention() && attn_tc_supported(T, hs); }
+// forward only: long rows / wide heads (ViT-H/14) on tcgen05; VITB200_ATTN_GEN=0 keeps them on mma.sync
+static bool use_tc_gen_forward(int T, int hs) {
+  static const bool off = [] {
+    const char* e = getenv("VITB200_ATTN_GEN");
+    return e != nullptr && e[0] == '0';
+  }();
+  return !off && !legacy_attention() && attn_tc_gen_supported(T, hs);
 }
 
 int attn_bf16_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
                       cudaStream_t stream) {
   if (use_tc_attention(T, hs)) return attn_tc_forward(qkv, out, lse, B, T, H, hs, scale, stream);
+  if (use_tc_gen_forward(T, hs)) return attn_tc_gen_forward(qkv, out, lse, B, T, H, hs, scale, stream);
   switch (hs) {
     case 16: return fwd_launch<16>(qkv, out, lse, B, T, H, scale, stream);
     case 32: return fwd_launch<32>(qkv, out, lse, B, T, H, scale, stream);

@@ -1,0 +1,399 @@
+// Fused self-attention FORWARD on the 5th-gen tensor cores for the shapes attention_tc.cu does not take: any number
+// of tokens and head sizes 16..128 (ViT-H/14: T = 577, head_size = 80).  Same semantics (reference
+// transformer.py:20-31,44-45: logits MULTIPLIED by sqrt(head_size), no mask, heads are column slices of the packed
+// [M,3E] qkv buffer, output concatenated in [M,E]) and the same building blocks as attention_tc.cu (S/P/O in tensor
+// memory, P written in place as bf16, TS-MMA for P.V), re-cut for long rows:
+//
+//   * a work item is (image, head, PAIR of 128-row query tiles); keys/values stream through a 2-stage TMA ring in
+//     chunks of 128 keys;
+//   * the head dimension is staged as 64-column swizzle atoms through a 3-D tensor map whose innermost extent is
+//     head_size, so the second atom of an 80-wide head arrives as 16 real columns + 48 zeros (no neighbour-head data);
+//     S = Q K^T uses only the head_size/16 real k-steps, O = P V runs with N = 64 * atoms;
+//   * softmax is TWO-PASS over the item instead of online: steps 0..n-1 recompute nothing but the row maximum
+//     (S chunk -> tcgen05.ld -> max), steps n..2n-1 recompute S, exponentiate against the final maximum and feed P.V.
+//     The accumulator is never rescaled (no correction pass, no dependence of P.V on the previous chunk's statistics);
+//     the price is a second Q K^T, which at these shapes is cheaper than the exponentials (16 ex2 / clk / SM).
+//   * the MMA thread interleaves the two tiles: while the softmax warps of one tile work on step s, the tensor pipe
+//     runs P.V of step s and S of step s+1 of the other tile.
+#include <cuda.h>
+#include <cstdlib>
+
+#include "common.cuh"
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace vb {
+
+namespace {
+
+constexpr int GQT = 128;                 // query rows per tile = UMMA M
+constexpr int GKC = 128;                 // keys per chunk = UMMA N of S, K extent of P.V
+constexpr int kGenThreads = 64 + 8 * 32; // producer, MMA issuer, 2 x 4 softmax warps
+constexpr float kGLog2e = 1.4426950408889634f;
+constexpr float kGLn2 = 0.6931471805599453f;
+
+template <int HS>
+struct GenCfg {
+  static constexpr int NA = (HS + 63) / 64;               // 64-column atoms per row
+  static constexpr int HSK = HS / 16;                     // real k-steps of S = Q K^T
+  static constexpr int ON = NA * 64;                      // UMMA N of O = P V (padded head dimension)
+  static constexpr int ATOM_Q = 2 * GQT * 128;            // one atom of the Q pair: 256 rows x 128 B
+  static constexpr int ATOM_KV = GKC * 128;               // one atom of a K or V chunk
+  static constexpr int Q_BYTES = NA * ATOM_Q;
+  static constexpr int KV_BYTES = NA * ATOM_KV;           // K (or V) chunk
+  static constexpr int STAGE_BYTES = 2 * KV_BYTES;        // K | V
+  static constexpr int SMEM_BYTES = Q_BYTES + 2 * STAGE_BYTES + 256 + 1024;
+};
+
+struct GenParams {
+  int T, H, npair, nchunk, items;   // npair = ceil(T / 256), nchunk = ceil(T / 128), items = B * H * npair
+  float scale_log2;                 // scale * log2(e)
+};
+
+template <int HS>
+__global__ void __launch_bounds__(kGenThreads, 1)
+attn_tc_gen_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict__ out, float* __restrict__ lse,
+                       const GenParams p) {
+  using Cfg = GenCfg<HS>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* s_q = smem;
+  uint8_t* s_kv = smem + Cfg::Q_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_kv + 2 * Cfg::STAGE_BYTES);
+  uint64_t* q_full = bars;              // [1] TMA -> MMA
+  uint64_t* q_empty = bars + 1;         // [1] MMA -> TMA (all S MMAs of the item issued and retired)
+  uint64_t* kv_full = bars + 2;         // [2] TMA -> MMA
+  uint64_t* kv_empty = bars + 4;        // [2] MMA -> TMA
+  uint64_t* s_full = bars + 6;          // [2] per tile: S chunk in tensor memory (MMA -> softmax)
+  uint64_t* ready = bars + 8;           // [2] per tile: softmax done with this step's S (max read / P written)
+  uint64_t* o_full = bars + 10;         // [2] per tile: O complete (MMA -> softmax)
+  uint64_t* o_free = bars + 12;         // [2] per tile: O drained (softmax -> MMA)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int E = p.H * HS;
+  const int nstep = 2 * p.nchunk;
+
+  if (threadIdx.x == 0) {
+    ptx::tma_prefetch_desc(&tm_qkv);
+    ptx::mbar_init(q_full, 1);
+    ptx::mbar_init(q_empty, 1);
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&kv_full[s], 1);
+      ptx::mbar_init(&kv_empty[s], 1);
+      ptx::mbar_init(&s_full[s], 1);
+      ptx::mbar_init(&ready[s], 4);
+      ptx::mbar_init(&o_full[s], 1);
+      ptx::mbar_init(&o_free[s], 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_ptr, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+  pdl_trigger();
+  // tensor-memory map per query tile t: S chunk (fp32, 128 columns) -> P (bf16 pairs, 64 columns) at t*256,
+  // O (fp32, ON <= 128 columns) at t*256 + 128
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      uint32_t n_item = 0, n_step = 0;
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n_item) {
+        const int pr = item % p.npair, bh = item / p.npair;
+        const int b = bh / p.H, h = bh - b * p.H;
+        const int row0 = b * p.T;
+        ptx::mbar_wait(q_empty, (n_item & 1u) ^ 1u);
+        ptx::mbar_arrive_expect_tx(q_full, Cfg::Q_BYTES);
+#pragma unroll
+        for (int j = 0; j < Cfg::NA; ++j)
+#pragma unroll
+          for (int t = 0; t < 2; ++t)
+            ptx::tma_load_3d(s_q + j * Cfg::ATOM_Q + t * (GQT * 128), &tm_qkv, q_full, 64 * j, h,
+                             row0 + pr * 2 * GQT + t * GQT);
+        for (int s = 0; s < nstep; ++s, ++n_step) {
+          const int st = n_step & 1;
+          const int c = s < p.nchunk ? s : s - p.nchunk;
+          const bool with_v = s >= p.nchunk;
+          uint8_t* base = s_kv + st * Cfg::STAGE_BYTES;
+          ptx::mbar_wait(&kv_empty[st], ((n_step >> 1) & 1u) ^ 1u);
+          ptx::mbar_arrive_expect_tx(&kv_full[st], with_v ? Cfg::STAGE_BYTES : Cfg::KV_BYTES);
+#pragma unroll
+          for (int j = 0; j < Cfg::NA; ++j) {
+            ptx::tma_load_3d(base + j * Cfg::ATOM_KV, &tm_qkv, &kv_full[st], 64 * j, p.H + h, row0 + c * GKC);
+            if (with_v)
+              ptx::tma_load_3d(base + Cfg::KV_BYTES + j * Cfg::ATOM_KV, &tm_qkv, &kv_full[st], 64 * j, 2 * p.H + h,
+                               row0 + c * GKC);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (one thread)
+    if (lane == 0) {
+      const uint32_t idesc_s = ptx::make_idesc_bf16_f32(GQT, GKC, 0, 0);       // S: M=128, N=128 keys, A,B K-major
+      const uint32_t idesc_o = ptx::make_idesc_bf16_f32(GQT, Cfg::ON, 0, 1);   // O: M=128, N=ON, B (=V) MN-major
+      const uint32_t sq = ptx::smem_u32(s_q);
+      const uint32_t skv = ptx::smem_u32(s_kv);
+      uint32_t n_item = 0, n_step = 0;
+      uint32_t n_ready[2] = {0u, 0u}, n_ofree[2] = {0u, 0u};
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n_item) {
+        const int pr = item % p.npair;
+        const bool live[2] = {pr * 2 * GQT < p.T, pr * 2 * GQT + GQT < p.T};
+        auto issue_s = [&](int t, uint32_t st) {
+          const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
+          const uint32_t sk = skv + st * Cfg::STAGE_BYTES;
+#pragma unroll
+          for (int k = 0; k < Cfg::HSK; ++k) {
+            const int j = k >> 2, kk = k & 3;
+            const uint64_t da = ptx::make_smem_desc_sw128(sq + j * Cfg::ATOM_Q + t * (GQT * 128) + kk * 32, 16, 1024);
+            const uint64_t db = ptx::make_smem_desc_sw128(sk + j * Cfg::ATOM_KV + kk * 32, 16, 1024);
+            ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&s_full[t]);
+        };
+        auto issue_pv = [&](int t, uint32_t st, bool first) {
+          const uint32_t a_p = tmem_base + static_cast<uint32_t>(t * 256);
+          const uint32_t d_o = a_p + 128u;
+          const uint32_t sv = skv + st * Cfg::STAGE_BYTES + Cfg::KV_BYTES;
+#pragma unroll
+          for (int k = 0; k < GKC / 16; ++k) {
+            // V as MN-major B: 16 key rows per k-step = 2048 B, 8-row groups 1024 B apart, next 64-wide atom ATOM_KV on
+            const uint64_t db = ptx::make_smem_desc_sw128(sv + k * 2048, Cfg::ATOM_KV, 1024);
+            ptx::umma_f16_ts(d_o, a_p + static_cast<uint32_t>(k * 8), db, idesc_o, (!first || k > 0) ? 1u : 0u);
+          }
+        };
+        ptx::mbar_wait(q_full, n_item & 1u);
+        ptx::mbar_wait(&kv_full[n_step & 1u], (n_step >> 1) & 1u);
+        ptx::tc_fence_after();
+        for (int t = 0; t < 2; ++t)
+          if (live[t]) issue_s(t, n_step & 1u);
+        for (int s = 0; s < nstep; ++s) {
+          const uint32_t cur = n_step + static_cast<uint32_t>(s);
+          const uint32_t st = cur & 1u;
+          const bool phase_b = s >= p.nchunk;
+          const int c = phase_b ? s - p.nchunk : s;
+          for (int t = 0; t < 2; ++t) {
+            if (live[t]) {
+              ptx::mbar_wait(&ready[t], n_ready[t] & 1u);     // softmax of tile t is done with step s
+              ++n_ready[t];
+              ptx::tc_fence_after();
+              if (phase_b) {
+                if (c == 0) {                                // previous item's O must have been drained
+                  ptx::mbar_wait(&o_free[t], (n_ofree[t] & 1u) ^ 1u);
+                  ++n_ofree[t];
+                  ptx::tc_fence_after();
+                }
+                issue_pv(t, st, c == 0);
+                if (c == p.nchunk - 1) ptx::umma_commit(&o_full[t]);
+              }
+            }
+            if (t == 1) ptx::umma_commit(&kv_empty[st]);      // both tiles have issued everything that reads stage st
+            if (s + 1 < nstep) {
+              const uint32_t nst = (cur + 1u) & 1u;
+              if (t == 0) {
+                ptx::mbar_wait(&kv_full[nst], ((cur + 1u) >> 1) & 1u);
+                ptx::tc_fence_after();
+              }
+              if (live[t]) issue_s(t, nst);
+              if (t == 1 && s + 2 == nstep) ptx::umma_commit(q_empty);   // last S of the item issued
+            }
+          }
+        }
+        n_step += static_cast<uint32_t>(nstep);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax + epilogue: one thread per query row
+    const int t = (warp - 2) >> 2;               // query tile of this warp within the pair
+    const int q = warp & 3;                      // tensor-memory lane quarter
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(t * 256);
+    const float sl2 = p.scale_log2;
+    uint32_t n_sfull = 0, n_ofull = 0;
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+      const int pr = item % p.npair, bh = item / p.npair;
+      const int tile0 = pr * 2 * GQT + t * GQT;
+      if (tile0 >= p.T) continue;                // dead tile: the MMA thread skips it too
+      const int b = bh / p.H, h = bh - b * p.H;
+      const int row = tile0 + q * 32 + lane;     // query index inside the image
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+      float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+      float mx = 0.f, mneg = 0.f;
+      for (int s = 0; s < nstep; ++s) {
+        const bool phase_b = s >= p.nchunk;
+        const int key0 = (phase_b ? s - p.nchunk : s) * GKC;
+        ptx::mbar_wait(&s_full[t], n_sfull & 1u);
+        ++n_sfull;
+        ptx::tc_fence_after();
+        if (!phase_b) {
+          // pass 1: running row maximum of the raw logits over the valid keys of this chunk
+#pragma unroll 1
+          for (int sub = 0; sub < GKC / 32; ++sub) {
+            const int kb = key0 + sub * 32;
+            if (kb >= p.T) break;                // warp-uniform
+            uint32_t r[32];
+            ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(sub * 32), r);
+            ptx::tmem_ld_wait();
+            if (kb + 32 <= p.T) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                mx0 = fmaxf(mx0, __uint_as_float(r[j]));
+                mx1 = fmaxf(mx1, __uint_as_float(r[j + 1]));
+                mx2 = fmaxf(mx2, __uint_as_float(r[j + 2]));
+                mx3 = fmaxf(mx3, __uint_as_float(r[j + 3]));
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (kb + j < p.T) mx0 = fmaxf(mx0, __uint_as_float(r[j]));
+            }
+          }
+          if (s == p.nchunk - 1) {
+            mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+            mneg = -mx * sl2;                    // scale > 0: max commutes with the scaling
+          }
+        } else {
+          // pass 2: p = exp2(s*c - m), row sum in fp32, P written over S as packed bf16 (zeros past the last key)
+#pragma unroll 1
+          for (int sub = 0; sub < GKC / 32; ++sub) {
+            const int kb = key0 + sub * 32;
+            uint32_t pk[16];
+            if (kb >= p.T) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) pk[j] = 0u;
+            } else {
+              uint32_t r[32];
+              ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(sub * 32), r);
+              ptx::tmem_ld_wait();
+              if (kb + 32 <= p.T) {
+#pragma unroll
+                for (int j = 0; j < 16; j += 2) {
+                  const float p0 = ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg));
+                  const float p1 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg));
+                  const float p2 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 2]), sl2, mneg));
+                  const float p3 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 3]), sl2, mneg));
+                  l0 += p0; l1 += p1; l2 += p2; l3 += p3;
+                  pk[j] = pack_bf16x2(p0, p1);
+                  pk[j + 1] = pack_bf16x2(p2, p3);
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const int k0 = kb + 2 * j;
+                  const float p0 = k0 < p.T ? ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg)) : 0.f;
+                  const float p1 = k0 + 1 < p.T ? ptx::ex2(fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg)) : 0.f;
+                  l0 += p0; l1 += p1;
+                  pk[j] = pack_bf16x2(p0, p1);
+                }
+              }
+            }
+            // the 16 packed columns of sub-chunk `sub` land on fp32 columns that sub-chunks <= sub/2 occupied:
+            // all of them have been read by this thread already (ascending order)
+            ptx::tmem_st_32x16(t_row + static_cast<uint32_t>(sub * 16), pk);
+          }
+          ptx::tmem_st_wait();
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&ready[t]);
+      }
+      // epilogue: O / l -> bf16 row, log-sum-exp
+      const float l = (l0 + l1) + (l2 + l3);
+      ptx::mbar_wait(&o_full[t], n_ofull & 1u);
+      ++n_ofull;
+      ptx::tc_fence_after();
+      const float inv = 1.f / l;
+      const bool live_row = row < p.T;
+      bf16* orow = out + (static_cast<int64_t>(b) * p.T + row) * E + h * HS;
+#pragma unroll
+      for (int c = 0; c < (HS + 31) / 32; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_row + 128u + static_cast<uint32_t>(c * 32), r);
+        ptx::tmem_ld_wait();
+        if (live_row) {
+          constexpr int kFull = HS / 32;         // loads whose 32 columns are all real
+          const int ngrp = c < kFull ? 4 : (HS - kFull * 32) / 8;
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) {
+            if (g8 < ngrp) {
+              uint4 w;
+              w.x = pack_bf16x2(__uint_as_float(r[8 * g8]) * inv, __uint_as_float(r[8 * g8 + 1]) * inv);
+              w.y = pack_bf16x2(__uint_as_float(r[8 * g8 + 2]) * inv, __uint_as_float(r[8 * g8 + 3]) * inv);
+              w.z = pack_bf16x2(__uint_as_float(r[8 * g8 + 4]) * inv, __uint_as_float(r[8 * g8 + 5]) * inv);
+              w.w = pack_bf16x2(__uint_as_float(r[8 * g8 + 6]) * inv, __uint_as_float(r[8 * g8 + 7]) * inv);
+              *reinterpret_cast<uint4*>(orow + c * 32 + g8 * 8) = w;
+            }
+          }
+        }
+      }
+      if (live_row && lse != nullptr)
+        lse[(static_cast<int64_t>(b) * p.H + h) * p.T + row] = (mx * sl2) * kGLn2 + logf(l);
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&o_free[t]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+template <int HS>
+int launch_gen_fwd(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, float scale, cudaStream_t stream) {
+  using Cfg = GenCfg<HS>;
+  const int E = H * HS;
+  const int64_t M = static_cast<int64_t>(B) * T;
+  CUtensorMap tm;
+  VB_PROPAGATE(make_tmap_bf16_heads(&tm, qkv, M, 3 * H, HS, 3 * static_cast<int64_t>(E), GQT));
+  static bool attr_done = false;
+  if (!attr_done) {
+    VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_gen_fwd_kernel<HS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::SMEM_BYTES));
+    attr_done = true;
+  }
+  GenParams p;
+  p.T = T; p.H = H;
+  p.npair = ceil_div(T, 2 * GQT);
+  p.nchunk = ceil_div(T, GKC);
+  p.items = B * H * p.npair;
+  p.scale_log2 = scale * kGLog2e;
+  ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * static_cast<double>(T) * HS, 1, stream);
+  const int grid = p.items < num_sms() ? p.items : num_sms();
+  VB_CHECK_CUDA(launch_pdl(attn_tc_gen_fwd_kernel<HS>, dim3(grid), dim3(kGenThreads), Cfg::SMEM_BYTES, stream, 1, tm,
+                           out, lse, p));
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+}  // namespace
+
+bool attn_tc_gen_supported(int T, int hs) { return T >= 1 && (hs == 64 || hs == 80 || hs == 96 || hs == 128); }
+
+int attn_tc_gen_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
+                        cudaStream_t stream) {
+  if (!attn_tc_gen_supported(T, hs)) {
+    set_error("attention (tcgen05, long rows): head_size %d not instantiated (64, 80, 96, 128)", hs);
+    return kErrUnsupported;
+  }
+  VB_REQUIRE(scale > 0.f, "attention: scale must be positive");
+  VB_REQUIRE(aligned16(qkv) && aligned16(out), "attention: qkv/out must be 16-byte aligned");
+  VB_REQUIRE(static_cast<int64_t>(B) * H * ceil_div(T, 2 * GQT) < (1ll << 31), "attention: too many work items");
+  switch (hs) {
+    case 64: return launch_gen_fwd<64>(qkv, out, lse, B, T, H, scale, stream);
+    case 80: return launch_gen_fwd<80>(qkv, out, lse, B, T, H, scale, stream);
+    case 96: return launch_gen_fwd<96>(qkv, out, lse, B, T, H, scale, stream);
+    default: return launch_gen_fwd<128>(qkv, out, lse, B, T, H, scale, stream);
+  }
+}
+
+}  // namespace vb

@@ -407,6 +407,34 @@ int make_tmap_bf16(void* map_out, const void* base, int64_t rows, int64_t cols, 
   return kOk;
 }
 
+// 3-D bf16 tensor map over the packed qkv buffer [rows][3H][hs] (dim0 = hs elements of one head section, dim1 = the 3H
+// head sections of a row, dim2 = rows; row stride ld elements): box = 64 x 1 x box_rows, 128B swizzle.  Because dim0
+// is BOUNDED at hs, a 64-wide box starting at column 64 of an hs = 80 head delivers 16 real columns and 48 zeros —
+// the head dimension is split into 64-column swizzle atoms without touching the neighbouring head.
+int make_tmap_bf16_heads(void* map_out, const void* base, int64_t rows, int sections, int hs, int64_t ld,
+                         int box_rows) {
+  CUtensorMap* map = static_cast<CUtensorMap*>(map_out);
+  EncodeTiledFn enc = get_encode_fn();
+  if (enc == nullptr) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return kErrCuda;
+  }
+  const cuuint64_t gdim[3] = {static_cast<cuuint64_t>(hs), static_cast<cuuint64_t>(sections),
+                              static_cast<cuuint64_t>(rows)};
+  const cuuint64_t gstr[2] = {static_cast<cuuint64_t>(hs) * 2, static_cast<cuuint64_t>(ld) * 2};
+  const cuuint32_t box[3] = {64, 1, static_cast<cuuint32_t>(box_rows)};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstr, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled (heads) failed (%d): rows=%lld sections=%d hs=%d ld=%lld", static_cast<int>(r),
+              static_cast<long long>(rows), sections, hs, static_cast<long long>(ld));
+    return kErrCuda;
+  }
+  return kOk;
+}
+
 namespace {
 
 template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG>

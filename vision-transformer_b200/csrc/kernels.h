@@ -21,6 +21,7 @@ int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int6
 // 2-D bf16 TMA descriptor over a row-major matrix [rows][ld] of logical width `cols`; box = box_cols x box_rows,
 // 128-byte swizzle, out-of-bounds reads return zero (defined in gemm_tc.cu; opaque 128-byte CUtensorMap)
 int make_tmap_bf16(void* map, const void* base, int64_t rows, int64_t cols, int64_t ld, int box_cols, int box_rows);
+int make_tmap_bf16_heads(void* map, const void* base, int64_t rows, int sections, int hs, int64_t ld, int box_rows);
 
 // layer norm
 int ln_forward(const float* x, const float* gamma, const float* beta, void* y, bool y_bf16, float* mean,
@@ -52,6 +53,10 @@ int attn_bf16_backward(const bf16* qkv, const bf16* out, const bf16* d_o, const 
 int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
                     cudaStream_t stream);
 bool attn_tc_supported(int T, int hs);
+// tcgen05 forward for any T and head sizes 16..128 (multiple of 16): keys in chunks of 128, two-pass softmax
+bool attn_tc_gen_supported(int T, int hs);
+int attn_tc_gen_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
+                        cudaStream_t stream);
 int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B, int T,
                      int H, int hs, float scale, cudaStream_t stream);
 
