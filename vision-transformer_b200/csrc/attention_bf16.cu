@@ -11,6 +11,8 @@
 
 namespace vb {
 
+static bool use_tc_gen_forward(int T, int hs);   // defined with the dispatchers at the end of this file
+
 namespace {
 
 constexpr int AT_THREADS = 128;  // 4 warps, 16 rows each
@@ -434,6 +436,8 @@ int bwd_launch(const bf16* qkv, const bf16* d_o, const float* lse, const float* 
   VB_PROPAGATE(set_attn_smem(attn_bf16_bwd_dkv_kernel<HS>, smem_kv));
   attn_bf16_bwd_dkv_kernel<HS><<<grid, AT_THREADS, smem_kv, stream>>>(qkv, d_o, lse, delta, dqkv, T, H, scale);
   VB_CHECK_LAUNCH();
+  if (use_tc_gen_forward(T, HS))   // dQ on tcgen05 (long rows / wide heads); dK, dV above stay on mma.sync for now
+    return attn_tc_gen_backward_dq(qkv, d_o, lse, delta, dqkv, B, T, H, HS, scale, stream);
   const size_t smem_q = 4 * Tile<HS>::BYTES;
   VB_PROPAGATE(set_attn_smem(attn_bf16_bwd_dq_kernel<HS>, smem_q));
   attn_bf16_bwd_dq_kernel<HS><<<grid, AT_THREADS, smem_q, stream>>>(qkv, d_o, lse, delta, dqkv, T, H, scale);

@@ -375,6 +375,318 @@ int launch_gen_fwd(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, 
   return kOk;
 }
 
+
+// ====================================================================================================== backward, dQ
+// dQ_t = dS K with dS = P o (dP - delta) * scale, P = exp2(S*c - lse*log2e), S = Q_t K^T, dP = dO_t V^T — the same
+// skeleton as the forward's second pass: a PAIR of 128-row query tiles per item, keys / values stream in chunks of 64
+// (S and dP of a chunk are 64 fp32 columns each, dS goes back IN PLACE over S as packed bf16 and is the TS-MMA A
+// operand of dQ += dS K, K chunk as MN-major B).  No row reductions: the statistics come from the forward (lse) and
+// the delta kernel, one value per thread.
+constexpr int DKC = 64;                  // keys per chunk
+
+template <int HS>
+struct DqCfg {
+  static constexpr int NA = (HS + 63) / 64;
+  static constexpr int HSK = HS / 16;
+  static constexpr int ON = NA * 64;
+  static constexpr int ATOM_Q = 2 * GQT * 128;            // 256 rows x 128 B
+  static constexpr int ATOM_KV = DKC * 128;               // 64 rows x 128 B
+  static constexpr int Q_BYTES = NA * ATOM_Q;             // Q pair (and dO pair)
+  static constexpr int KV_BYTES = NA * ATOM_KV;
+  static constexpr int STAGE_BYTES = 2 * KV_BYTES;        // K | V
+  static constexpr int SMEM_BYTES = 2 * Q_BYTES + 2 * STAGE_BYTES + 256 + 1024;
+};
+
+struct DqParams {
+  int T, H, npair, nchunk, items;   // nchunk = ceil(T / 64)
+  float scale, scale_log2;
+};
+
+template <int HS>
+__global__ void __launch_bounds__(kGenThreads, 1)
+attn_tc_gen_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_kv,
+                      const __grid_constant__ CUtensorMap tm_do, const float* __restrict__ lse,
+                      const float* __restrict__ delta, bf16* __restrict__ dqkv, const DqParams p) {
+  using Cfg = DqCfg<HS>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* s_q = smem;
+  uint8_t* s_do = smem + Cfg::Q_BYTES;
+  uint8_t* s_kv = smem + 2 * Cfg::Q_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_kv + 2 * Cfg::STAGE_BYTES);
+  uint64_t* q_full = bars;              // [1] Q and dO pair landed
+  uint64_t* q_empty = bars + 1;         // [1] last S/dP of the item retired
+  uint64_t* kv_full = bars + 2;         // [2]
+  uint64_t* kv_empty = bars + 4;        // [2]
+  uint64_t* s_full = bars + 6;          // [2] per tile: S and dP of a chunk in tensor memory
+  uint64_t* ready = bars + 8;           // [2] per tile: dS written
+  uint64_t* o_full = bars + 10;         // [2] per tile: dQ complete
+  uint64_t* o_free = bars + 12;         // [2] per tile: dQ drained
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int E = p.H * HS;
+  const int nstep = p.nchunk;
+
+  if (threadIdx.x == 0) {
+    ptx::tma_prefetch_desc(&tm_q);
+    ptx::tma_prefetch_desc(&tm_kv);
+    ptx::tma_prefetch_desc(&tm_do);
+    ptx::mbar_init(q_full, 1);
+    ptx::mbar_init(q_empty, 1);
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&kv_full[s], 1);
+      ptx::mbar_init(&kv_empty[s], 1);
+      ptx::mbar_init(&s_full[s], 1);
+      ptx::mbar_init(&ready[s], 4);
+      ptx::mbar_init(&o_full[s], 1);
+      ptx::mbar_init(&o_free[s], 4);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_ptr, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+  pdl_trigger();
+  // tensor memory per query tile t (base t*256): S (64 fp32 columns) -> dS (32 packed columns) at +0, dP at +64,
+  // dQ accumulator (ON <= 128 columns) at +128
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t n_item = 0, n_step = 0;
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n_item) {
+        const int pr = item % p.npair, bh = item / p.npair;
+        const int b = bh / p.H, h = bh - b * p.H;
+        const int row0 = b * p.T;
+        ptx::mbar_wait(q_empty, (n_item & 1u) ^ 1u);
+        ptx::mbar_arrive_expect_tx(q_full, 2 * Cfg::Q_BYTES);
+#pragma unroll
+        for (int j = 0; j < Cfg::NA; ++j)
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            const int r = row0 + pr * 2 * GQT + t * GQT;
+            ptx::tma_load_3d(s_q + j * Cfg::ATOM_Q + t * (GQT * 128), &tm_q, q_full, 64 * j, h, r);
+            ptx::tma_load_3d(s_do + j * Cfg::ATOM_Q + t * (GQT * 128), &tm_do, q_full, 64 * j, h, r);
+          }
+        for (int s = 0; s < nstep; ++s, ++n_step) {
+          const int st = n_step & 1;
+          uint8_t* base = s_kv + st * Cfg::STAGE_BYTES;
+          ptx::mbar_wait(&kv_empty[st], ((n_step >> 1) & 1u) ^ 1u);
+          ptx::mbar_arrive_expect_tx(&kv_full[st], Cfg::STAGE_BYTES);
+#pragma unroll
+          for (int j = 0; j < Cfg::NA; ++j) {
+            ptx::tma_load_3d(base + j * Cfg::ATOM_KV, &tm_kv, &kv_full[st], 64 * j, p.H + h, row0 + s * DKC);
+            ptx::tma_load_3d(base + Cfg::KV_BYTES + j * Cfg::ATOM_KV, &tm_kv, &kv_full[st], 64 * j, 2 * p.H + h,
+                             row0 + s * DKC);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = ptx::make_idesc_bf16_f32(GQT, DKC, 0, 0);       // S, dP: M=128, N=64 keys
+      const uint32_t idesc_o = ptx::make_idesc_bf16_f32(GQT, Cfg::ON, 0, 1);   // dQ: N=ON, B (=K) MN-major
+      const uint32_t sq = ptx::smem_u32(s_q), sdo = ptx::smem_u32(s_do), skv = ptx::smem_u32(s_kv);
+      uint32_t n_item = 0, n_step = 0;
+      uint32_t n_ready[2] = {0u, 0u}, n_ofree[2] = {0u, 0u};
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n_item) {
+        const int pr = item % p.npair;
+        const bool live[2] = {pr * 2 * GQT < p.T, pr * 2 * GQT + GQT < p.T};
+        auto issue_sdp = [&](int t, uint32_t st) {
+          const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
+          const uint32_t sk = skv + st * Cfg::STAGE_BYTES, sv = sk + Cfg::KV_BYTES;
+#pragma unroll
+          for (int k = 0; k < Cfg::HSK; ++k) {
+            const int j = k >> 2, kk = k & 3;
+            const uint64_t da = ptx::make_smem_desc_sw128(sq + j * Cfg::ATOM_Q + t * (GQT * 128) + kk * 32, 16, 1024);
+            const uint64_t db = ptx::make_smem_desc_sw128(sk + j * Cfg::ATOM_KV + kk * 32, 16, 1024);
+            ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
+          }
+#pragma unroll
+          for (int k = 0; k < Cfg::HSK; ++k) {
+            const int j = k >> 2, kk = k & 3;
+            const uint64_t da = ptx::make_smem_desc_sw128(sdo + j * Cfg::ATOM_Q + t * (GQT * 128) + kk * 32, 16, 1024);
+            const uint64_t db = ptx::make_smem_desc_sw128(sv + j * Cfg::ATOM_KV + kk * 32, 16, 1024);
+            ptx::umma_f16(d_s + 64u, da, db, idesc_s, k > 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&s_full[t]);
+        };
+        auto issue_dq = [&](int t, uint32_t st, bool first) {
+          const uint32_t a_ds = tmem_base + static_cast<uint32_t>(t * 256);
+          const uint32_t sk = skv + st * Cfg::STAGE_BYTES;
+#pragma unroll
+          for (int k = 0; k < DKC / 16; ++k) {
+            const uint64_t db = ptx::make_smem_desc_sw128(sk + k * 2048, Cfg::ATOM_KV, 1024);
+            ptx::umma_f16_ts(a_ds + 128u, a_ds + static_cast<uint32_t>(k * 8), db, idesc_o, (!first || k > 0) ? 1u : 0u);
+          }
+        };
+        ptx::mbar_wait(q_full, n_item & 1u);
+        ptx::mbar_wait(&kv_full[n_step & 1u], (n_step >> 1) & 1u);
+        ptx::tc_fence_after();
+        for (int t = 0; t < 2; ++t)
+          if (live[t]) issue_sdp(t, n_step & 1u);
+        if (nstep == 1) ptx::umma_commit(q_empty);
+        for (int s = 0; s < nstep; ++s) {
+          const uint32_t cur = n_step + static_cast<uint32_t>(s);
+          const uint32_t st = cur & 1u;
+          for (int t = 0; t < 2; ++t) {
+            if (live[t]) {
+              ptx::mbar_wait(&ready[t], n_ready[t] & 1u);
+              ++n_ready[t];
+              ptx::tc_fence_after();
+              if (s == 0) {
+                ptx::mbar_wait(&o_free[t], (n_ofree[t] & 1u) ^ 1u);
+                ++n_ofree[t];
+                ptx::tc_fence_after();
+              }
+              issue_dq(t, st, s == 0);
+              if (s == nstep - 1) ptx::umma_commit(&o_full[t]);
+            }
+            if (t == 1) ptx::umma_commit(&kv_empty[st]);
+            if (s + 1 < nstep) {
+              const uint32_t nst = (cur + 1u) & 1u;
+              if (t == 0) {
+                ptx::mbar_wait(&kv_full[nst], ((cur + 1u) >> 1) & 1u);
+                ptx::tc_fence_after();
+              }
+              if (live[t]) issue_sdp(t, nst);
+              if (t == 1 && s + 2 == nstep) ptx::umma_commit(q_empty);
+            }
+          }
+        }
+        n_step += static_cast<uint32_t>(nstep);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ element-wise + drain: one thread per query row
+    const int t = (warp - 2) >> 2;
+    const int q = warp & 3;
+    const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(t * 256);
+    const float sl2 = p.scale_log2, scale = p.scale;
+    uint32_t n_sfull = 0, n_ofull = 0;
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+      const int pr = item % p.npair, bh = item / p.npair;
+      const int tile0 = pr * 2 * GQT + t * GQT;
+      if (tile0 >= p.T) continue;
+      const int b = bh / p.H, h = bh - b * p.H;
+      const int row = tile0 + q * 32 + lane;
+      const bool live_row = row < p.T;
+      // dead rows: lse = +inf => P = 0 => dS = 0
+      const float lse2 = live_row ? lse[static_cast<int64_t>(bh) * p.T + row] * kGLog2e : INFINITY;
+      const float dlt = live_row ? delta[static_cast<int64_t>(bh) * p.T + row] : 0.f;
+      for (int s = 0; s < nstep; ++s) {
+        const int key0 = s * DKC;
+        ptx::mbar_wait(&s_full[t], n_sfull & 1u);
+        ++n_sfull;
+        ptx::tc_fence_after();
+#pragma unroll 1
+        for (int sub = 0; sub < DKC / 32; ++sub) {
+          const int kb = key0 + sub * 32;
+          uint32_t pk[16];
+          if (kb >= p.T) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) pk[j] = 0u;
+          } else {
+            uint32_t rs[32], rp[32];
+            ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(sub * 32), rs);
+            ptx::tmem_ld_32x32(t_row + 64u + static_cast<uint32_t>(sub * 32), rp);
+            ptx::tmem_ld_wait();
+            const bool full = kb + 32 <= p.T;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float p0 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j]), sl2, -lse2));
+              const float p1 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j + 1]), sl2, -lse2));
+              float d0 = p0 * (__uint_as_float(rp[2 * j]) - dlt) * scale;
+              float d1 = p1 * (__uint_as_float(rp[2 * j + 1]) - dlt) * scale;
+              if (!full) {
+                if (kb + 2 * j >= p.T) d0 = 0.f;
+                if (kb + 2 * j + 1 >= p.T) d1 = 0.f;
+              }
+              pk[j] = pack_bf16x2(d0, d1);
+            }
+          }
+          ptx::tmem_st_32x16(t_row + static_cast<uint32_t>(sub * 16), pk);
+        }
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&ready[t]);
+      }
+      ptx::mbar_wait(&o_full[t], n_ofull & 1u);
+      ++n_ofull;
+      ptx::tc_fence_after();
+      bf16* orow = dqkv + (static_cast<int64_t>(b) * p.T + row) * (3 * static_cast<int64_t>(E)) + h * HS;
+#pragma unroll
+      for (int c = 0; c < (HS + 31) / 32; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_row + 128u + static_cast<uint32_t>(c * 32), r);
+        ptx::tmem_ld_wait();
+        if (live_row) {
+          constexpr int kFull = HS / 32;
+          const int ngrp = c < kFull ? 4 : (HS - kFull * 32) / 8;
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) {
+            if (g8 < ngrp) {
+              uint4 w;
+              w.x = pack_bf16x2(__uint_as_float(r[8 * g8]), __uint_as_float(r[8 * g8 + 1]));
+              w.y = pack_bf16x2(__uint_as_float(r[8 * g8 + 2]), __uint_as_float(r[8 * g8 + 3]));
+              w.z = pack_bf16x2(__uint_as_float(r[8 * g8 + 4]), __uint_as_float(r[8 * g8 + 5]));
+              w.w = pack_bf16x2(__uint_as_float(r[8 * g8 + 6]), __uint_as_float(r[8 * g8 + 7]));
+              *reinterpret_cast<uint4*>(orow + c * 32 + g8 * 8) = w;
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&o_free[t]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+template <int HS>
+int launch_gen_dq(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B, int T,
+                  int H, float scale, cudaStream_t stream) {
+  using Cfg = DqCfg<HS>;
+  const int E = H * HS;
+  const int64_t M = static_cast<int64_t>(B) * T;
+  CUtensorMap tq, tkv, tdo;
+  VB_PROPAGATE(make_tmap_bf16_heads(&tq, qkv, M, 3 * H, HS, 3 * static_cast<int64_t>(E), GQT));
+  VB_PROPAGATE(make_tmap_bf16_heads(&tkv, qkv, M, 3 * H, HS, 3 * static_cast<int64_t>(E), DKC));
+  VB_PROPAGATE(make_tmap_bf16_heads(&tdo, d_o, M, H, HS, E, GQT));
+  static bool attr_done = false;
+  if (!attr_done) {
+    VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_gen_dq_kernel<HS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::SMEM_BYTES));
+    attr_done = true;
+  }
+  DqParams p;
+  p.T = T; p.H = H;
+  p.npair = ceil_div(T, 2 * GQT);
+  p.nchunk = ceil_div(T, DKC);
+  p.items = B * H * p.npair;
+  p.scale = scale;
+  p.scale_log2 = scale * kGLog2e;
+  const int grid = p.items < num_sms() ? p.items : num_sms();
+  VB_CHECK_CUDA(launch_pdl(attn_tc_gen_dq_kernel<HS>, dim3(grid), dim3(kGenThreads), Cfg::SMEM_BYTES, stream, 1, tq,
+                           tkv, tdo, lse, delta, dqkv, p));
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
 }  // namespace
 
 bool attn_tc_gen_supported(int T, int hs) { return T >= 1 && (hs == 64 || hs == 80 || hs == 96 || hs == 128); }
@@ -393,6 +705,23 @@ int attn_tc_gen_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, in
     case 80: return launch_gen_fwd<80>(qkv, out, lse, B, T, H, scale, stream);
     case 96: return launch_gen_fwd<96>(qkv, out, lse, B, T, H, scale, stream);
     default: return launch_gen_fwd<128>(qkv, out, lse, B, T, H, scale, stream);
+  }
+}
+
+// dQ only (the q section of dqkv); dK / dV stay with the caller's other kernel.
+int attn_tc_gen_backward_dq(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B,
+                            int T, int H, int hs, float scale, cudaStream_t stream) {
+  if (!attn_tc_gen_supported(T, hs)) {
+    set_error("attention dQ (tcgen05, long rows): head_size %d not instantiated (64, 80, 96, 128)", hs);
+    return kErrUnsupported;
+  }
+  VB_REQUIRE(scale > 0.f, "attention: scale must be positive");
+  VB_REQUIRE(aligned16(qkv) && aligned16(d_o) && aligned16(dqkv), "attention: operands must be 16-byte aligned");
+  switch (hs) {
+    case 64: return launch_gen_dq<64>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
+    case 80: return launch_gen_dq<80>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
+    case 96: return launch_gen_dq<96>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
+    default: return launch_gen_dq<128>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
   }
 }
 
