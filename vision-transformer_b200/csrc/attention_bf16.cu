@@ -432,6 +432,13 @@ int bwd_launch(const bf16* qkv, const bf16* d_o, const float* lse, const float* 
                float scale, cudaStream_t stream) {
   dim3 grid(ceil_div(T, AT_BLK), B * H);
   ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * T * HS, 2, stream);
+  if (use_tc_gen_forward(T, HS)) {   // long rows / wide heads: both backward kernels on tcgen05
+    static const bool dkv_legacy = getenv("VITB200_ATTN_GEN_DKV") && getenv("VITB200_ATTN_GEN_DKV")[0] == '0';
+    if (!dkv_legacy) {
+      VB_PROPAGATE(attn_tc_gen_backward_dkv(qkv, d_o, lse, delta, dqkv, B, T, H, HS, scale, stream));
+      return attn_tc_gen_backward_dq(qkv, d_o, lse, delta, dqkv, B, T, H, HS, scale, stream);
+    }
+  }
   const size_t smem_kv = 4 * Tile<HS>::BYTES + 4 * AT_BLK * sizeof(float);
   VB_PROPAGATE(set_attn_smem(attn_bf16_bwd_dkv_kernel<HS>, smem_kv));
   attn_bf16_bwd_dkv_kernel<HS><<<grid, AT_THREADS, smem_kv, stream>>>(qkv, d_o, lse, delta, dqkv, T, H, scale);

@@ -687,6 +687,324 @@ int launch_gen_dq(const bf16* qkv, const bf16* d_o, const float* lse, const floa
   return kOk;
 }
 
+
+// ====================================================================================================== backward, dK / dV
+// Transposed orientation (a tensor-memory A operand cannot be transposed): rows = keys.  An item is (image, head, ONE
+// 128-key tile); queries stream in chunks of 64 through a 3-stage TMA ring (Q chunk | dO chunk):
+//   S^T = K_t Q_c^T, dP^T = V_t dO_c^T  (64 fp32 columns each)  ->  P^T = exp2(S^T*c - lse[q]*log2e),
+//   dS^T = P^T o (dP^T - delta[q]) * scale, both written back in place as packed bf16
+//   dV_t += P^T dO_c, dK_t += dS^T Q_c   (TS-MMA, the chunk operands as MN-major B)
+// Chunks alternate between two tensor-memory slots, each owned by one group of four element-wise warps, so the S/dP
+// MMAs of chunk c+2 and the output MMAs of chunk c+1 run while a group works on chunk c.  The per-QUERY statistics are
+// per-column here: each lane holds them for two columns of the chunk and they are broadcast with warp shuffles.
+constexpr int KQC = 64;                  // queries per chunk
+constexpr int kKvStages = 3;
+
+template <int HS>
+struct DkvCfg {
+  static constexpr int NA = (HS + 63) / 64;
+  static constexpr int HSK = HS / 16;
+  static constexpr int ON = NA * 64;
+  static constexpr int ATOM_T = GQT * 128;                // key tile atom: 128 rows x 128 B
+  static constexpr int ATOM_C = KQC * 128;                // chunk atom: 64 rows x 128 B
+  static constexpr int T_BYTES = NA * ATOM_T;             // K tile (and V tile)
+  static constexpr int C_BYTES = NA * ATOM_C;             // Q chunk (and dO chunk)
+  static constexpr int STAGE_BYTES = 2 * C_BYTES;         // Q | dO
+  static constexpr int SMEM_BYTES = 2 * T_BYTES + kKvStages * STAGE_BYTES + 256 + 1024;
+};
+
+struct DkvParams {
+  int T, H, ntile, nchunk, items;   // ntile = ceil(T / 128), nchunk = ceil(T / 64), items = B * H * ntile
+  float scale, scale_log2;
+};
+
+template <int HS>
+__global__ void __launch_bounds__(kGenThreads, 1)
+attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_constant__ CUtensorMap tm_q,
+                       const __grid_constant__ CUtensorMap tm_do, const float* __restrict__ lse,
+                       const float* __restrict__ delta, bf16* __restrict__ dqkv, const DkvParams p) {
+  using Cfg = DkvCfg<HS>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* s_k = smem;
+  uint8_t* s_v = smem + Cfg::T_BYTES;
+  uint8_t* s_c = smem + 2 * Cfg::T_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_c + kKvStages * Cfg::STAGE_BYTES);
+  uint64_t* kv_full = bars;             // [1] K and V tile landed
+  uint64_t* kv_empty = bars + 1;        // [1] last S/dP of the item retired
+  uint64_t* c_full = bars + 2;          // [3] chunk ring
+  uint64_t* c_empty = bars + 5;         // [3]
+  uint64_t* s_full = bars + 8;          // [2] per slot: S^T and dP^T in tensor memory
+  uint64_t* ready = bars + 10;          // [2] per slot: P^T and dS^T written
+  uint64_t* o_full = bars + 12;         // [1] dV and dK complete
+  uint64_t* o_free = bars + 13;         // [1] both accumulators drained (8 warps)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int E = p.H * HS;
+  const int n = p.nchunk;
+
+  if (threadIdx.x == 0) {
+    ptx::tma_prefetch_desc(&tm_kv);
+    ptx::tma_prefetch_desc(&tm_q);
+    ptx::tma_prefetch_desc(&tm_do);
+    ptx::mbar_init(kv_full, 1);
+    ptx::mbar_init(kv_empty, 1);
+    for (int s = 0; s < kKvStages; ++s) {
+      ptx::mbar_init(&c_full[s], 1);
+      ptx::mbar_init(&c_empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&s_full[s], 1);
+      ptx::mbar_init(&ready[s], 4);
+    }
+    ptx::mbar_init(o_full, 1);
+    ptx::mbar_init(o_free, 8);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_ptr, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  pdl_wait();
+  pdl_trigger();
+  // tensor memory: slot g at g*128: S^T (64 fp32 columns) -> P^T (32 packed) at +0, dP^T -> dS^T at +64;
+  // dV accumulator at 256, dK accumulator at 384 (ON <= 128 columns each)
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t n_item = 0, n_chunk = 0;
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n_item) {
+        const int tile = item % p.ntile, bh = item / p.ntile;
+        const int b = bh / p.H, h = bh - b * p.H;
+        const int row0 = b * p.T;
+        ptx::mbar_wait(kv_empty, (n_item & 1u) ^ 1u);
+        ptx::mbar_arrive_expect_tx(kv_full, 2 * Cfg::T_BYTES);
+#pragma unroll
+        for (int j = 0; j < Cfg::NA; ++j) {
+          ptx::tma_load_3d(s_k + j * Cfg::ATOM_T, &tm_kv, kv_full, 64 * j, p.H + h, row0 + tile * GQT);
+          ptx::tma_load_3d(s_v + j * Cfg::ATOM_T, &tm_kv, kv_full, 64 * j, 2 * p.H + h, row0 + tile * GQT);
+        }
+        for (int c = 0; c < n; ++c, ++n_chunk) {
+          const uint32_t st = n_chunk % kKvStages;
+          uint8_t* base = s_c + st * Cfg::STAGE_BYTES;
+          ptx::mbar_wait(&c_empty[st], ((n_chunk / kKvStages) & 1u) ^ 1u);
+          ptx::mbar_arrive_expect_tx(&c_full[st], Cfg::STAGE_BYTES);
+#pragma unroll
+          for (int j = 0; j < Cfg::NA; ++j) {
+            ptx::tma_load_3d(base + j * Cfg::ATOM_C, &tm_q, &c_full[st], 64 * j, h, row0 + c * KQC);
+            ptx::tma_load_3d(base + Cfg::C_BYTES + j * Cfg::ATOM_C, &tm_do, &c_full[st], 64 * j, h, row0 + c * KQC);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = ptx::make_idesc_bf16_f32(GQT, KQC, 0, 0);       // S^T, dP^T: M=128 keys, N=64 queries
+      const uint32_t idesc_o = ptx::make_idesc_bf16_f32(GQT, Cfg::ON, 0, 1);   // dV, dK: N=ON, B MN-major
+      const uint32_t sk = ptx::smem_u32(s_k), sv = ptx::smem_u32(s_v), sc = ptx::smem_u32(s_c);
+      uint32_t n_item = 0, n_chunk = 0;
+      uint32_t n_ready[2] = {0u, 0u};
+      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n_item) {
+        auto issue_s = [&](int c, int slot) {
+          const uint32_t g = n_chunk + static_cast<uint32_t>(c);
+          const uint32_t st = g % kKvStages;
+          ptx::mbar_wait(&c_full[st], (g / kKvStages) & 1u);
+          ptx::tc_fence_after();
+          const uint32_t cq = sc + st * Cfg::STAGE_BYTES, cdo = cq + Cfg::C_BYTES;
+          const uint32_t d = tmem_base + static_cast<uint32_t>(slot * 128);
+#pragma unroll
+          for (int k = 0; k < Cfg::HSK; ++k) {
+            const int j = k >> 2, kk = k & 3;
+            const uint64_t da = ptx::make_smem_desc_sw128(sk + j * Cfg::ATOM_T + kk * 32, 16, 1024);
+            const uint64_t db = ptx::make_smem_desc_sw128(cq + j * Cfg::ATOM_C + kk * 32, 16, 1024);
+            ptx::umma_f16(d, da, db, idesc_s, k > 0 ? 1u : 0u);
+          }
+#pragma unroll
+          for (int k = 0; k < Cfg::HSK; ++k) {
+            const int j = k >> 2, kk = k & 3;
+            const uint64_t da = ptx::make_smem_desc_sw128(sv + j * Cfg::ATOM_T + kk * 32, 16, 1024);
+            const uint64_t db = ptx::make_smem_desc_sw128(cdo + j * Cfg::ATOM_C + kk * 32, 16, 1024);
+            ptx::umma_f16(d + 64u, da, db, idesc_s, k > 0 ? 1u : 0u);
+          }
+          ptx::umma_commit(&s_full[slot]);
+        };
+        auto issue_out = [&](int c, int slot, bool first) {
+          const uint32_t g = n_chunk + static_cast<uint32_t>(c);
+          const uint32_t st = g % kKvStages;
+          const uint32_t cq = sc + st * Cfg::STAGE_BYTES, cdo = cq + Cfg::C_BYTES;
+          const uint32_t a = tmem_base + static_cast<uint32_t>(slot * 128);
+#pragma unroll
+          for (int k = 0; k < KQC / 16; ++k) {   // dV += P^T dO_c
+            const uint64_t db = ptx::make_smem_desc_sw128(cdo + k * 2048, Cfg::ATOM_C, 1024);
+            ptx::umma_f16_ts(tmem_base + 256u, a + static_cast<uint32_t>(k * 8), db, idesc_o, (!first || k > 0) ? 1u : 0u);
+          }
+#pragma unroll
+          for (int k = 0; k < KQC / 16; ++k) {   // dK += dS^T Q_c
+            const uint64_t db = ptx::make_smem_desc_sw128(cq + k * 2048, Cfg::ATOM_C, 1024);
+            ptx::umma_f16_ts(tmem_base + 384u, a + 64u + static_cast<uint32_t>(k * 8), db, idesc_o,
+                             (!first || k > 0) ? 1u : 0u);
+          }
+          ptx::umma_commit(&c_empty[st]);
+        };
+        ptx::mbar_wait(kv_full, n_item & 1u);
+        ptx::tc_fence_after();
+        issue_s(0, 0);
+        if (n > 1) issue_s(1, 1);
+        if (n <= 2) ptx::umma_commit(kv_empty);
+        for (int c = 0; c < n; ++c) {
+          const int slot = c & 1;
+          ptx::mbar_wait(&ready[slot], n_ready[slot] & 1u);
+          ++n_ready[slot];
+          ptx::tc_fence_after();
+          if (c == 0) {
+            ptx::mbar_wait(o_free, (n_item & 1u) ^ 1u);
+            ptx::tc_fence_after();
+          }
+          issue_out(c, slot, c == 0);
+          if (c == n - 1) ptx::umma_commit(o_full);
+          if (c + 2 < n) {
+            issue_s(c + 2, slot);
+            if (c + 2 == n - 1) ptx::umma_commit(kv_empty);
+          }
+        }
+        n_chunk += static_cast<uint32_t>(n);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ element-wise groups: one thread per key row
+    const int g = (warp - 2) >> 2;               // group = tensor-memory slot = chunk parity
+    const int q = warp & 3;
+    const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const uint32_t t_slot = t_lane + static_cast<uint32_t>(g * 128);
+    const float sl2 = p.scale_log2, scale = p.scale;
+    uint32_t n_sfull = 0, n_item = 0;
+    for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++n_item) {
+      const int tile = item % p.ntile, bh = item / p.ntile;
+      const int b = bh / p.H, h = bh - b * p.H;
+      const int key = tile * GQT + q * 32 + lane;
+      const float* lse_bh = lse + static_cast<int64_t>(bh) * p.T;
+      const float* dl_bh = delta + static_cast<int64_t>(bh) * p.T;
+      for (int c = g; c < n; c += 2) {
+        const int q0 = c * KQC;
+        // statistics of query columns q0 + lane and q0 + 32 + lane; columns past the last query: lse = +inf => P = 0
+        const int qa = q0 + lane, qb = q0 + 32 + lane;
+        const float nl_a = qa < p.T ? -__ldg(lse_bh + qa) * kGLog2e : -INFINITY;
+        const float nl_b = qb < p.T ? -__ldg(lse_bh + qb) * kGLog2e : -INFINITY;
+        const float dl_a = qa < p.T ? __ldg(dl_bh + qa) : 0.f;
+        const float dl_b = qb < p.T ? __ldg(dl_bh + qb) : 0.f;
+        ptx::mbar_wait(&s_full[g], n_sfull & 1u);
+        ++n_sfull;
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int sub = 0; sub < KQC / 32; ++sub) {
+          uint32_t pkp[16], pkd[16];
+          if (q0 + sub * 32 >= p.T) {            // warp-uniform
+#pragma unroll
+            for (int j = 0; j < 16; ++j) { pkp[j] = 0u; pkd[j] = 0u; }
+          } else {
+            uint32_t rs[32], rp[32];
+            ptx::tmem_ld_32x32(t_slot + static_cast<uint32_t>(sub * 32), rs);
+            ptx::tmem_ld_32x32(t_slot + 64u + static_cast<uint32_t>(sub * 32), rp);
+            ptx::tmem_ld_wait();
+            const float nl_mine = sub == 0 ? nl_a : nl_b;
+            const float dl_mine = sub == 0 ? dl_a : dl_b;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const float nl0 = __shfl_sync(0xffffffffu, nl_mine, 2 * j), nl1 = __shfl_sync(0xffffffffu, nl_mine, 2 * j + 1);
+              const float dl0 = __shfl_sync(0xffffffffu, dl_mine, 2 * j), dl1 = __shfl_sync(0xffffffffu, dl_mine, 2 * j + 1);
+              const float p0 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j]), sl2, nl0));
+              const float p1 = ptx::ex2(fmaf(__uint_as_float(rs[2 * j + 1]), sl2, nl1));
+              const float d0 = p0 * (__uint_as_float(rp[2 * j]) - dl0) * scale;
+              const float d1 = p1 * (__uint_as_float(rp[2 * j + 1]) - dl1) * scale;
+              pkp[j] = pack_bf16x2(p0, p1);
+              pkd[j] = pack_bf16x2(d0, d1);
+            }
+          }
+          ptx::tmem_st_32x16(t_slot + static_cast<uint32_t>(sub * 16), pkp);
+          ptx::tmem_st_32x16(t_slot + 64u + static_cast<uint32_t>(sub * 16), pkd);
+        }
+        ptx::tmem_st_wait();
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(&ready[g]);
+      }
+      // drain: group 0 stores dV (section 2 of dqkv), group 1 stores dK (section 1)
+      ptx::mbar_wait(o_full, n_item & 1u);
+      ptx::tc_fence_after();
+      const bool live_key = key < p.T;
+      bf16* orow = dqkv + (static_cast<int64_t>(b) * p.T + key) * (3 * static_cast<int64_t>(E)) + (g == 0 ? 2 : 1) * E +
+                   h * HS;
+      const uint32_t t_acc = t_lane + (g == 0 ? 256u : 384u);
+#pragma unroll
+      for (int c = 0; c < (HS + 31) / 32; ++c) {
+        uint32_t r[32];
+        ptx::tmem_ld_32x32(t_acc + static_cast<uint32_t>(c * 32), r);
+        ptx::tmem_ld_wait();
+        if (live_key) {
+          constexpr int kFull = HS / 32;
+          const int ngrp = c < kFull ? 4 : (HS - kFull * 32) / 8;
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) {
+            if (g8 < ngrp) {
+              uint4 w;
+              w.x = pack_bf16x2(__uint_as_float(r[8 * g8]), __uint_as_float(r[8 * g8 + 1]));
+              w.y = pack_bf16x2(__uint_as_float(r[8 * g8 + 2]), __uint_as_float(r[8 * g8 + 3]));
+              w.z = pack_bf16x2(__uint_as_float(r[8 * g8 + 4]), __uint_as_float(r[8 * g8 + 5]));
+              w.w = pack_bf16x2(__uint_as_float(r[8 * g8 + 6]), __uint_as_float(r[8 * g8 + 7]));
+              *reinterpret_cast<uint4*>(orow + c * 32 + g8 * 8) = w;
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(o_free);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+template <int HS>
+int launch_gen_dkv(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B, int T,
+                   int H, float scale, cudaStream_t stream) {
+  using Cfg = DkvCfg<HS>;
+  const int E = H * HS;
+  const int64_t M = static_cast<int64_t>(B) * T;
+  CUtensorMap tkv, tq, tdo;
+  VB_PROPAGATE(make_tmap_bf16_heads(&tkv, qkv, M, 3 * H, HS, 3 * static_cast<int64_t>(E), GQT));
+  VB_PROPAGATE(make_tmap_bf16_heads(&tq, qkv, M, 3 * H, HS, 3 * static_cast<int64_t>(E), KQC));
+  VB_PROPAGATE(make_tmap_bf16_heads(&tdo, d_o, M, H, HS, E, KQC));
+  static bool attr_done = false;
+  if (!attr_done) {
+    VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_gen_dkv_kernel<HS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       Cfg::SMEM_BYTES));
+    attr_done = true;
+  }
+  DkvParams p;
+  p.T = T; p.H = H;
+  p.ntile = ceil_div(T, GQT);
+  p.nchunk = ceil_div(T, KQC);
+  p.items = B * H * p.ntile;
+  p.scale = scale;
+  p.scale_log2 = scale * kGLog2e;
+  const int grid = p.items < num_sms() ? p.items : num_sms();
+  VB_CHECK_CUDA(launch_pdl(attn_tc_gen_dkv_kernel<HS>, dim3(grid), dim3(kGenThreads), Cfg::SMEM_BYTES, stream, 1, tkv,
+                           tq, tdo, lse, delta, dqkv, p));
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
 }  // namespace
 
 bool attn_tc_gen_supported(int T, int hs) { return T >= 1 && (hs == 64 || hs == 80 || hs == 96 || hs == 128); }
@@ -708,7 +1026,24 @@ int attn_tc_gen_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, in
   }
 }
 
-// dQ only (the q section of dqkv); dK / dV stay with the caller's other kernel.
+// dK and dV (the k and v sections of dqkv).
+int attn_tc_gen_backward_dkv(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B,
+                             int T, int H, int hs, float scale, cudaStream_t stream) {
+  if (!attn_tc_gen_supported(T, hs)) {
+    set_error("attention dK/dV (tcgen05, long rows): head_size %d not instantiated (64, 80, 96, 128)", hs);
+    return kErrUnsupported;
+  }
+  VB_REQUIRE(scale > 0.f, "attention: scale must be positive");
+  VB_REQUIRE(aligned16(qkv) && aligned16(d_o) && aligned16(dqkv), "attention: operands must be 16-byte aligned");
+  switch (hs) {
+    case 64: return launch_gen_dkv<64>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
+    case 80: return launch_gen_dkv<80>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
+    case 96: return launch_gen_dkv<96>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
+    default: return launch_gen_dkv<128>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);
+  }
+}
+
+// dQ only (the q section of dqkv).
 int attn_tc_gen_backward_dq(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B,
                             int T, int H, int hs, float scale, cudaStream_t stream) {
   if (!attn_tc_gen_supported(T, hs)) {

@@ -57,6 +57,8 @@ bool attn_tc_supported(int T, int hs);
 bool attn_tc_gen_supported(int T, int hs);
 int attn_tc_gen_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
                         cudaStream_t stream);
+int attn_tc_gen_backward_dkv(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B,
+                             int T, int H, int hs, float scale, cudaStream_t stream);
 int attn_tc_gen_backward_dq(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B,
                             int T, int H, int hs, float scale, cudaStream_t stream);
 int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const float* delta, bf16* dqkv, int B, int T,
