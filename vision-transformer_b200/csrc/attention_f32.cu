@@ -120,6 +120,45 @@ attn_delta_vec_kernel(const uint4* __restrict__ o, const uint4* __restrict__ d_o
   }
 }
 
+// Head slices that are a whole number of 16-byte chunks but not a power of two of them (head_size 80 / 96 in bf16):
+// one thread owns one (token, head) slice, consecutive threads consecutive heads, so a warp still sweeps one
+// contiguous span of o and dO.
+template <typename T_>
+__global__ void __launch_bounds__(256)
+attn_delta_slice_kernel(const uint4* __restrict__ o, const uint4* __restrict__ d_o, float* __restrict__ delta,
+                        int64_t slices, int cph, int T, int H) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  pdl_wait();
+  pdl_trigger();
+  for (int64_t hr = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; hr < slices; hr += stride) {
+    const uint4* a4 = o + hr * cph;
+    const uint4* b4 = d_o + hr * cph;
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll 2
+    for (int j = 0; j < cph; ++j) {
+      const uint4 a = __ldg(a4 + j), b = __ldg(b4 + j);
+      if constexpr (sizeof(T_) == 2) {
+        const uint32_t av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          s0 = fmaf(__uint_as_float(av[k] << 16), __uint_as_float(bv[k] << 16), s0);
+          s1 = fmaf(__uint_as_float(av[k] & 0xffff0000u), __uint_as_float(bv[k] & 0xffff0000u), s1);
+        }
+      } else {
+        s0 = fmaf(__uint_as_float(a.x), __uint_as_float(b.x), s0);
+        s1 = fmaf(__uint_as_float(a.y), __uint_as_float(b.y), s1);
+        s0 = fmaf(__uint_as_float(a.z), __uint_as_float(b.z), s0);
+        s1 = fmaf(__uint_as_float(a.w), __uint_as_float(b.w), s1);
+      }
+    }
+    const int64_t tok = hr / H;
+    const int h = static_cast<int>(hr - tok * H);
+    const int64_t b = tok / T;
+    const int i = static_cast<int>(tok - b * T);
+    delta[(b * H + h) * T + i] = s0 + s1;
+  }
+}
+
 // dQ: one warp per query row i.  ds_ij = p_ij (dP_ij - delta_i) * scale ; dq_i = sum_j ds_ij k_j
 __global__ void __launch_bounds__(AF_WARPS * 32)
 attn_f32_bwd_dq_kernel(const float* __restrict__ qkv, const float* __restrict__ d_o, const float* __restrict__ lse,
@@ -239,6 +278,20 @@ int attn_delta(const void* o, const void* d_o, bool is_bf16, float* delta, int B
       }
     }
 #undef VB_DELTA
+    VB_CHECK_LAUNCH();
+    return kOk;
+  }
+  if (hs * (is_bf16 ? 2 : 4) % 16 == 0 && cph >= 1 && aligned16(o) && aligned16(d_o)) {
+    const int64_t slices = static_cast<int64_t>(B) * T * H;
+    const int grid_s = static_cast<int>(std::min<int64_t>((slices + 255) / 256, static_cast<int64_t>(num_sms()) * 16));
+    const uint4* o4 = static_cast<const uint4*>(o);
+    const uint4* d4 = static_cast<const uint4*>(d_o);
+    if (is_bf16)
+      VB_CHECK_CUDA(launch_pdl(attn_delta_slice_kernel<bf16>, dim3(grid_s), dim3(256), 0, stream, 1, o4, d4, delta,
+                               slices, cph, T, H));
+    else
+      VB_CHECK_CUDA(launch_pdl(attn_delta_slice_kernel<float>, dim3(grid_s), dim3(256), 0, stream, 1, o4, d4, delta,
+                               slices, cph, T, H));
     VB_CHECK_LAUNCH();
     return kOk;
   }
