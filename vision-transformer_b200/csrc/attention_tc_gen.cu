@@ -31,6 +31,7 @@ constexpr int GKC = 128;                 // keys per chunk = UMMA N of S, K exte
 constexpr int kGenThreads = 64 + 8 * 32; // producer, MMA issuer, 2 x 4 softmax warps
 constexpr float kGLog2e = 1.4426950408889634f;
 constexpr float kGLn2 = 0.6931471805599453f;
+constexpr uint32_t kDescHi = ptx::smem_desc_hi_sw128(1024);   // 128B-swizzle descriptors, 8-row groups 1024 B apart
 
 template <int HS>
 struct GenCfg {
@@ -147,27 +148,27 @@ attn_tc_gen_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restr
         const int pr = item % p.npair;
         const bool live[2] = {pr * 2 * GQT < p.T, pr * 2 * GQT + GQT < p.T};
         auto issue_s = [&](int t, uint32_t st) {
+          // lean issue: descriptor low words advance by plain adds, the high word is a constant (ptx.cuh)
           const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
-          const uint32_t sk = skv + st * Cfg::STAGE_BYTES;
+          const uint32_t a0 = ptx::smem_desc_lo(sq + t * (GQT * 128), 16);
+          const uint32_t b0 = ptx::smem_desc_lo(skv + st * Cfg::STAGE_BYTES, 16);
 #pragma unroll
           for (int k = 0; k < Cfg::HSK; ++k) {
             const int j = k >> 2, kk = k & 3;
-            const uint64_t da = ptx::make_smem_desc_sw128(sq + j * Cfg::ATOM_Q + t * (GQT * 128) + kk * 32, 16, 1024);
-            const uint64_t db = ptx::make_smem_desc_sw128(sk + j * Cfg::ATOM_KV + kk * 32, 16, 1024);
-            ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
+            ptx::umma_f16_lh(d_s, a0 + ((j * Cfg::ATOM_Q + kk * 32) >> 4), b0 + ((j * Cfg::ATOM_KV + kk * 32) >> 4),
+                             kDescHi, idesc_s, k > 0 ? 1u : 0u);
           }
           ptx::umma_commit(&s_full[t]);
         };
         auto issue_pv = [&](int t, uint32_t st, bool first) {
           const uint32_t a_p = tmem_base + static_cast<uint32_t>(t * 256);
           const uint32_t d_o = a_p + 128u;
-          const uint32_t sv = skv + st * Cfg::STAGE_BYTES + Cfg::KV_BYTES;
+          // V as MN-major B: 16 key rows per k-step = 2048 B, 8-row groups 1024 B apart, next 64-wide atom ATOM_KV on
+          const uint32_t b0 = ptx::smem_desc_lo(skv + st * Cfg::STAGE_BYTES + Cfg::KV_BYTES, Cfg::ATOM_KV);
 #pragma unroll
-          for (int k = 0; k < GKC / 16; ++k) {
-            // V as MN-major B: 16 key rows per k-step = 2048 B, 8-row groups 1024 B apart, next 64-wide atom ATOM_KV on
-            const uint64_t db = ptx::make_smem_desc_sw128(sv + k * 2048, Cfg::ATOM_KV, 1024);
-            ptx::umma_f16_ts(d_o, a_p + static_cast<uint32_t>(k * 8), db, idesc_o, (!first || k > 0) ? 1u : 0u);
-          }
+          for (int k = 0; k < GKC / 16; ++k)
+            ptx::umma_f16_ts_lh(d_o, a_p + static_cast<uint32_t>(k * 8), b0 + k * 128, kDescHi, idesc_o,
+                                (!first || k > 0) ? 1u : 0u);
         };
         ptx::mbar_wait(q_full, n_item & 1u);
         ptx::mbar_wait(&kv_full[n_step & 1u], (n_step >> 1) & 1u);
@@ -383,6 +384,15 @@ int launch_gen_fwd(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, 
 // operand of dQ += dS K, K chunk as MN-major B).  No row reductions: the statistics come from the forward (lse) and
 // the delta kernel, one value per thread.
 constexpr int DKC = 64;                  // keys per chunk
+// The backward kernels are bound by the element-wise chain of ONE warp per 32 rows (~950 instructions per 64-column
+// chunk), so they run 16 element-wise warps: two warps share each 32-row quarter of a tile / slot and take one
+// 32-column half of every chunk each.
+constexpr int kBwdGenThreads = 64 + 16 * 32;
+// The packed bf16 half written by one warp of a pair lands on fp32 columns the OTHER warp still has to read, so the
+// pair meets on its own named barrier between the tensor-memory loads and the stores.
+__device__ __forceinline__ void pair_sync(int pair) {
+  asm volatile("bar.sync %0, 64;" ::"r"(pair + 1) : "memory");
+}
 
 template <int HS>
 struct DqCfg {
@@ -403,7 +413,7 @@ struct DqParams {
 };
 
 template <int HS>
-__global__ void __launch_bounds__(kGenThreads, 1)
+__global__ void __launch_bounds__(kBwdGenThreads, 1)
 attn_tc_gen_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_constant__ CUtensorMap tm_kv,
                       const __grid_constant__ CUtensorMap tm_do, const float* __restrict__ lse,
                       const float* __restrict__ delta, bf16* __restrict__ dqkv, const DqParams p) {
@@ -438,9 +448,9 @@ attn_tc_gen_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       ptx::mbar_init(&kv_full[s], 1);
       ptx::mbar_init(&kv_empty[s], 1);
       ptx::mbar_init(&s_full[s], 1);
-      ptx::mbar_init(&ready[s], 4);
+      ptx::mbar_init(&ready[s], 8);
       ptx::mbar_init(&o_full[s], 1);
-      ptx::mbar_init(&o_free[s], 4);
+      ptx::mbar_init(&o_free[s], 8);
     }
     ptx::fence_barrier_init();
   }
@@ -500,31 +510,26 @@ attn_tc_gen_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         const bool live[2] = {pr * 2 * GQT < p.T, pr * 2 * GQT + GQT < p.T};
         auto issue_sdp = [&](int t, uint32_t st) {
           const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
-          const uint32_t sk = skv + st * Cfg::STAGE_BYTES, sv = sk + Cfg::KV_BYTES;
+          const uint32_t sk = skv + st * Cfg::STAGE_BYTES;
+          const uint32_t qa0 = ptx::smem_desc_lo(sq + t * (GQT * 128), 16), kb0 = ptx::smem_desc_lo(sk, 16);
+          const uint32_t oa0 = ptx::smem_desc_lo(sdo + t * (GQT * 128), 16), vb0 = ptx::smem_desc_lo(sk + Cfg::KV_BYTES, 16);
+          // S and dP are independent accumulator chains: alternate them so that no MMA waits on its predecessor
 #pragma unroll
           for (int k = 0; k < Cfg::HSK; ++k) {
             const int j = k >> 2, kk = k & 3;
-            const uint64_t da = ptx::make_smem_desc_sw128(sq + j * Cfg::ATOM_Q + t * (GQT * 128) + kk * 32, 16, 1024);
-            const uint64_t db = ptx::make_smem_desc_sw128(sk + j * Cfg::ATOM_KV + kk * 32, 16, 1024);
-            ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
-          }
-#pragma unroll
-          for (int k = 0; k < Cfg::HSK; ++k) {
-            const int j = k >> 2, kk = k & 3;
-            const uint64_t da = ptx::make_smem_desc_sw128(sdo + j * Cfg::ATOM_Q + t * (GQT * 128) + kk * 32, 16, 1024);
-            const uint64_t db = ptx::make_smem_desc_sw128(sv + j * Cfg::ATOM_KV + kk * 32, 16, 1024);
-            ptx::umma_f16(d_s + 64u, da, db, idesc_s, k > 0 ? 1u : 0u);
+            const uint32_t oa = (j * Cfg::ATOM_Q + kk * 32) >> 4, ob = (j * Cfg::ATOM_KV + kk * 32) >> 4;
+            ptx::umma_f16_lh(d_s, qa0 + oa, kb0 + ob, kDescHi, idesc_s, k > 0 ? 1u : 0u);
+            ptx::umma_f16_lh(d_s + 64u, oa0 + oa, vb0 + ob, kDescHi, idesc_s, k > 0 ? 1u : 0u);
           }
           ptx::umma_commit(&s_full[t]);
         };
         auto issue_dq = [&](int t, uint32_t st, bool first) {
           const uint32_t a_ds = tmem_base + static_cast<uint32_t>(t * 256);
-          const uint32_t sk = skv + st * Cfg::STAGE_BYTES;
+          const uint32_t b0 = ptx::smem_desc_lo(skv + st * Cfg::STAGE_BYTES, Cfg::ATOM_KV);
 #pragma unroll
-          for (int k = 0; k < DKC / 16; ++k) {
-            const uint64_t db = ptx::make_smem_desc_sw128(sk + k * 2048, Cfg::ATOM_KV, 1024);
-            ptx::umma_f16_ts(a_ds + 128u, a_ds + static_cast<uint32_t>(k * 8), db, idesc_o, (!first || k > 0) ? 1u : 0u);
-          }
+          for (int k = 0; k < DKC / 16; ++k)
+            ptx::umma_f16_ts_lh(a_ds + 128u, a_ds + static_cast<uint32_t>(k * 8), b0 + k * 128, kDescHi, idesc_o,
+                                (!first || k > 0) ? 1u : 0u);
         };
         ptx::mbar_wait(q_full, n_item & 1u);
         ptx::mbar_wait(&kv_full[n_step & 1u], (n_step >> 1) & 1u);
@@ -565,7 +570,8 @@ attn_tc_gen_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
     }
   } else {
     // ------------------------------------------------------------------ element-wise + drain: one thread per query row
-    const int t = (warp - 2) >> 2;
+    const int t = ((warp - 2) >> 2) & 1;         // query tile
+    const int half = (warp - 2) >> 3;            // which 32-key half of every chunk this warp converts
     const int q = warp & 3;
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(t * 256);
     const float sl2 = p.scale_log2, scale = p.scale;
@@ -585,18 +591,20 @@ attn_tc_gen_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
         ptx::mbar_wait(&s_full[t], n_sfull & 1u);
         ++n_sfull;
         ptx::tc_fence_after();
-#pragma unroll 1
-        for (int sub = 0; sub < DKC / 32; ++sub) {
+        {
+          const int sub = half;
           const int kb = key0 + sub * 32;
           uint32_t pk[16];
           if (kb >= p.T) {
 #pragma unroll
             for (int j = 0; j < 16; ++j) pk[j] = 0u;
+            pair_sync(t * 4 + q);
           } else {
             uint32_t rs[32], rp[32];
             ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(sub * 32), rs);
             ptx::tmem_ld_32x32(t_row + 64u + static_cast<uint32_t>(sub * 32), rp);
             ptx::tmem_ld_wait();
+            pair_sync(t * 4 + q);
             const bool full = kb + 32 <= p.T;
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
@@ -623,7 +631,7 @@ attn_tc_gen_dq_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_con
       ptx::tc_fence_after();
       bf16* orow = dqkv + (static_cast<int64_t>(b) * p.T + row) * (3 * static_cast<int64_t>(E)) + h * HS;
 #pragma unroll
-      for (int c = 0; c < (HS + 31) / 32; ++c) {
+      for (int c = half; c < (HS + 31) / 32; c += 2) {   // the two warps of a quarter split the 32-column groups
         uint32_t r[32];
         ptx::tmem_ld_32x32(t_row + 128u + static_cast<uint32_t>(c * 32), r);
         ptx::tmem_ld_wait();
@@ -681,7 +689,7 @@ int launch_gen_dq(const bf16* qkv, const bf16* d_o, const float* lse, const floa
   p.scale = scale;
   p.scale_log2 = scale * kGLog2e;
   const int grid = p.items < num_sms() ? p.items : num_sms();
-  VB_CHECK_CUDA(launch_pdl(attn_tc_gen_dq_kernel<HS>, dim3(grid), dim3(kGenThreads), Cfg::SMEM_BYTES, stream, 1, tq,
+  VB_CHECK_CUDA(launch_pdl(attn_tc_gen_dq_kernel<HS>, dim3(grid), dim3(kBwdGenThreads), Cfg::SMEM_BYTES, stream, 1, tq,
                            tkv, tdo, lse, delta, dqkv, p));
   VB_CHECK_LAUNCH();
   return kOk;
@@ -719,7 +727,7 @@ struct DkvParams {
 };
 
 template <int HS>
-__global__ void __launch_bounds__(kGenThreads, 1)
+__global__ void __launch_bounds__(kBwdGenThreads, 1)
 attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_constant__ CUtensorMap tm_q,
                        const __grid_constant__ CUtensorMap tm_do, const float* __restrict__ lse,
                        const float* __restrict__ delta, bf16* __restrict__ dqkv, const DkvParams p) {
@@ -756,10 +764,10 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&s_full[s], 1);
-      ptx::mbar_init(&ready[s], 4);
+      ptx::mbar_init(&ready[s], 8);
     }
     ptx::mbar_init(o_full, 1);
-    ptx::mbar_init(o_free, 8);
+    ptx::mbar_init(o_free, 16);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -817,19 +825,15 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
           ptx::tc_fence_after();
           const uint32_t cq = sc + st * Cfg::STAGE_BYTES, cdo = cq + Cfg::C_BYTES;
           const uint32_t d = tmem_base + static_cast<uint32_t>(slot * 128);
+          // independent accumulator chains, alternated; lean descriptor arithmetic
+          const uint32_t ka0 = ptx::smem_desc_lo(sk, 16), qb0 = ptx::smem_desc_lo(cq, 16);
+          const uint32_t va0 = ptx::smem_desc_lo(sv, 16), ob0 = ptx::smem_desc_lo(cdo, 16);
 #pragma unroll
           for (int k = 0; k < Cfg::HSK; ++k) {
             const int j = k >> 2, kk = k & 3;
-            const uint64_t da = ptx::make_smem_desc_sw128(sk + j * Cfg::ATOM_T + kk * 32, 16, 1024);
-            const uint64_t db = ptx::make_smem_desc_sw128(cq + j * Cfg::ATOM_C + kk * 32, 16, 1024);
-            ptx::umma_f16(d, da, db, idesc_s, k > 0 ? 1u : 0u);
-          }
-#pragma unroll
-          for (int k = 0; k < Cfg::HSK; ++k) {
-            const int j = k >> 2, kk = k & 3;
-            const uint64_t da = ptx::make_smem_desc_sw128(sv + j * Cfg::ATOM_T + kk * 32, 16, 1024);
-            const uint64_t db = ptx::make_smem_desc_sw128(cdo + j * Cfg::ATOM_C + kk * 32, 16, 1024);
-            ptx::umma_f16(d + 64u, da, db, idesc_s, k > 0 ? 1u : 0u);
+            const uint32_t oa = (j * Cfg::ATOM_T + kk * 32) >> 4, ob = (j * Cfg::ATOM_C + kk * 32) >> 4;
+            ptx::umma_f16_lh(d, ka0 + oa, qb0 + ob, kDescHi, idesc_s, k > 0 ? 1u : 0u);
+            ptx::umma_f16_lh(d + 64u, va0 + oa, ob0 + ob, kDescHi, idesc_s, k > 0 ? 1u : 0u);
           }
           ptx::umma_commit(&s_full[slot]);
         };
@@ -838,16 +842,13 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
           const uint32_t st = g % kKvStages;
           const uint32_t cq = sc + st * Cfg::STAGE_BYTES, cdo = cq + Cfg::C_BYTES;
           const uint32_t a = tmem_base + static_cast<uint32_t>(slot * 128);
+          const uint32_t db0 = ptx::smem_desc_lo(cdo, Cfg::ATOM_C), qb0 = ptx::smem_desc_lo(cq, Cfg::ATOM_C);
 #pragma unroll
-          for (int k = 0; k < KQC / 16; ++k) {   // dV += P^T dO_c
-            const uint64_t db = ptx::make_smem_desc_sw128(cdo + k * 2048, Cfg::ATOM_C, 1024);
-            ptx::umma_f16_ts(tmem_base + 256u, a + static_cast<uint32_t>(k * 8), db, idesc_o, (!first || k > 0) ? 1u : 0u);
-          }
-#pragma unroll
-          for (int k = 0; k < KQC / 16; ++k) {   // dK += dS^T Q_c
-            const uint64_t db = ptx::make_smem_desc_sw128(cq + k * 2048, Cfg::ATOM_C, 1024);
-            ptx::umma_f16_ts(tmem_base + 384u, a + 64u + static_cast<uint32_t>(k * 8), db, idesc_o,
-                             (!first || k > 0) ? 1u : 0u);
+          for (int k = 0; k < KQC / 16; ++k) {   // dV += P^T dO_c and dK += dS^T Q_c, alternated
+            ptx::umma_f16_ts_lh(tmem_base + 256u, a + static_cast<uint32_t>(k * 8), db0 + k * 128, kDescHi, idesc_o,
+                                (!first || k > 0) ? 1u : 0u);
+            ptx::umma_f16_ts_lh(tmem_base + 384u, a + 64u + static_cast<uint32_t>(k * 8), qb0 + k * 128, kDescHi,
+                                idesc_o, (!first || k > 0) ? 1u : 0u);
           }
           ptx::umma_commit(&c_empty[st]);
         };
@@ -877,7 +878,8 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
     }
   } else {
     // ------------------------------------------------------------------ element-wise groups: one thread per key row
-    const int g = (warp - 2) >> 2;               // group = tensor-memory slot = chunk parity
+    const int g = ((warp - 2) >> 2) & 1;         // group = tensor-memory slot = chunk parity
+    const int half = (warp - 2) >> 3;            // which 32-query half of every chunk this warp converts
     const int q = warp & 3;
     const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
     const uint32_t t_slot = t_lane + static_cast<uint32_t>(g * 128);
@@ -891,28 +893,26 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
       const float* dl_bh = delta + static_cast<int64_t>(bh) * p.T;
       for (int c = g; c < n; c += 2) {
         const int q0 = c * KQC;
-        // statistics of query columns q0 + lane and q0 + 32 + lane; columns past the last query: lse = +inf => P = 0
-        const int qa = q0 + lane, qb = q0 + 32 + lane;
-        const float nl_a = qa < p.T ? -__ldg(lse_bh + qa) * kGLog2e : -INFINITY;
-        const float nl_b = qb < p.T ? -__ldg(lse_bh + qb) * kGLog2e : -INFINITY;
-        const float dl_a = qa < p.T ? __ldg(dl_bh + qa) : 0.f;
-        const float dl_b = qb < p.T ? __ldg(dl_bh + qb) : 0.f;
+        // statistics of query column q0 + 32*half + lane; columns past the last query: lse = +inf => P = 0
+        const int qa = q0 + half * 32 + lane;
+        const float nl_mine = qa < p.T ? -__ldg(lse_bh + qa) * kGLog2e : -INFINITY;
+        const float dl_mine = qa < p.T ? __ldg(dl_bh + qa) : 0.f;
         ptx::mbar_wait(&s_full[g], n_sfull & 1u);
         ++n_sfull;
         ptx::tc_fence_after();
-#pragma unroll
-        for (int sub = 0; sub < KQC / 32; ++sub) {
+        {
+          const int sub = half;
           uint32_t pkp[16], pkd[16];
           if (q0 + sub * 32 >= p.T) {            // warp-uniform
 #pragma unroll
             for (int j = 0; j < 16; ++j) { pkp[j] = 0u; pkd[j] = 0u; }
+            pair_sync(g * 4 + q);
           } else {
             uint32_t rs[32], rp[32];
             ptx::tmem_ld_32x32(t_slot + static_cast<uint32_t>(sub * 32), rs);
             ptx::tmem_ld_32x32(t_slot + 64u + static_cast<uint32_t>(sub * 32), rp);
             ptx::tmem_ld_wait();
-            const float nl_mine = sub == 0 ? nl_a : nl_b;
-            const float dl_mine = sub == 0 ? dl_a : dl_b;
+            pair_sync(g * 4 + q);
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               const float nl0 = __shfl_sync(0xffffffffu, nl_mine, 2 * j), nl1 = __shfl_sync(0xffffffffu, nl_mine, 2 * j + 1);
@@ -941,7 +941,7 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
                    h * HS;
       const uint32_t t_acc = t_lane + (g == 0 ? 256u : 384u);
 #pragma unroll
-      for (int c = 0; c < (HS + 31) / 32; ++c) {
+      for (int c = half; c < (HS + 31) / 32; c += 2) {   // the two warps of a quarter split the 32-column groups
         uint32_t r[32];
         ptx::tmem_ld_32x32(t_acc + static_cast<uint32_t>(c * 32), r);
         ptx::tmem_ld_wait();
@@ -999,7 +999,7 @@ int launch_gen_dkv(const bf16* qkv, const bf16* d_o, const float* lse, const flo
   p.scale = scale;
   p.scale_log2 = scale * kGLog2e;
   const int grid = p.items < num_sms() ? p.items : num_sms();
-  VB_CHECK_CUDA(launch_pdl(attn_tc_gen_dkv_kernel<HS>, dim3(grid), dim3(kGenThreads), Cfg::SMEM_BYTES, stream, 1, tkv,
+  VB_CHECK_CUDA(launch_pdl(attn_tc_gen_dkv_kernel<HS>, dim3(grid), dim3(kBwdGenThreads), Cfg::SMEM_BYTES, stream, 1, tkv,
                            tq, tdo, lse, delta, dqkv, p));
   VB_CHECK_LAUNCH();
   return kOk;
