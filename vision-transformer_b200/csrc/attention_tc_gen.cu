@@ -49,6 +49,9 @@ struct GenCfg {
 struct GenParams {
   int T, H, npair, nchunk, items;   // npair = ceil(T / 256), nchunk = ceil(T / 128), items = B * H * npair
   float scale_log2;                 // scale * log2(e)
+  int dbg;                          // timing experiments only (VITB200_ATTN_DBG), 0 in production:
+                                    // 1 = the max pass reads no tensor memory, 2 = no ex2, 4 = pass 2 reads/writes no
+                                    // tensor memory (results are wrong in all three)
 };
 
 template <int HS>
@@ -238,6 +241,7 @@ attn_tc_gen_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restr
           for (int sub = 0; sub < GKC / 32; ++sub) {
             const int kb = key0 + sub * 32;
             if (kb >= p.T) break;                // warp-uniform
+            if (p.dbg & 1) { mx0 = 0.f; continue; }
             uint32_t r[32];
             ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(sub * 32), r);
             ptx::tmem_ld_wait();
@@ -268,11 +272,23 @@ attn_tc_gen_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restr
             if (kb >= p.T) {
 #pragma unroll
               for (int j = 0; j < 16; ++j) pk[j] = 0u;
+            } else if (p.dbg & 4) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) pk[j] = 0x3c003c00u;
+              l0 += 1.f;
+              continue;
             } else {
               uint32_t r[32];
               ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(sub * 32), r);
               ptx::tmem_ld_wait();
-              if (kb + 32 <= p.T) {
+              if (p.dbg & 2) {
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                  const float p0 = fmaf(__uint_as_float(r[2 * j]), sl2, mneg), p1 = fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg);
+                  l0 += p0; l1 += p1;
+                  pk[j] = pack_bf16x2(p0, p1);
+                }
+              } else if (kb + 32 <= p.T) {
 #pragma unroll
                 for (int j = 0; j < 16; j += 2) {
                   const float p0 = ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg));
@@ -368,6 +384,8 @@ int launch_gen_fwd(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, 
   p.nchunk = ceil_div(T, GKC);
   p.items = B * H * p.npair;
   p.scale_log2 = scale * kGLog2e;
+  static const int dbg = getenv("VITB200_ATTN_DBG") ? atoi(getenv("VITB200_ATTN_DBG")) : 0;
+  p.dbg = dbg;
   ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * static_cast<double>(T) * HS, 1, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
   VB_CHECK_CUDA(launch_pdl(attn_tc_gen_fwd_kernel<HS>, dim3(grid), dim3(kGenThreads), Cfg::SMEM_BYTES, stream, 1, tm,
@@ -706,7 +724,7 @@ int launch_gen_dq(const bf16* qkv, const bf16* d_o, const float* lse, const floa
 // MMAs of chunk c+2 and the output MMAs of chunk c+1 run while a group works on chunk c.  The per-QUERY statistics are
 // per-column here: each lane holds them for two columns of the chunk and they are broadcast with warp shuffles.
 constexpr int KQC = 64;                  // queries per chunk
-constexpr int kKvStages = 3;
+constexpr int kKvStages = 3;             // 5 stages measured slower (958 vs 888 us per ViT-H/14 layer backward)
 
 template <int HS>
 struct DkvCfg {
@@ -724,6 +742,7 @@ struct DkvCfg {
 struct DkvParams {
   int T, H, ntile, nchunk, items;   // ntile = ceil(T / 128), nchunk = ceil(T / 64), items = B * H * ntile
   float scale, scale_log2;
+  int dbg;                          // timing experiments only (VITB200_ATTN_DBG): 1 = element-wise pass does nothing
 };
 
 template <int HS>
@@ -740,13 +759,13 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_c + kKvStages * Cfg::STAGE_BYTES);
   uint64_t* kv_full = bars;             // [1] K and V tile landed
   uint64_t* kv_empty = bars + 1;        // [1] last S/dP of the item retired
-  uint64_t* c_full = bars + 2;          // [3] chunk ring
-  uint64_t* c_empty = bars + 5;         // [3]
-  uint64_t* s_full = bars + 8;          // [2] per slot: S^T and dP^T in tensor memory
-  uint64_t* ready = bars + 10;          // [2] per slot: P^T and dS^T written
-  uint64_t* o_full = bars + 12;         // [1] dV and dK complete
-  uint64_t* o_free = bars + 13;         // [1] both accumulators drained (8 warps)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* c_full = bars + 2;                     // [kKvStages] chunk ring
+  uint64_t* c_empty = c_full + kKvStages;          // [kKvStages]
+  uint64_t* s_full = c_empty + kKvStages;          // [2] per slot: S^T and dP^T in tensor memory
+  uint64_t* ready = s_full + 2;                    // [2] per slot: P^T and dS^T written
+  uint64_t* o_full = ready + 2;                    // [1] dV and dK complete
+  uint64_t* o_free = o_full + 1;                   // [1] both accumulators drained (16 warps)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int E = p.H * HS;
@@ -903,6 +922,9 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
         {
           const int sub = half;
           uint32_t pkp[16], pkd[16];
+          if (p.dbg & 1) {
+            // nothing
+          } else
           if (q0 + sub * 32 >= p.T) {            // warp-uniform
 #pragma unroll
             for (int j = 0; j < 16; ++j) { pkp[j] = 0u; pkd[j] = 0u; }
@@ -925,8 +947,10 @@ attn_tc_gen_dkv_kernel(const __grid_constant__ CUtensorMap tm_kv, const __grid_c
               pkd[j] = pack_bf16x2(d0, d1);
             }
           }
-          ptx::tmem_st_32x16(t_slot + static_cast<uint32_t>(sub * 16), pkp);
-          ptx::tmem_st_32x16(t_slot + 64u + static_cast<uint32_t>(sub * 16), pkd);
+          if (!(p.dbg & 1)) {
+            ptx::tmem_st_32x16(t_slot + static_cast<uint32_t>(sub * 16), pkp);
+            ptx::tmem_st_32x16(t_slot + 64u + static_cast<uint32_t>(sub * 16), pkd);
+          }
         }
         ptx::tmem_st_wait();
         ptx::tc_fence_before();
@@ -998,6 +1022,8 @@ int launch_gen_dkv(const bf16* qkv, const bf16* d_o, const float* lse, const flo
   p.items = B * H * p.ntile;
   p.scale = scale;
   p.scale_log2 = scale * kGLog2e;
+  static const int dbg = getenv("VITB200_ATTN_DBG") ? atoi(getenv("VITB200_ATTN_DBG")) : 0;
+  p.dbg = dbg;
   const int grid = p.items < num_sms() ? p.items : num_sms();
   VB_CHECK_CUDA(launch_pdl(attn_tc_gen_dkv_kernel<HS>, dim3(grid), dim3(kBwdGenThreads), Cfg::SMEM_BYTES, stream, 1, tkv,
                            tq, tdo, lse, delta, dqkv, p));
