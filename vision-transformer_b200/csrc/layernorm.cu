@@ -568,7 +568,8 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
                  1, stream);
   // ---- ring kernel
   if ((E & 7) == 0 && E <= 1536 && M >= 4 * LNB_WARPS) {
-    const int nwarps = E <= 1024 ? LNB_WARPS : 4;   // wide rows: fewer, deeper rings
+    static const int wide_warps = getenv("VITB200_LNB_WIDE_WARPS") ? atoi(getenv("VITB200_LNB_WIDE_WARPS")) : 6;
+    const int nwarps = E <= 1024 ? LNB_WARPS : wide_warps;   // wide rows: fewer, deeper rings (6 warps: 4.15 -> 4.80 TB/s at E=1280 with dropout live)
     const size_t stage = static_cast<size_t>(E) * (4 + (add_to_g ? 4 : 0) + (dy_bf16 ? 2 : 4));
     const size_t fixed = static_cast<size_t>(E) * 16 + LNB_WARPS * LNB_MAX_STAGES * 8;
     int nst = static_cast<int>((216 * 1024 - fixed) / (nwarps * stage));
