@@ -95,6 +95,28 @@ __global__ void im2col_u8_kernel(const uint8_t* __restrict__ x, OutT* __restrict
   }
 }
 
+// Patch-embedding weight rows whose length is not a multiple of 8 (P = 14: K = 588): bf16 copy with every row
+// zero-padded to Kpad, so that the row pitch is TMA-legal (16 B) and the tensor-core GEMM can run on it; and the
+// inverse for the weight gradient (fp32 [rows, Kpad] scratch accumulated into the dense [rows, K] gradient).
+__global__ void cast_pad_rows_kernel(const float* __restrict__ w, bf16* __restrict__ out, int rows, int K, int Kpad) {
+  const int64_t total = static_cast<int64_t>(rows) * Kpad;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int k = static_cast<int>(i % Kpad);
+    const int64_t r = i / Kpad;
+    out[i] = from_f32<bf16>(k < K ? w[r * K + k] : 0.f);
+  }
+}
+__global__ void add_unpad_rows_kernel(float* __restrict__ dst, const float* __restrict__ src, int rows, int K, int Kpad) {
+  const int64_t total = static_cast<int64_t>(rows) * K;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int k = static_cast<int>(i % K);
+    const int64_t r = i / K;
+    dst[i] += src[r * Kpad + k];
+  }
+}
+
 // out[b, N, :] = cls[b, :] + pos[N, :]   (CLS appended LAST: reference vit.py:41-42)
 __global__ void cls_rows_kernel(const float* __restrict__ cls, const float* __restrict__ pos, float* __restrict__ out,
                                 int B, int T, int E) {
@@ -490,6 +512,19 @@ int cross_entropy(const float* logits, const int64_t* labels, float* loss, float
                   float grad_scale, cudaStream_t s) {
   ProfScope prof(kProfEltwise, 0.0, 1, s);
   ce_kernel<<<1, 1024, 0, s>>>(logits, labels, loss, dlogits, B, C, grad_scale);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int cast_pad_rows(const float* w, bf16* out, int rows, int K, int Kpad, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
+  cast_pad_rows_kernel<<<grid_for(static_cast<int64_t>(rows) * Kpad, 256), 256, 0, s>>>(w, out, rows, K, Kpad);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+int add_unpad_rows(float* dst, const float* src, int rows, int K, int Kpad, cudaStream_t s) {
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
+  add_unpad_rows_kernel<<<grid_for(static_cast<int64_t>(rows) * K, 256), 256, 0, s>>>(dst, src, rows, K, Kpad);
   VB_CHECK_LAUNCH();
   return kOk;
 }

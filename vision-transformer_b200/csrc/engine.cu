@@ -68,15 +68,30 @@ inline uint64_t drop_stream(int layer, int which) { return static_cast<uint64_t>
 // ------------------------------------------------------------------------------------------------ embed
 struct EmbedGeom {
   int N, K, Kpad;
-  bool lp;  // patch GEMM runs on the bf16 tensor-core path
+  bool lp;   // patch GEMM runs on the bf16 tensor-core path
+  bool pad;  // K = C*P*P is not a multiple of 8 (P = 14): operands are zero-padded to Kpad columns, the bf16 weight is
+             // re-padded from the fp32 master in the stage's own buffer, dW goes through a padded fp32 scratch
 };
 EmbedGeom embed_geom(const vitb200_dims* d) {
   EmbedGeom g;
   g.N = (d->Hi / d->P) * (d->Wi / d->P);
   g.K = d->C * d->P * d->P;
-  g.lp = is_bf16(d) && (g.K % 8 == 0);
-  g.Kpad = g.K;
+  g.lp = is_bf16(d);
+  g.pad = g.lp && (g.K % 8 != 0);
+  g.Kpad = g.pad ? (g.K + 7) / 8 * 8 : g.K;
   return g;
+}
+struct EmbedBufs { void* A; void* dY; bf16* w_pad; float* dw_pad; };
+EmbedBufs carve_embed(const vitb200_dims* d, const EmbedGeom& g, void* base, size_t* total = nullptr) {
+  Carver c(base);
+  EmbedBufs b;
+  const size_t rows = static_cast<size_t>(d->B) * g.N, es = g.lp ? 2 : 4;
+  b.A = c.take(rows * g.Kpad * es);        // im2col
+  b.dY = c.take(rows * d->E * es);         // backward: compacted gradient of the patch rows
+  b.w_pad = g.pad ? c.take<bf16>(static_cast<size_t>(d->E) * g.Kpad * 2) : nullptr;
+  b.dw_pad = g.pad ? c.take<float>(static_cast<size_t>(d->E) * g.Kpad * 4) : nullptr;
+  if (total) *total = c.off;
+  return b;
 }
 
 // ------------------------------------------------------------------------------------------------ head
@@ -163,9 +178,9 @@ extern "C" {
 // ================================================================================================ embed
 int64_t vitb200_embed_act_bytes(const vitb200_dims* d) {
   const EmbedGeom g = embed_geom(d);
-  const size_t rows = static_cast<size_t>(d->B) * g.N;
-  // A (im2col) and, in backward, the compacted dY [B*N, E]
-  return static_cast<int64_t>(align256(rows * g.Kpad * (g.lp ? 2 : 4)) + align256(rows * d->E * (g.lp ? 2 : 4)));
+  size_t total = 0;
+  carve_embed(d, g, nullptr, &total);
+  return static_cast<int64_t>(total);
 }
 
 // images_f32 XOR images_u8 (u8_layout: 0 NCHW, 1 NHWC; the ToTensor /255 is fused into the gather)
@@ -176,15 +191,17 @@ static int embed_forward(const vitb200_dims* d, const vitb200_embed_params* p, c
   const EmbedGeom g = embed_geom(d);
   VB_REQUIRE(g.N + 1 == d->T, "num_patches (%d) != (H/P)*(W/P) (%d): pos_embd add would fail (reference vit.py:42)",
              d->T - 1, g.N);
-  VB_REQUIRE(!g.lp || p->w_lp != nullptr, "embed: bf16 weight copy missing");
-  Carver c(acts);
-  void* A = c.take(static_cast<size_t>(d->B) * g.N * g.Kpad * (g.lp ? 2 : 4));
+  VB_REQUIRE(!g.lp || g.pad || p->w_lp != nullptr, "embed: bf16 weight copy missing");
+  const EmbedBufs eb = carve_embed(d, g, acts);
+  void* A = eb.A;
+  if (g.pad) VB_PROPAGATE(cast_pad_rows(p->w_f32, eb.w_pad, d->E, g.K, g.Kpad, s));
   if (images_u8) VB_PROPAGATE(im2col_u8(images_u8, u8_layout, A, g.lp, d->B, d->C, d->Hi, d->Wi, d->P, g.Kpad, s));
   else VB_PROPAGATE(im2col(images, A, g.lp, d->B, d->C, d->Hi, d->Wi, d->P, g.Kpad, s));
   Lin l;
-  l.M = d->B * g.N; l.N = d->E; l.K = g.K;
+  l.M = d->B * g.N; l.N = d->E; l.K = g.Kpad;   // pad columns are zero in both operands
   l.A = A; l.lda = g.Kpad;
-  l.B = g.lp ? p->w_lp : static_cast<const void*>(p->w_f32); l.ldb = g.K;
+  l.B = g.pad ? static_cast<const void*>(eb.w_pad) : g.lp ? p->w_lp : static_cast<const void*>(p->w_f32);
+  l.ldb = g.Kpad;
   l.ep = make_ep(x_out, d->E);
   l.ep.bias = p->bias;
   l.ep.row_add = p->pos;           // + pos[token]
@@ -214,21 +231,23 @@ int vitb200_embed_bwd(const vitb200_dims* d, const vitb200_embed_grads* gr, cons
   const EmbedGeom g = embed_geom(d);
   const size_t rows = static_cast<size_t>(d->B) * g.N;
   const void* A = acts;
-  // dY lives after A in the same carve order as forward
-  Carver c(scratch);
-  c.take(rows * g.Kpad * (g.lp ? 2 : 4));
-  void* dY = c.take(rows * d->E * (g.lp ? 2 : 4));
+  // dY (and the padded dW scratch) live after A in the same carve order as forward
+  const EmbedBufs eb = carve_embed(d, g, scratch);
+  void* dY = eb.dY;
   VB_PROPAGATE(embed_bwd_reduce(g_in, gr->pos, gr->cls, dY, g.lp, d->B, d->T, d->E, s));
   VB_PROPAGATE(colsum(dY, g.lp, d->E, gr->bias, static_cast<int>(rows), d->E, s));
   Lin l;  // dW[E, K] += dY^T[E, rows] @ A[rows, K]
-  l.M = d->E; l.N = g.K; l.K = static_cast<int>(rows);
+  l.M = d->E; l.N = g.Kpad; l.K = static_cast<int>(rows);
   l.a_major = 1; l.b_major = 1;
   l.A = dY; l.lda = d->E;
   l.B = A; l.ldb = g.Kpad;
-  l.ep = make_ep(gr->w, g.K);
+  l.ep = make_ep(g.pad ? eb.dw_pad : gr->w, g.Kpad);
   l.ep.accumulate = 1;
   l.out_f32 = true;
-  return run_lin(g.lp, l, s);
+  if (g.pad) VB_CHECK_CUDA(cudaMemsetAsync(eb.dw_pad, 0, static_cast<size_t>(d->E) * g.Kpad * 4, s));
+  VB_PROPAGATE(run_lin(g.lp, l, s));
+  if (g.pad) VB_PROPAGATE(add_unpad_rows(gr->w, eb.dw_pad, d->E, g.K, g.Kpad, s));
+  return kOk;
 }
 
 // ================================================================================================ head

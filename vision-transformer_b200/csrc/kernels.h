@@ -80,6 +80,8 @@ int gelu_backward(const float* x, float* dy_inout, int64_t n, cudaStream_t s);
 int cross_entropy(const float* logits, const int64_t* labels, float* loss, float* dlogits, int B, int C,
                   float grad_scale, cudaStream_t s);
 int cast_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t s);
+int cast_pad_rows(const float* w, bf16* out, int rows, int K, int Kpad, cudaStream_t s);
+int add_unpad_rows(float* dst, const float* src, int rows, int K, int Kpad, cudaStream_t s);
 int mask_cast(const float* g, void* out, bool out_bf16, const Dropout& drop, int64_t n, cudaStream_t s);
 int dropout_mask(uint8_t* keep, int64_t n, const Dropout& drop, cudaStream_t s);
 
