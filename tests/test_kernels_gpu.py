@@ -213,7 +213,10 @@ def _attn_ref(qkv, B, T, H, hs, scale):
                                        (5, 256, 2, 64), (3, 128, 1, 64), (2, 100, 3, 64), (7, 5, 2, 64), (40, 129, 12, 64),
                                        # long rows / wide heads: the chunked tcgen05 kernels of attention_tc_gen.cu (bf16)
                                        (2, 300, 3, 64), (1, 1000, 2, 96), (2, 130, 2, 128), (3, 40, 2, 80),
-                                       (2, 730, 2, 80), (3, 257, 1, 128), (20, 577, 16, 80)])
+                                       (2, 730, 2, 80), (3, 257, 1, 128), (20, 577, 16, 80),
+                                       # chunk / tile boundaries of those kernels
+                                       (2, 5, 2, 80), (1, 64, 1, 96), (1, 128, 1, 128), (2, 129, 1, 80), (1, 256, 2, 80),
+                                       (1, 65, 1, 128), (2, 512, 1, 80)])
 def test_attention_fwd_bwd(lib, dt, B, T, H, hs):
     C = _C()
     torch.manual_seed(5)
