@@ -580,8 +580,12 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
       const int grid = std::min(num_sms(), ceil_div(M, nwarps));
 #define VB_LN_RING(T, C)                                                                                          \
   do {                                                                                                            \
-    VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C, (C <= 8)>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                       static_cast<int>(smem)));                                                  \
+    static bool attr_set = false; /* one flag per instantiation: the opt-in is the 216 KB bound, not this call's size */ \
+    if (!attr_set) {                                                                                              \
+      VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C, (C <= 8)>,                                      \
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));               \
+      attr_set = true;                                                                                            \
+    }                                                                                                             \
     VB_CHECK_CUDA(launch_pdl(ln_bwd_ring_kernel<T, C, (C <= 8)>, dim3(grid), dim3(nwarps * 32), smem, stream, 1,    \
                              static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta,         \
                              static_cast<T*>(dyn), dyn_colsum, drop, M, E, nst));                                 \
