@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-module-path", action="store_true", help="skip the drop-in nn.Module side number")
     ap.add_argument("--no-row0", action="store_true", help="skip the last-block dead-row-elimination side number")
+    ap.add_argument("--no-ref-eager", action="store_true", help="skip the reference-eager-on-this-GPU side number")
     ap.add_argument("--bucket-mb", type=float, default=48)
     return ap.parse_args()
 
@@ -114,14 +115,71 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------------- CPU arms
-def cpu_sample(args, batch, steps, warmup):
-    """Oracle port of the reference's CPU path (oracle/cpu_step.py) on `batch` images per step."""
+def cpu_sample(args, batch, steps, warmup, wl=None):
+    """One CPU arm sample: the reference's OWN modules + step lines (oracle/ref_step.py over the sources staged in
+    oracle/_ref/py by oracle/Makefile) when staged -> kind "reference"; else the restated port (oracle/cpu_step.py)
+    -> kind "port".  All host threads.  -> (images/s, s/step, host description, threads, kind)"""
     import torch
-    from oracle import cpu_step
-    tr = cpu_step.CpuTrainer(batch_size=batch, **workload(args))
-    sec = cpu_step.time_steps(tr, steps, warmup)
+    from oracle import cpu_step, ref_loader, ref_step
+    threads = ref_step.use_all_host_threads()
+    wl = wl or workload(args)
+    if ref_loader.available():
+        tr = ref_step.RefTrainer(batch_size=batch, device="cpu", **wl)
+        sec, _ = ref_step.time_steps(tr, steps, warmup)
+        kind = "reference"
+    else:
+        tr = cpu_step.CpuTrainer(batch_size=batch, **wl)
+        sec = cpu_step.time_steps(tr, steps, warmup)
+        kind = "port"
     host = cpu_step.host_description()
-    return batch / sec, sec, host, torch.get_num_threads()
+    return batch / sec, sec, host, threads, kind
+
+
+def c1_sample():
+    """BASELINE.json configs[0]: the repo-default ViT of src/train.py:126-139 (E=4, 4 heads, 4 blocks, batch 5) as a
+    CPU PyTorch fwd+bwd+AdamW step on 224x224x3 synthetic images (2 classes), plus the literal train.py variant
+    (256x256, 100 classes)."""
+    out = {}
+    for tag, img, classes in (("c1_224_2cls", 224, 2), ("c1_train_py_literal_256_100cls", 256, 100)):
+        wl = dict(input_channels=3, num_classes=classes, image_size=img, patch_size=16, embedding_size=4, num_heads=4,
+                  num_blocks=4)
+        try:
+            ips, sec, _, threads, kind = cpu_sample(None, 5, 5, 2, wl=wl)
+            out[tag] = {"value": ips, "unit": UNIT, "ms_per_step": sec * 1e3, "batch": 5, "cores": threads, "kind": kind,
+                        "sample": "5 steps x 5 images after 2 warm-up; fwd+CE+bwd+AdamW, dropout on, fp32"}
+        except Exception as e:  # a reported baseline must never fail the bench
+            out[tag] = {"error": repr(e)[:160]}
+    return out
+
+
+def reference_gpu_eager(args, dev):
+    """The competitor SURVEY section 0 names: the reference's modules, unchanged, in PyTorch eager on the SAME B200 with
+    the same workload (fp32 as train.py runs it, and under torch.autocast(bf16)).  Largest batch <= args.batch that
+    fits; dropout live; device-timed."""
+    import torch
+    from oracle import ref_loader, ref_step
+    if not ref_loader.available():
+        return {"unavailable": "reference sources not staged (make -C oracle)"}
+    out = {}
+    for tag, autocast in (("fp32", False), ("autocast_bf16", True)):
+        batch = args.batch
+        while batch >= 8:
+            try:
+                tr = ref_step.RefTrainer(batch_size=batch, device=str(dev), autocast=autocast, **workload(args))
+                sec, loss = ref_step.time_steps(tr, 5, 2)
+                out[tag] = {"value": batch / sec, "unit": UNIT, "ms_per_step": sec * 1e3, "batch": batch,
+                            "last_loss": loss, "peak_mem_gb": torch.cuda.max_memory_allocated(dev) / 2 ** 30}
+                del tr
+                break
+            except torch.OutOfMemoryError:
+                tr = None
+                torch.cuda.empty_cache()
+                batch //= 2
+        torch.cuda.empty_cache()
+        torch.cuda.reset_peak_memory_stats(dev)
+    out["what"] = ("oracle/_ref/py (the unmodified reference package) + train.py:89-98 step lines, PyTorch "
+                   f"{torch.__version__} eager, TF32 off, 5 steps after 2 warm-up, CUDA events")
+    return out
 
 
 def vit_c_sample(E, H, P, img):
@@ -151,28 +209,31 @@ def vit_c_sample(E, H, P, img):
 
 
 def run_reference(args):
-    """`--impl reference`: the reference's own CPU implementation of the step (its PyTorch path restated in
-    oracle/, since /root/reference is a Python tree that does not travel to the GPU box), all host threads."""
+    """`--impl reference`: the reference's own CPU implementation of the step — its unmodified modules staged in
+    oracle/_ref/py (else the oracle port) — on the box's host cores with ALL host threads (torchrun exports
+    OMP_NUM_THREADS=1; the thread count is reset and printed).  Rank 0 alone runs; other ranks exit 0."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import torch
     # size the per-step sample so that (steps + warmup) steps end within ~3 minutes
-    ips, _, _, _ = cpu_sample(args, 2, 1, 1)
+    ips, _, _, _, _ = cpu_sample(args, 2, 1, 1)
     budget = 170.0 / max(args.steps + args.warmup, 1)
     batch = int(max(1, min(16, ips * budget)))
-    ips, sec, host, threads = cpu_sample(args, batch, args.steps, args.warmup)
+    ips, sec, host, threads, kind = cpu_sample(args, batch, args.steps, args.warmup)
     E, H, L, P, img = MODELS[args.model]
     line = {
         "impl": "reference", "metric": METRIC, "value": ips, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.model} train step (fwd+CE+bwd+AdamW), {img}x{img}x3 synthetic, dropout 0.2, "
-                               f"{args.classes} classes; CPU sample of {batch} images per step",
+        "config": {"workload": f"{args.model} train step, {img}x{img}x3, {args.classes} cls, dropout on; "
+                               f"CPU sample {batch} img/step",
                    "global_batch": batch},
-        "cpu_baseline": {"value": ips, "unit": UNIT, "cores": threads, "kind": "port",
+        "cpu_baseline": {"value": ips, "unit": UNIT, "cores": threads, "kind": kind,
                          "sample": f"{args.steps} steps x {batch} images after {args.warmup} warm-up, torch "
-                                   f"{torch.__version__} CPU, {host['cpu_model']}, os.cpu_count={host['os_cpu_count']}"},
+                                   f"{torch.__version__} CPU, {threads} threads (OMP_NUM_THREADS env was "
+                                   f"{os.environ.get('OMP_NUM_THREADS')!r}, reset), {host['cpu_model']}, "
+                                   f"os.cpu_count={host['os_cpu_count']}"},
         "e2e": {"value": ips, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -310,7 +371,7 @@ def run_b200(args):
     row0 = None
     if not args.no_row0 and world == 1:
         alg = tr.flops_per_image()
-        del tr.blk_acts, tr.xs
+        del tr.blk_acts[:], tr.xs[:]
         torch.cuda.empty_cache()
         tr0 = train_dp.DPTrainer(batch_size=args.batch, dtype=dtype, device=dev, process_group=pg, world_size=world,
                                  bucket_mb=args.bucket_mb, seed=0, last_block_row0=True, **wl)
@@ -358,6 +419,20 @@ def run_b200(args):
                                "VisionTransformer package: synchronous .to(device) of a pinned fp32 batch, "
                                "model(x), CrossEntropyLoss, backward, torch.optim.AdamW, loss.item() every step"}
         del model, opt
+        if e2e is not None:
+            e2e["module_api"] = {"value": module_path["value"], "unit": UNIT, "ms_per_step": module_path["ms_per_step"],
+                                 "api": "the reference's train.py:91-98 lines on the drop-in nn.Module package"}
+
+    ref_eager = None
+    if not args.no_ref_eager and world == 1:
+        del tr.blk_acts[:], tr.xs[:]
+        torch.cuda.empty_cache()
+        torch.backends.cuda.matmul.allow_tf32 = False
+        torch.backends.cudnn.allow_tf32 = False
+        try:
+            ref_eager = reference_gpu_eager(args, dev)
+        except Exception as e:  # a side number must never fail the bench
+            ref_eager = {"error": repr(e)[:200]}
 
     if rank != 0:
         if world > 1:
@@ -368,11 +443,13 @@ def run_b200(args):
     if not args.no_cpu_baseline and world == 1:
         torch.cuda.synchronize()
         b, ksteps = 16, 8
-        ips, sec, host, threads = cpu_sample(args, b, ksteps, 1)
-        cpu = {"value": ips, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": f"{ksteps} steps x {b} images after 1 warm-up ({sec:.2f} s/step), oracle/cpu_step.py "
-                         f"(restated reference PyTorch path, fwd+CE+bwd+AdamW, dropout on), {host['cpu_model']}, "
+        ips, sec, host, threads, kind = cpu_sample(args, b, ksteps, 1)
+        cpu = {"value": ips, "unit": UNIT, "cores": threads, "kind": kind,
+               "sample": f"{ksteps} steps x {b} images after 1 warm-up ({sec:.2f} s/step), "
+                         f"{'the unmodified reference modules (oracle/_ref/py)' if kind == 'reference' else 'oracle/cpu_step.py port'}"
+                         f" + train.py:89-98 step lines (fwd+CE+bwd+AdamW, dropout on), {host['cpu_model']}, "
                          f"os.cpu_count={host['os_cpu_count']}",
+               "c1": c1_sample(),
                "vit_c": vit_c_sample(*[MODELS[args.model][i] for i in (0, 1, 3, 4)])}
 
     E, H, L, P, img = MODELS[args.model]
@@ -380,8 +457,8 @@ def run_b200(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": args.dtype, "data": "synthetic",
-        "config": {"workload": f"{args.model} train step (fwd + CE + bwd + grad all-reduce + AdamW), {img}x{img}x3 "
-                               f"synthetic images, {args.classes} classes, dropout 0.2 live, batch {args.batch}/GPU",
+        "config": {"workload": f"{args.model} B={args.batch}/GPU train step (fwd+CE+bwd+allreduce+AdamW), {img}x{img}x3, "
+                               f"{args.classes} cls, dropout on",
                    "global_batch": gb, "tokens_per_image": tr.T, "parallelism": f"dp{world}",
                    "l2_policy": "inputs (154 MB/step at B=256) and activations (~13 GB) exceed the 126 MB L2; "
                                 "no explicit flush",
@@ -391,7 +468,7 @@ def run_b200(args):
         "mfu": {"algorithmic_tflops_per_gpu": step_tflops, "of_measured_sustained": step_tflops / pk["tflops_sustained"],
                 "of_measured_burst": step_tflops / pk["tflops_burst"], "of_datasheet_2250": step_tflops / 2250.0},
         "kernels": kern, "loss_after": loss_after, "last_block_row0": row0,
-        "module_path": module_path,
+        "module_path": module_path, "reference_gpu_eager": ref_eager,
     }
     emit(line)
     if world > 1:

@@ -151,6 +151,12 @@ typedef struct {
 } vitb200_adamw_hyper;
 int vitb200_adamw_flat(float* p, const float* g, float* m, float* v, void* shadow_bf16, int64_t n,
                        vitb200_adamw_hyper h, void* stream);
+/* Range form (data-parallel trainer, ZeRO-1 shards): AdamW over n elements of arenas already offset to a 16-byte
+ * aligned range start.  g_bf16 != NULL: gradients are read from that bf16 buffer (reduce-scattered bf16 gradient
+ * exchange) instead of the fp32 g.  zero_grad != 0: the fp32 gradient range is cleared in the same pass
+ * (optimizer.zero_grad(), train.py:94 — the backward kernels accumulate into it). */
+int vitb200_adamw_range(float* p, float* g, const void* g_bf16, float* m, float* v, void* shadow_bf16, int64_t n,
+                        int zero_grad, vitb200_adamw_hyper h, void* stream);
 /* Multi-tensor form: device arrays of tensor addresses / sizes and a (block -> tensor, chunk of 65536) table. */
 int vitb200_adamw_multi(const uint64_t* p_ptrs, const uint64_t* g_ptrs, const uint64_t* m_ptrs,
                         const uint64_t* v_ptrs, const uint64_t* shadow_ptrs, const int64_t* sizes,
@@ -207,6 +213,10 @@ typedef struct {
 } vitb200_block_grads;
 int64_t vitb200_block_act_bytes(const vitb200_dims* d);
 int64_t vitb200_block_scratch_bytes(const vitb200_dims* d);
+/* Byte offset, inside a block's `acts` arena, of one saved tensor (-1: unknown id).  Lets the host export
+ * MultiHeadAttention.attention_probs (transformer.py:48) from the qkv a whole-model forward already stored. */
+enum { VITB200_ACT_QKV = 0, VITB200_ACT_ATTN = 1, VITB200_ACT_LSE = 2, VITB200_ACT_XMID = 3 };
+int64_t vitb200_block_act_offset(const vitb200_dims* d, int which);
 /* x_in, x_out fp32 [B*T, E] (may not alias).  acts: saved activations for backward (or scratch in eval). */
 int vitb200_block_fwd(const vitb200_dims* d, int layer, const vitb200_block_params* p, const float* x_in,
                       float* x_out, void* acts, void* stream);

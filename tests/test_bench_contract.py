@@ -16,7 +16,8 @@ def _run(env_extra):
 
 
 def test_reference_arm_prints_one_json_line_with_contract_keys():
-    r = _run({"RANK": "0", "WORLD_SIZE": "1"})
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to its children: the arm must reset the thread count itself
+    r = _run({"RANK": "0", "WORLD_SIZE": "1", "OMP_NUM_THREADS": "1"})
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
     assert len(lines) == 1, r.stdout
@@ -27,7 +28,10 @@ def test_reference_arm_prints_one_json_line_with_contract_keys():
         assert key in j, key
     assert j["value"] > 0 and j["e2e"]["value"] == j["value"]
     assert j["e2e"]["h2d_bytes_per_step"] == 0 and j["e2e"]["d2h_bytes_per_step"] == 0
-    assert j["cpu_baseline"]["kind"] == "port" and j["cpu_baseline"]["cores"] >= 1
+    from oracle import ref_loader
+    assert j["cpu_baseline"]["kind"] == ("reference" if ref_loader.available() else "port")
+    ncpu = min(os.cpu_count(), len(os.sched_getaffinity(0)))
+    assert j["cpu_baseline"]["cores"] == ncpu, (j["cpu_baseline"], ncpu)   # every host core, not torchrun's 1
     assert "workload" in j["config"] and "model" not in j["config"]
 
 

@@ -294,6 +294,93 @@ def test_batch_size_contract_and_no_grad(lib):
     assert torch.equal(a.detach(), b) and not b.requires_grad
 
 
+def test_no_grad_skips_the_activation_stash(lib):
+    """evaluate() of the reference runs under @torch.no_grad (train.py:28-44): the forward must then keep ONE scratch
+    arena and two ping-pong residual buffers instead of L saved-activation arenas (`needs_input_grad`
+    does not see grad mode)."""
+    cfg, c, sd, x, y = _synthetic_case(256, 4, 8, 16, 16, 224, 2, seed=5)
+    m = _build(c).eval()
+    m.load_state_dict(sd)
+    xs = x.to(DEV)
+    m(xs)                                              # warm the shadow caches / lazily created buffers
+    torch.cuda.synchronize()
+
+    def peak(no_grad):
+        torch.cuda.empty_cache()
+        torch.cuda.reset_peak_memory_stats()
+        base = torch.cuda.memory_allocated()
+        if no_grad:
+            with torch.no_grad():
+                out = m(xs)
+        else:
+            out = m(xs)
+        torch.cuda.synchronize()
+        return torch.cuda.max_memory_allocated() - base, out.detach().clone()
+
+    p_grad, a = peak(False)
+    p_nograd, b = peak(True)
+    assert torch.equal(a, b)
+    # 8 blocks stash 8 arenas with grad; without it one arena + 2 residual buffers: < 1/3 of the training peak
+    assert p_nograd < p_grad / 3, (p_nograd, p_grad)
+
+
+def test_whole_model_attention_probs_export(lib):
+    """The reference sets blocks[i].multi_head.attention_probs on EVERY forward (transformer.py:48) and the notebook /
+    make_golden.py read it after a whole-model forward; the drop-in fills it from the whole-model path when the
+    module opted in, and matches the reference fixture's probs0."""
+    g = load_golden("tiny")
+    m = _build(g["config"]).eval()
+    m.load_state_dict(g["state_dict"])
+    x = (g["images_u8"].float() / 255.0).to(DEV)
+    m(x)
+    assert m.transformer_encoder.blocks[0].multi_head.attention_probs is None     # opt-in: default None
+    for blk in m.transformer_encoder.blocks:
+        blk.multi_head.export_attention_probs = True
+    m(x)
+    p0 = m.transformer_encoder.blocks[0].multi_head.attention_probs
+    assert p0.shape == g["probs0"].shape
+    assert rel_err(p0, g["probs0"]) < 1e-5
+    with torch.no_grad():                                                        # same through the eval fast path
+        m(x)
+    assert rel_err(m.transformer_encoder.blocks[0].multi_head.attention_probs, g["probs0"]) < 1e-5
+    last = m.transformer_encoder.blocks[-1].multi_head.attention_probs
+    assert torch.allclose(last.sum(-1), torch.ones_like(last.sum(-1)), atol=1e-5)
+    # a Block called on its own exports too
+    blk = m.transformer_encoder.blocks[0]
+    xb = torch.randn(g["config"]["batch_size"], g["config"]["num_patches"] + 1, g["config"]["embedding_size"], device=DEV)
+    blk(xb)
+    assert blk.multi_head.attention_probs.shape == p0.shape
+
+
+def test_second_backward_raises_clearly_and_old_graph_keeps_its_weights(lib):
+    cfg, c, sd, x, y = _synthetic_case(64, 2, 2, 4, 8, 32, 2, seed=6)
+    m = _build(c, precision=torch.bfloat16).eval()
+    m.load_state_dict(sd)
+    xs, ys = x.to(DEV), y.to(DEV)
+    loss = torch.nn.functional.cross_entropy(m(xs).float(), ys)
+    loss.backward()
+    with pytest.raises(RuntimeError, match="already consumed|second time"):
+        loss.backward()
+    # forward A, in-place parameter update (as an optimizer step does), forward B, THEN backward of A: torch refuses
+    # this for its own ops (saved-tensor version check); the drop-in reads parameters through raw pointers, so it
+    # checks the versions itself instead of silently differentiating A with B's weights
+    m.zero_grad()
+    loss_a = torch.nn.functional.cross_entropy(m(xs).float(), ys)
+    with torch.no_grad():
+        for p in m.parameters():
+            p.add_(0.05 * torch.randn_like(p))
+    m(xs)
+    with pytest.raises(RuntimeError, match="modified by an inplace operation"):
+        loss_a.backward()
+    # updates through .data do not move the version counter: invalidate_shadows() is the documented escape hatch
+    m.zero_grad()
+    ref = m(xs).detach()
+    for p in m.parameters():
+        p.data.mul_(1.5)
+    m.invalidate_shadows()
+    assert rel_err(m(xs).detach(), ref) > 1e-3
+
+
 def test_training_mode_dropout_statistics_and_determinism(lib):
     """train(): dropout p=0.2 live (hard-coded, reference transformer.py:35,53); backward regenerates the same
     masks (gradient check by finite differences is impossible with fresh masks, so check grad consistency)."""

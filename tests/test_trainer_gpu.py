@@ -252,3 +252,45 @@ def test_two_rank_data_parallel_step_matches_oracle(lib):
         assert nb >= 3, "the test must exercise several buckets"
         assert worst < 1e-4, (r, worst)
         assert ok_step, r
+
+
+def test_trainer_rejects_bad_labels_and_out_of_range_targets(lib):
+    tr, cfg, sd, x, y = _make(torch.float32)
+    with pytest.raises(RuntimeError, match="int64"):
+        tr.step(x.cuda(), y.cuda().int())
+    with pytest.raises(RuntimeError, match="int64"):
+        tr.step(x.cuda(), y)                          # CPU labels
+    bad = y.clone()
+    bad[0] = 99                                       # out of range: torch device-asserts; here the loss turns NaN
+    loss = tr.step(x.cuda(), bad.cuda())
+    assert torch.isnan(loss).all()
+
+
+def test_adamw_range_bf16_gradients_and_fused_zero(lib):
+    """vitb200_adamw_range: a sub-range of the arena, gradients from a bf16 exchange buffer, fp32 gradient cleared."""
+    import ctypes
+    from VisionTransformer import _C
+    n, a, b = 10007, 1024, 9220                      # odd sizes: vector body + scalar tail
+    g = torch.Generator(device="cuda").manual_seed(0)
+    p = torch.randn(n, device="cuda", generator=g)
+    gr = torch.randn(n, device="cuda", generator=g)
+    gb = gr.to(torch.bfloat16)
+    m = torch.rand(n, device="cuda", generator=g) * 0.1
+    v = torch.rand(n, device="cuda", generator=g) * 0.01
+    sh = torch.zeros(n, dtype=torch.bfloat16, device="cuda")
+    p0, m0, v0, g0 = p.clone(), m.clone(), v.clone(), gr.clone()
+    h = _C.AdamWHyper(1e-3, 0.9, 0.999, 1e-8, 1e-2, 3, 0.5)
+    L = _C.lib()
+    _C.check(L.vitb200_adamw_range(p[a:].data_ptr(), gr[a:].data_ptr(), gb[a:].data_ptr(), m[a:].data_ptr(),
+                                   v[a:].data_ptr(), sh[a:].data_ptr(), b - a, 1, h, _C.stream_ptr()))
+    torch.cuda.synchronize()
+    for t, t0 in ((p, p0), (m, m0), (v, v0)):
+        assert torch.equal(t[:a], t0[:a]) and torch.equal(t[b:], t0[b:])
+    assert torch.equal(gr[:a], g0[:a]) and torch.equal(gr[b:], g0[b:]) and torch.count_nonzero(gr[a:b]) == 0
+    gg = gb[a:b].float() * 0.5
+    em = 0.9 * m0[a:b] + 0.1 * gg
+    ev = 0.999 * v0[a:b] + 0.001 * gg * gg
+    ep = p0[a:b] * (1 - 1e-3 * 1e-2) - (1e-3 / (1 - 0.9 ** 3)) * em / (ev.sqrt() / (1 - 0.999 ** 3) ** 0.5 + 1e-8)
+    assert torch.allclose(m[a:b], em, rtol=1e-6, atol=1e-8) and torch.allclose(v[a:b], ev, rtol=1e-6, atol=1e-10)
+    assert torch.allclose(p[a:b], ep, rtol=1e-5, atol=1e-7)
+    assert torch.equal(sh[a:b], p[a:b].to(torch.bfloat16)) and torch.count_nonzero(sh[:a]) == 0

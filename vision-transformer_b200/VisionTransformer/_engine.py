@@ -126,7 +126,12 @@ def cast_bf16(src, dst=None):
 
 
 class ShadowCache:
-    """bf16 copies of fp32 master parameters, refreshed when the parameter's version counter moves."""
+    """bf16 copies of fp32 master parameters, refreshed when the parameter's version counter (or storage) moves.
+
+    A refresh writes into a NEW buffer: an earlier forward may still hold the old shadow for its backward
+    (forward, optimizer.step(), forward, backward-of-the-first must see the weights of ITS forward).  In-place
+    updates made through `p.data` do not bump `p._version`; call `invalidate()` (or
+    `model.invalidate_shadows()`) after such an update."""
 
     def __init__(self):
         self._c = {}
@@ -136,11 +141,13 @@ class ShadowCache:
         ent = self._c.get(key)
         tag = (p._version, p.data_ptr())
         if ent is None or ent[0] != tag or ent[1].device != p.device:
-            buf = ent[1] if ent is not None and ent[1].shape == p.shape and ent[1].device == p.device else None
-            buf = cast_bf16(p.detach().contiguous(), buf)
+            buf = cast_bf16(p.detach().contiguous())
             self._c[key] = (tag, buf)
             return buf
         return ent[1]
+
+    def invalidate(self):
+        self._c.clear()
 
 
 def mask_cast(g, dtype, p, seed, stream_id):

@@ -53,6 +53,14 @@ class _Precision:
             object.__setattr__(self, "_shadow", eng.ShadowCache())
         return self._shadow.get(p)
 
+    def invalidate_shadows(self):
+        """Drop every cached bf16 weight copy below this module (needed only after in-place updates through
+        `param.data`, which do not move the version counter the cache keys on)."""
+        for m in self.modules():
+            if isinstance(m, _Precision) and hasattr(m, "_shadow"):
+                m._shadow.invalidate()
+        return self
+
     def set_precision(self, dtype):
         for m in self.modules():
             if isinstance(m, _Precision):
@@ -117,7 +125,8 @@ class Head(_Precision, nn.Module):
         x = _check_input(x, self.key.in_features)
         if self._kernel_dtype() == torch.bfloat16 and self.key.out_features % 16 != 0:
             raise RuntimeError("bf16 Head needs head_size % 16 == 0; use precision float32")
-        return _HeadFn.apply(x, self.query.weight, self.key.weight, self.value.weight, self)
+        with torch.cuda.device(x.device):
+            return _HeadFn.apply(x, self.query.weight, self.key.weight, self.value.weight, self)
 
 
 # ------------------------------------------------------------------------------------------------ MHA
@@ -244,7 +253,8 @@ class MultiHeadAttention(_Precision, nn.Module):
     def forward(self, x):
         x = _check_input(x, self.n_embd)
         p = self._drop() and self.dropout.p
-        return _MHAFn.apply(x, self.qkv_weight, self.proj.weight, self.proj.bias, self, float(p), eng.next_seed())
+        with torch.cuda.device(x.device):
+            return _MHAFn.apply(x, self.qkv_weight, self.proj.weight, self.proj.bias, self, float(p), eng.next_seed())
 
 
 # ------------------------------------------------------------------------------------------------ FeedForward
@@ -300,8 +310,9 @@ class FeedForward(_Precision, nn.Module):
     def forward(self, x):
         x = _check_input(x, self.mlp[0].in_features)
         p = self._drop() and self.mlp[3].p
-        return _FFNFn.apply(x, self.mlp[0].weight, self.mlp[0].bias, self.mlp[2].weight, self.mlp[2].bias, self,
-                            float(p), eng.next_seed())
+        with torch.cuda.device(x.device):
+            return _FFNFn.apply(x, self.mlp[0].weight, self.mlp[0].bias, self.mlp[2].weight, self.mlp[2].bias, self,
+                                float(p), eng.next_seed())
 
 
 # ------------------------------------------------------------------------------------------------ Block
@@ -324,6 +335,25 @@ def block_param_dict(blk, tensors=None):
     return out
 
 
+def export_block_probs(blk, d, acts):
+    """MultiHeadAttention.attention_probs (B,H,T,T), which the reference sets on EVERY forward (transformer.py:48):
+    recomputed from the q/k the block forward just stored in its activation arena, only when the module opted in
+    (`export_attention_probs`) — the fused attention kernel never materialises it."""
+    mh = blk.multi_head
+    if not mh.export_attention_probs:
+        mh.attention_probs = None
+        return
+    M, E, hs = d.B * d.T, d.E, d.E // d.H
+    dt = torch.bfloat16 if d.dtype == _C.BF16 else torch.float32
+    off = int(_C.lib().vitb200_block_act_offset(ctypes.byref(d), _C.ACT_QKV))
+    qkv = acts[off: off + M * 3 * E * dt.itemsize].view(dt).view(M, 3 * E)
+    qkv32 = qkv if dt == torch.float32 else qkv.float()
+    probs = torch.empty(d.B, d.H, d.T, d.T, dtype=torch.float32, device=acts.device)
+    _C.check(_C.lib().vitb200_attn_probs(qkv32.data_ptr(), probs.data_ptr(), d.B, d.T, d.H, hs, math.sqrt(hs),
+                                         _C.stream_ptr()))
+    mh.attention_probs = probs
+
+
 class _BlockFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, blk, layer, p_drop, seed, *params):
@@ -336,6 +366,7 @@ class _BlockFn(torch.autograd.Function):
         pd = block_param_dict(blk, params)
         plan = eng.Plan.__new__(eng.Plan)
         eng.Plan.block_fwd(plan, d, layer, pd, x, y, acts)
+        export_block_probs(blk, d, acts)
         ctx.save_for_backward(x, acts, *[pd[n] for n in _C.BLOCK_FIELDS_P])
         ctx.meta = (d, layer, blk._kernel_dtype())
         return y.reshape(B, T, E)
@@ -375,7 +406,9 @@ class Block(_Precision, nn.Module):
         x = _check_input(x, E)
         if self.multi_head.num_heads * self.multi_head.head_size != E:
             raise RuntimeError("Block requires n_embd divisible by n_head")
-        return _BlockFn.apply(x, self, self.layer_index, self._drop(), eng.next_seed(), *block_param_tensors(self))
+        with torch.cuda.device(x.device):
+            return _BlockFn.apply(x, self, self.layer_index, self._drop(), eng.next_seed(),
+                                  *block_param_tensors(self))
 
 
 class TransformerEncoder(_Precision, nn.Module):

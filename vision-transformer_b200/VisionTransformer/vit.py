@@ -16,7 +16,7 @@ import torch.nn as nn
 
 from . import _C, config, transformer  # noqa: F401  (same sub-module imports as the reference vit.py:3)
 from . import _engine as eng
-from .transformer import _Precision, block_param_dict, block_param_tensors
+from .transformer import _Precision, block_param_dict, block_param_tensors, export_block_probs
 
 
 def _autocast_bf16():
@@ -104,7 +104,8 @@ class PatchEmbedding(_Precision, nn.Module):
     def forward(self, x):
         x = _check_images(x, self.input_channels, self.batch_size)
         conv = self.sequence[0]
-        return _EmbedFn.apply(x, conv.weight, conv.bias, self.cls_tkn_embd, self.pos_embd, self)
+        with torch.cuda.device(x.device):   # kernels go to torch's current stream OF THE TENSORS' device
+            return _EmbedFn.apply(x, conv.weight, conv.bias, self.cls_tkn_embd, self.pos_embd, self)
 
 
 # ------------------------------------------------------------------------------------------------ whole model
@@ -126,7 +127,7 @@ class _ViTFn(torch.autograd.Function):
     4 embedding tensors, 11 per block (C-ABI order), 6 head tensors."""
 
     @staticmethod
-    def forward(ctx, x, model, p_drop, seed, *params):
+    def forward(ctx, x, model, p_drop, seed, grad_mode, *params):
         emb, blocks = model.emdeddings, list(model.transformer_encoder.blocks)
         nL = len(blocks)
         dt = model._kernel_dtype()
@@ -139,7 +140,10 @@ class _ViTFn(torch.autograd.Function):
         plan.L = nL
         L = _C.lib()
         dev = x.device
-        need_grad = any(ctx.needs_input_grad)  # False under torch.no_grad(): no activation stash (train.py:29-44)
+        # `needs_input_grad` mirrors requires_grad of the inputs, NOT grad mode, and Function.forward itself always
+        # runs with grad disabled: the caller captures torch.is_grad_enabled().  False under the reference's
+        # `@torch.no_grad evaluate()` (train.py:29-44): no activation stash, one scratch arena, ping-pong residuals.
+        need_grad = bool(grad_mode) and any(ctx.needs_input_grad)
         nb = lambda n: torch.empty(max(int(n), 256), dtype=torch.uint8, device=dev)  # noqa: E731
 
         pe = _embed_param_dict(emb, *params[:4])
@@ -158,6 +162,7 @@ class _ViTFn(torch.autograd.Function):
             else:
                 x_out = xs[-2] if len(xs) >= 2 else torch.empty_like(xs[0])
             eng.Plan.block_fwd(plan, d, i, pd, xs[-1], x_out, acts)
+            export_block_probs(blk, d, acts)
             xs.append(x_out)
             if need_grad:
                 blk_acts.append(acts)
@@ -174,12 +179,24 @@ class _ViTFn(torch.autograd.Function):
         if need_grad:
             ctx.state = (d, nL, dt, emb_acts, xs, blk_acts, blk_params, hp, head_acts,
                          [tuple(p.shape) for p in params])
+            # the kernels read the live fp32 parameters (and bf16 shadows of them) through raw pointers, outside
+            # autograd's saved-tensor version check: remember the versions and check them in backward ourselves
+            ctx.versions = [(p, p._version) for p in params]
         return logits
 
     @staticmethod
     def backward(ctx, dlogits):
+        if getattr(ctx, "state", None) is None:
+            raise RuntimeError("VisionTransformer (B200): the saved activations of this forward were already consumed "
+                               "and released by a backward pass; retain_graph / a second backward is not supported")
+        for p, ver in ctx.versions:
+            if p._version != ver:
+                raise RuntimeError("one of the variables needed for gradient computation has been modified by an "
+                                   f"inplace operation: a parameter of shape {tuple(p.shape)} is at version "
+                                   f"{p._version}; expected version {ver} (VisionTransformer B200 forward)")
         d, nL, dt, emb_acts, xs, blk_acts, blk_params, hp, head_acts, shapes = ctx.state
         ctx.state = None
+        ctx.versions = None
         dev = dlogits.device
         L = _C.lib()
         plan = eng.Plan.__new__(eng.Plan)
@@ -209,7 +226,7 @@ class _ViTFn(torch.autograd.Function):
             dy_a, dy_b = dy_b, dy_a
         eg = dict(zip(_C.EMBED_FIELDS_G, gv[:4]))
         eng.Plan.embed_bwd(plan, d, eg, g, emb_acts)
-        return (None, None, None, None) + tuple(gv)
+        return (None, None, None, None, None) + tuple(gv)
 
 
 class VisionTransformer(_Precision, nn.Module):
@@ -254,4 +271,5 @@ class VisionTransformer(_Precision, nn.Module):
         params = self.all_param_tensors()
         for p in params:
             eng.require_cuda(p, "model parameters (call model.to('cuda'))")
-        return _ViTFn.apply(x, self, self._drop(), eng.next_seed(), *params)
+        with torch.cuda.device(x.device):   # kernels go to torch's current stream OF THE TENSORS' device
+            return _ViTFn.apply(x, self, self._drop(), eng.next_seed(), torch.is_grad_enabled(), *params)

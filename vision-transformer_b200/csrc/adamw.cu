@@ -59,6 +59,54 @@ adamw_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __r
   adamw_span(p, g, m, v, shadow, 0, n, h, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
 }
 
+// Range form for the data-parallel trainer: elements [0, n) of arenas already offset to the range start (a 16-byte
+// aligned offset).  GB: the gradient is read from a bf16 exchange buffer (reduce-scattered bf16 gradients) instead of
+// the fp32 arena.  ZERO: the fp32 gradient range is cleared in the same pass — the kernels of the next backward
+// accumulate into it, so this is optimizer.zero_grad() (reference train.py:94) without a separate memset.
+template <bool GB, bool ZERO>
+__global__ void __launch_bounds__(256)
+adamw_range_kernel(float* __restrict__ p, float* __restrict__ g, const bf16* __restrict__ gb, float* __restrict__ m,
+                   float* __restrict__ v, bf16* __restrict__ shadow, int64_t n, const AdamWHyper h) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 4;
+  const int64_t n4 = n & ~int64_t(3);
+  for (int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4; i < n4; i += stride) {
+    float4 pp = *reinterpret_cast<float4*>(p + i);
+    float4 gg;
+    if (GB) {
+      const uint2 raw = __ldcs(reinterpret_cast<const uint2*>(gb + i));
+      gg.x = __uint_as_float(raw.x << 16); gg.y = __uint_as_float(raw.x & 0xFFFF0000u);
+      gg.z = __uint_as_float(raw.y << 16); gg.w = __uint_as_float(raw.y & 0xFFFF0000u);
+    } else {
+      gg = __ldcs(reinterpret_cast<const float4*>(g + i));
+    }
+    float4 mm = *reinterpret_cast<float4*>(m + i);
+    float4 vv = *reinterpret_cast<float4*>(v + i);
+    pp.x = adamw_one(pp.x, gg.x, mm.x, vv.x, h);
+    pp.y = adamw_one(pp.y, gg.y, mm.y, vv.y, h);
+    pp.z = adamw_one(pp.z, gg.z, mm.z, vv.z, h);
+    pp.w = adamw_one(pp.w, gg.w, mm.w, vv.w, h);
+    *reinterpret_cast<float4*>(p + i) = pp;
+    *reinterpret_cast<float4*>(m + i) = mm;
+    *reinterpret_cast<float4*>(v + i) = vv;
+    if (ZERO) *reinterpret_cast<float4*>(g + i) = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (shadow != nullptr) {
+      uint2 o;
+      o.x = pack_bf16x2(pp.x, pp.y);
+      o.y = pack_bf16x2(pp.z, pp.w);
+      *reinterpret_cast<uint2*>(shadow + i) = o;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n - n4)) {
+    const int64_t i = n4 + threadIdx.x;
+    float mm = m[i], vv = v[i];
+    const float gi = GB ? __bfloat162float(gb[i]) : g[i];
+    const float pp = adamw_one(p[i], gi, mm, vv, h);
+    p[i] = pp; m[i] = mm; v[i] = vv;
+    if (ZERO) g[i] = 0.f;
+    if (shadow != nullptr) shadow[i] = __float2bfloat16_rn(pp);
+  }
+}
+
 // Multi-tensor form: block -> (tensor, chunk) through a device-resident table.
 constexpr int64_t kChunk = 65536;
 __global__ void __launch_bounds__(256)
@@ -83,6 +131,28 @@ int adamw_flat(float* p, const float* g, float* m, float* v, bf16* shadow, int64
   const int64_t cap = static_cast<int64_t>(num_sms()) * 8;
   ProfScope prof(kProfAdamW, static_cast<double>(n) * (28 + (shadow ? 2 : 0)), 1, s);
   adamw_flat_kernel<<<static_cast<int>(blocks < cap ? blocks : cap), 256, 0, s>>>(p, g, m, v, shadow, n, h);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int adamw_range(float* p, float* g, const bf16* gb, float* m, float* v, bf16* shadow, int64_t n, bool zero_grad,
+                const AdamWHyper& h, cudaStream_t s) {
+  VB_REQUIRE(n > 0, "adamw: empty range");
+  VB_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) |
+               reinterpret_cast<uintptr_t>(v)) & 15u) == 0 && (reinterpret_cast<uintptr_t>(shadow) & 7u) == 0 &&
+             (reinterpret_cast<uintptr_t>(gb) & 7u) == 0, "adamw_range: range start must be 16-byte aligned");
+  const int64_t blocks = ceil_div<int64_t>(n, 256 * 4 * 4);
+  const int64_t cap = static_cast<int64_t>(num_sms()) * 8;
+  const int grid = static_cast<int>(blocks < cap ? blocks : cap);
+  // bytes: p, m, v read + written (24), gradient read (4 fp32 / 2 bf16), gradient cleared (4), bf16 shadow written (2)
+  ProfScope prof(kProfAdamW, static_cast<double>(n) * (24 + (gb ? 2 : 4) + (zero_grad ? 4 : 0) + (shadow ? 2 : 0)), 1, s);
+  if (gb != nullptr) {
+    if (zero_grad) adamw_range_kernel<true, true><<<grid, 256, 0, s>>>(p, g, gb, m, v, shadow, n, h);
+    else adamw_range_kernel<true, false><<<grid, 256, 0, s>>>(p, g, gb, m, v, shadow, n, h);
+  } else {
+    if (zero_grad) adamw_range_kernel<false, true><<<grid, 256, 0, s>>>(p, g, gb, m, v, shadow, n, h);
+    else adamw_range_kernel<false, false><<<grid, 256, 0, s>>>(p, g, gb, m, v, shadow, n, h);
+  }
   VB_CHECK_LAUNCH();
   return kOk;
 }

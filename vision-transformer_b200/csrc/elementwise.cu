@@ -321,9 +321,11 @@ __global__ void ce_kernel(const float* __restrict__ logits, const int64_t* __res
     float s = 0.f;
     for (int c = lane; c < C; c += 32) s += expf(row[c] - mx);
     s = warp_sum(s);
-    const int y = static_cast<int>(labels[b]);
+    const int64_t y64 = labels[b];
+    const bool y_ok = y64 >= 0 && y64 < C;   // torch device-asserts on an out-of-range target; here the loss turns NaN
+    const int y = y_ok ? static_cast<int>(y64) : 0;
     const float lse = mx + logf(s);
-    if (lane == 0) acc += lse - row[y];
+    if (lane == 0) acc += y_ok ? lse - row[y] : __int_as_float(0x7fc00000);
     if (dlogits != nullptr)
       for (int c = lane; c < C; c += 32)
         dlogits[static_cast<int64_t>(b) * C + c] = (expf(row[c] - lse) - (c == y ? 1.f : 0.f)) * gs;

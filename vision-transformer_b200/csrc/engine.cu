@@ -359,6 +359,18 @@ int64_t vitb200_block_scratch_bytes(const vitb200_dims* d) {
   carve_scratch(d, nullptr, &total);
   return static_cast<int64_t>(total);
 }
+int64_t vitb200_block_act_offset(const vitb200_dims* d, int which) {
+  const BlockActs a = carve_block(d, nullptr);
+  const void* ptr = nullptr;
+  switch (which) {
+    case VITB200_ACT_QKV: ptr = a.qkv; break;
+    case VITB200_ACT_ATTN: ptr = a.attn; break;
+    case VITB200_ACT_LSE: ptr = a.lse; break;
+    case VITB200_ACT_XMID: ptr = a.x_mid; break;
+    default: return -1;
+  }
+  return static_cast<int64_t>(reinterpret_cast<uintptr_t>(ptr));
+}
 
 }  // extern "C"
 
@@ -590,6 +602,12 @@ int vitb200_adamw_flat(float* p, const float* g, float* m, float* v, void* shado
                        vitb200_adamw_hyper h, void* stream) {
   VB_REQUIRE(h.step >= 1, "adamw: step must be >= 1");
   return adamw_flat(p, g, m, v, static_cast<bf16*>(shadow_bf16), n, to_hyper(h), static_cast<cudaStream_t>(stream));
+}
+int vitb200_adamw_range(float* p, float* g, const void* g_bf16, float* m, float* v, void* shadow_bf16, int64_t n,
+                        int zero_grad, vitb200_adamw_hyper h, void* stream) {
+  VB_REQUIRE(h.step >= 1, "adamw: step must be >= 1");
+  return adamw_range(p, g, static_cast<const bf16*>(g_bf16), m, v, static_cast<bf16*>(shadow_bf16), n, zero_grad != 0,
+                     to_hyper(h), static_cast<cudaStream_t>(stream));
 }
 int vitb200_adamw_multi(const uint64_t* p_ptrs, const uint64_t* g_ptrs, const uint64_t* m_ptrs,
                         const uint64_t* v_ptrs, const uint64_t* shadow_ptrs, const int64_t* sizes,

@@ -224,6 +224,9 @@ int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int6
     return kOk;
   }
   int s = ep.accumulate ? splits : 1;
+  // a K-split accumulates PARTIAL sums with atomics: an epilogue that is not linear in the accumulator (ReLU, ReLU-style
+  // aux mask, dropout) would be applied to the partials — refuse to split then (one CTA owns the whole K range)
+  if (ep.accumulate && (ep.relu || ep.mask_aux != nullptr || ep.drop.p > 0.f)) s = 1;
   const int tiles = ceil_div(M, FBM) * ceil_div(N, FBN);
   // Few output tiles but a long K (the classifier head, M = batch): split K across CTAs into a zeroed output.
   // Only for epilogues that are linear in the accumulator (bias / row_add / residual are added by split 0).

@@ -132,6 +132,9 @@ class DPTrainer:
         self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
         self.dropout_p, self.seed, self.step_no = float(dropout_p), int(seed), 0
         self.pg, self.world = process_group, int(world_size)
+        # every data-parallel rank draws its OWN dropout masks (independent regularisation over the global batch)
+        self.rank = torch.distributed.get_rank(process_group) if (self.world > 1 and
+                                                                  torch.distributed.is_initialized()) else 0
         # opt-in dead-row elimination: only token 0 of the LAST block feeds the classifier (reference vit.py:80), so
         # that block's proj / LayerNorm-2 / MLP and their backward run on B rows instead of B*T.  Same logits, same
         # gradients; fewer executed FLOPs than the algorithmic count, hence off unless asked for.
@@ -349,7 +352,8 @@ class DPTrainer:
 
     # ------------------------------------------------------------------------------------------ one step
     def _dims(self, train):
-        seed = (self.seed * 0x9E3779B97F4A7C15 + self.step_no * 0xD1B54A32D192ED03) & 0xFFFFFFFFFFFFFFFF
+        seed = (self.seed * 0x9E3779B97F4A7C15 + self.step_no * 0xD1B54A32D192ED03 +
+                self.rank * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
         return self.plan.dims(self.dropout_p if train else 0.0, seed)
 
     def forward(self, images, d, u8_layout=0):
@@ -364,8 +368,15 @@ class DPTrainer:
     def _bucket_ready(self, stage, handles):
         self.reducer.ready(stage, handles)
 
+    def _check_labels(self, labels):
+        if labels.dtype != torch.int64 or labels.device != self.dev or not labels.is_contiguous() or \
+                labels.numel() != self.B:
+            raise RuntimeError(f"labels must be a contiguous int64 tensor of {self.B} class indices on {self.dev}, got "
+                               f"{labels.dtype} {tuple(labels.shape)} on {labels.device}")
+
     def backward(self, labels, d):
         pl, L = self.plan, _C.lib()
+        self._check_labels(labels)
         _C.check(L.vitb200_cross_entropy(self.logits.data_ptr(), labels.data_ptr(), self.loss.data_ptr(),
                                          self.dlogits.data_ptr(), self.B, self.classes, 1.0, _C.stream_ptr()))
         handles = []
@@ -385,11 +396,24 @@ class DPTrainer:
     def optimizer_step(self):
         self.step_no += 1
         h = _C.AdamWHyper(self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.step_no, 1.0 / self.world)
-        _C.check(_C.lib().vitb200_adamw_flat(self.p.data_ptr(), self.g.data_ptr(), self.m.data_ptr(), self.v.data_ptr(),
-                                             None if self.shadow is None else self.shadow.data_ptr(), self.total, h,
-                                             _C.stream_ptr()))
-        self.g.zero_()
+        # one launch: AdamW over the arena, bf16 shadow written, gradient arena cleared for the next backward
+        _C.check(_C.lib().vitb200_adamw_range(self.p.data_ptr(), self.g.data_ptr(), None, self.m.data_ptr(),
+                                              self.v.data_ptr(),
+                                              None if self.shadow is None else self.shadow.data_ptr(), self.total, 1,
+                                              h, _C.stream_ptr(self.dev)))
 
+    def _on_device(fn):
+        """Run a public entry point with the trainer's device current, so that torch's 'current stream' (where the
+        C ABI enqueues) is the stream of THIS trainer's device even when the caller's current device differs."""
+        import functools
+
+        @functools.wraps(fn)
+        def wrapped(self, *a, **k):
+            with torch.cuda.device(self.dev):
+                return fn(self, *a, **k)
+        return wrapped
+
+    @_on_device
     def step(self, images, labels, train=True):
         """fwd + CE + bwd + grad all-reduce + AdamW on device-resident inputs; returns the (device) loss tensor."""
         if images.shape != self._in[0][0].shape:
@@ -401,6 +425,7 @@ class DPTrainer:
         self.optimizer_step()
         return self.loss
 
+    @_on_device
     def step_host(self, images_host, labels_host):
         """Same step from PINNED host tensors: H2D of this step's inputs on a copy stream (double-buffered, so it
         overlaps the previous step's compute) and an async D2H of the loss.  -> index into self.loss_host."""
@@ -424,6 +449,7 @@ class DPTrainer:
         self._loss_ev[li].record(cur)
         return li
 
+    @_on_device
     def step_host_u8(self, images_host_u8, labels_host, layout=0):
         """step_host fed with raw uint8 pixels: pinned (B,C,H,W) [layout 0] or (B,H,W,C) [layout 1]
         uint8 -> one H2D of 1 byte per pixel, the ToTensor /255 (train.py:151-155) fused into the patch gather."""
