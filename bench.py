@@ -48,6 +48,11 @@ def parse():
     ap.add_argument("--no-row0", action="store_true", help="skip the last-block dead-row-elimination side number")
     ap.add_argument("--no-ref-eager", action="store_true", help="skip the reference-eager-on-this-GPU side number")
     ap.add_argument("--bucket-mb", type=float, default=48)
+    ap.add_argument("--zero1", default="auto", choices=["auto", "0", "1"],
+                    help="ZeRO-1 exchange (reduce-scatter / sharded AdamW / all-gather); auto = on when N > 1")
+    ap.add_argument("--grad-comm", default="auto", choices=["auto", "bf16", "fp32"], help="gradient exchange dtype")
+    ap.add_argument("--nccl-max-ctas", type=int, default=0,
+                    help="cap NCCL's CTAs per collective so the persistent GEMM clusters keep their SMs (0 = NCCL default)")
     return ap.parse_args()
 
 
@@ -269,13 +274,20 @@ def run_b200(args):
     pg = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        opts = None
+        if args.nccl_max_ctas > 0:
+            opts = dist.ProcessGroupNCCL.Options()
+            opts.config.max_ctas = args.nccl_max_ctas
+            opts.config.min_ctas = min(args.nccl_max_ctas, 4)
+        dist.init_process_group("nccl", device_id=dev, pg_options=opts)
         pg = dist.group.WORLD
 
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     wl = workload(args)
+    zero1 = None if args.zero1 == "auto" else args.zero1 == "1"
+    grad_comm = None if args.grad_comm == "auto" else args.grad_comm
     tr = train_dp.DPTrainer(batch_size=args.batch, dtype=dtype, device=dev, process_group=pg, world_size=world,
-                            bucket_mb=args.bucket_mb, seed=0, **wl)
+                            bucket_mb=args.bucket_mb, seed=0, zero1=zero1, grad_comm=grad_comm, **wl)
     tr.init_parameters(seed=0)  # random-init weights of the architecture (no checkpoints offline)
     tr.broadcast_parameters()
 
@@ -460,6 +472,10 @@ def run_b200(args):
         "config": {"workload": f"{args.model} B={args.batch}/GPU train step (fwd+CE+bwd+allreduce+AdamW), {img}x{img}x3, "
                                f"{args.classes} cls, dropout on",
                    "global_batch": gb, "tokens_per_image": tr.T, "parallelism": f"dp{world}",
+                   "exchange": ("none (1 GPU)" if world == 1 else
+                                (f"ZeRO-1: reduce-scatter {str(tr.comm_dtype).split('.')[-1]} gradients, sharded AdamW, "
+                                 f"all-gather fp32 parameters" if tr.zero1 else "all-reduce fp32 gradients") +
+                                (f", NCCL max_ctas {args.nccl_max_ctas}" if args.nccl_max_ctas else "")),
                    "l2_policy": "inputs (154 MB/step at B=256) and activations (~13 GB) exceed the 126 MB L2; "
                                 "no explicit flush",
                    "grad_buckets_mb": [round((b_ - a_) * 4 / 2 ** 20, 1) for a_, b_, _ in tr.buckets]},

@@ -151,6 +151,10 @@ typedef struct {
 } vitb200_adamw_hyper;
 int vitb200_adamw_flat(float* p, const float* g, float* m, float* v, void* shadow_bf16, int64_t n,
                        vitb200_adamw_hyper h, void* stream);
+/* Gradient-exchange staging (data-parallel trainer): out_bf16 = bf16(g) when out_bf16 != NULL, and g = 0, in one
+ * pass over n elements — the bf16 copy feeds the reduce-scatter, the cleared arena is optimizer.zero_grad()
+ * (train.py:94).  out_bf16 == NULL: clear only. */
+int vitb200_grad_pack(float* g, void* out_bf16, int64_t n, void* stream);
 /* Range form (data-parallel trainer, ZeRO-1 shards): AdamW over n elements of arenas already offset to a 16-byte
  * aligned range start.  g_bf16 != NULL: gradients are read from that bf16 buffer (reduce-scattered bf16 gradient
  * exchange) instead of the fp32 g.  zero_grad != 0: the fp32 gradient range is cleared in the same pass

@@ -105,3 +105,79 @@ def test_single_rank_reducer_is_a_no_op():
     red.ready("head", handles)
     red.finish(handles)
     assert handles == [] and bool((g == 1).all())
+
+
+# ---------------------------------------------------------------------------------------------- ZeRO-1 exchange (CPU)
+def _cpu_pack(g_slice, out_slice):
+    """CPU stand-in for vitb200_grad_pack (test only): cast copy (if any) + clear."""
+    if out_slice is not None:
+        out_slice.copy_(g_slice.to(out_slice.dtype))
+    g_slice.zero_()
+
+
+def _zero1_worker(rank, world, port, comm, out):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        layout, offs, total = _layout()
+        buckets = train_dp.make_buckets(layout, offs, total, 5000)
+        comm_dtype = torch.bfloat16 if comm == "bf16" else torch.float32
+        gs_all = [torch.randn(total, generator=torch.Generator().manual_seed(200 + r)) for r in range(world)]
+        g = gs_all[rank].clone()
+        red = train_dp.ShardedReducer(g, buckets, dist.group.WORLD, world, rank, comm_dtype, _cpu_pack)
+        handles = []
+        for stage in ["head"] + list(range(CFG["L"] - 1, -1, -1)) + ["embed"]:
+            red.ready(stage, handles)
+        red.finish(handles)
+        ok = handles == list(range(len(buckets))) and int(torch.count_nonzero(g)) == 0
+        # my shard of every bucket holds the sum over ranks (of the bf16-rounded values in bf16 mode)
+        expect = torch.stack([t.to(comm_dtype).float() for t in gs_all]).sum(0)
+        covered = torch.zeros(total, dtype=torch.bool)
+        for k in range(len(buckets)):
+            s0, s1 = red.shard_range(k)
+            got = red.gs[red.shard_off[k]: red.shard_off[k] + red.shard_len[k]].float()
+            tol = 1e-6 if comm == "fp32" else 4e-2
+            ok = ok and torch.allclose(got, expect[s0:s1], rtol=0, atol=tol)
+            ok = ok and s0 % train_dp.ALIGN == 0 and (s1 - s0) * world == buckets[k][1] - buckets[k][0]
+            covered[s0:s1] = True
+        # the shards of all ranks tile the arena exactly once
+        cov = covered.to(torch.int32)
+        dist.all_reduce(cov)
+        ok = ok and bool((cov == 1).all())
+        # "sharded optimizer": every rank rewrites ONLY its shards, gather() rebuilds the full arena everywhere
+        p = torch.full((total,), -1.0)
+        for k in range(len(buckets)):
+            s0, s1 = red.shard_range(k)
+            p[s0:s1] = float(rank + 1)
+        seen = []
+        red.gather(p, after=lambda k, a, b: seen.append(k))
+        ok = ok and seen == list(range(len(buckets) - 1, -1, -1))      # forward order: embedding bucket first
+        for k, (a, b, _) in enumerate(buckets):
+            n = red.shard_len[k]
+            for r in range(world):
+                ok = ok and bool((p[a + r * n: a + (r + 1) * n] == float(r + 1)).all())
+        out[rank] = bool(ok)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("comm", ["fp32", "bf16"])
+def test_world2_zero1_reduce_scatter_and_all_gather(comm):
+    world = 2
+    with mp.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_zero1_worker, args=(world, _free_port(), comm, out), nprocs=world, join=True)
+        assert dict(out) == {0: True, 1: True}
+
+
+def test_every_stage_starts_on_a_shard_boundary():
+    layout, offs, total = _layout()
+    assert total % train_dp.SHARD_ALIGN == 0
+    prev = None
+    for (stage, _, _, _), (o, _) in zip(layout, offs):
+        if stage != prev:
+            assert o % train_dp.SHARD_ALIGN == 0, stage
+            prev = stage
+    for be in (1, 5000, 10 ** 9):
+        for a, b, _ in train_dp.make_buckets(layout, offs, total, be):
+            assert (b - a) % (8 * train_dp.ALIGN) == 0

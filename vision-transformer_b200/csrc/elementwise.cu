@@ -353,6 +353,31 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ in, bf16* __restr
     for (int64_t i = n4 * 4; i < n; ++i) out[i] = __float2bfloat16_rn(in[i]);
 }
 
+// Gradient exchange staging of the data-parallel trainer: out = bf16(g) (when out != null) and g = 0 in ONE pass —
+// the bf16 copy is what the reduce-scatter sends, the cleared fp32 arena is what the next backward accumulates into
+// (optimizer.zero_grad(), reference train.py:94).  out == null: clear only.
+__global__ void __launch_bounds__(256)
+grad_pack_kernel(float* __restrict__ g, bf16* __restrict__ out, int64_t n) {
+  const int64_t n4 = n / 4;
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    if (out != nullptr) {
+      const float4 v = __ldcs(reinterpret_cast<const float4*>(g + i * 4));
+      uint2 o;
+      o.x = pack_bf16x2(v.x, v.y);
+      o.y = pack_bf16x2(v.z, v.w);
+      *reinterpret_cast<uint2*>(out + i * 4) = o;
+    }
+    *reinterpret_cast<float4*>(g + i * 4) = z;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (int64_t i = n4 * 4; i < n; ++i) {
+      if (out != nullptr) out[i] = __float2bfloat16_rn(g[i]);
+      g[i] = 0.f;
+    }
+}
+
 // keep[i] = 1 if element i of the (seed, stream) dropout stream is kept.  Test/debug export of the mask that the
 // fused epilogues regenerate on the fly.
 __global__ void dropout_mask_kernel(uint8_t* __restrict__ keep, int64_t n, const Dropout drop) {
@@ -535,6 +560,17 @@ int cast_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t s) {
   ProfScope prof(kProfEltwise, 0.0, 1, s);
   VB_REQUIRE(aligned16(in) && (reinterpret_cast<uintptr_t>(out) & 7u) == 0, "cast: unaligned buffers");
   cast_f32_bf16_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, s>>>(in, out, n);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int grad_pack(float* g, bf16* out, int64_t n, cudaStream_t s) {
+  VB_REQUIRE(n > 0, "grad_pack: empty range");
+  VB_REQUIRE(aligned16(g) && (reinterpret_cast<uintptr_t>(out) & 7u) == 0, "grad_pack: unaligned buffers");
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
+  const int64_t blocks = ceil_div<int64_t>(n / 4 + 1, 256 * 4);
+  const int64_t cap = static_cast<int64_t>(num_sms()) * 8;
+  grad_pack_kernel<<<static_cast<int>(blocks < cap ? blocks : cap), 256, 0, s>>>(g, out, n);
   VB_CHECK_LAUNCH();
   return kOk;
 }

@@ -603,6 +603,9 @@ int vitb200_adamw_flat(float* p, const float* g, float* m, float* v, void* shado
   VB_REQUIRE(h.step >= 1, "adamw: step must be >= 1");
   return adamw_flat(p, g, m, v, static_cast<bf16*>(shadow_bf16), n, to_hyper(h), static_cast<cudaStream_t>(stream));
 }
+int vitb200_grad_pack(float* g, void* out_bf16, int64_t n, void* stream) {
+  return grad_pack(g, static_cast<bf16*>(out_bf16), n, static_cast<cudaStream_t>(stream));
+}
 int vitb200_adamw_range(float* p, float* g, const void* g_bf16, float* m, float* v, void* shadow_bf16, int64_t n,
                         int zero_grad, vitb200_adamw_hyper h, void* stream) {
   VB_REQUIRE(h.step >= 1, "adamw: step must be >= 1");

@@ -5,11 +5,17 @@ One process per GPU.  All parameters live in ONE flat fp32 arena (forward order:
 every tensor 256-byte aligned), gradients / Adam moments / bf16 shadow weights in arenas of the same layout, and
 every activation buffer is allocated once: a steady-state step performs no allocation and no host sync.
 
-Multi-GPU: the path shards by images (pure data parallel).  Gradients are summed with NCCL all-reduce on contiguous
-arena slices ("buckets", reverse layer order) issued on a side stream as soon as the backward stage that completes
-a bucket has been enqueued, so the exchange overlaps the rest of backward; the fused AdamW kernel folds the 1/world
-mean into its gradient read.  `cls_tkn_embd` is a per-batch-slot parameter (reference vit.py:31-33) and is averaged
-across ranks like any other parameter, exactly as DistributedDataParallel would treat it.
+Multi-GPU: the path shards by images (pure data parallel).  Gradients are exchanged on contiguous arena slices
+("buckets", reverse layer order) issued on a side stream as soon as the backward stage that completes a bucket has
+been enqueued, so the exchange overlaps the rest of backward; the fused AdamW kernel folds the 1/world mean into its
+gradient read.  Two exchange schemes:
+  * all-reduce (`zero1=False`): every rank sums every bucket and runs AdamW over the whole arena;
+  * ZeRO-1 (`zero1=True`, default for world > 1): each bucket is REDUCE-SCATTERED (bf16 or fp32), every rank runs
+    AdamW on its 1/world shard of every bucket only (Adam moments exist only for that shard), and the updated fp32
+    parameters are ALL-GATHERED bucket by bucket in forward order on the side stream while the next forward already
+    runs (each stage waits for the event of its own bucket).
+`cls_tkn_embd` is a per-batch-slot parameter (reference vit.py:31-33) and is averaged across ranks like any other
+parameter, exactly as DistributedDataParallel would treat it.
 """
 import ctypes
 import os
@@ -25,6 +31,8 @@ from VisionTransformer import _C  # noqa: E402
 from VisionTransformer import _engine as eng  # noqa: E402
 
 ALIGN = 64  # elements: 256 B in fp32, 128 B in bf16 — keeps every tensor TMA-legal (16 B) in both arenas
+SHARD_ALIGN = ALIGN * 8  # every STAGE starts at a multiple of 512 elements, so any bucket (a union of whole stages)
+#                          splits evenly over 1 / 2 / 4 / 8 ranks into ALIGN-aligned shards (ZeRO-1)
 _SECTIONS = ("query", "key", "value")
 
 
@@ -51,14 +59,17 @@ def param_layout(*, C, P, E, H, L, T, B, classes):
 
 
 def arena_offsets(layout):
-    offs, tot = [], 0
-    for _, _, _, shape in layout:
+    offs, tot, prev = [], 0, None
+    for stage, _, _, shape in layout:
+        if stage != prev:
+            tot = (tot + SHARD_ALIGN - 1) // SHARD_ALIGN * SHARD_ALIGN
+            prev = stage
         n = 1
         for s in shape:
             n *= s
         offs.append((tot, n))
         tot += (n + ALIGN - 1) // ALIGN * ALIGN
-    return offs, tot
+    return offs, (tot + SHARD_ALIGN - 1) // SHARD_ALIGN * SHARD_ALIGN
 
 
 def make_buckets(layout, offs, total, bucket_elems):
@@ -113,12 +124,104 @@ class BucketReducer:
             h.wait()  # CUDA: the compute stream waits for the reduced buckets; the host does not block
 
 
+class ShardedReducer:
+    """ZeRO-1 exchange of the data-parallel path.  Backward order: each completed bucket [a, b) is staged
+    (`pack(g[a:b], gb[a:b])`: bf16 copy + the fp32 arena cleared, one pass) and reduce-scattered, so rank r receives
+    the SUM over ranks of its shard [a + r*(b-a)/world, a + (r+1)*(b-a)/world) into `gs` (all shards back to back,
+    bucket order).  After the sharded AdamW, `gather(p)` all-gathers every bucket of the parameter arena in place, in
+    FORWARD order, and records one event per bucket for the next forward to wait on.  CUDA: everything runs on a side
+    stream; CPU tensors (gloo, the world_size-2 tests): same calls, no streams.
+
+    pack(g_slice, out_slice_or_None): stage one bucket — out = cast(g) when the exchange dtype is bf16, g = 0."""
+
+    def __init__(self, flat_grad, buckets, process_group, world_size, rank, comm_dtype, pack):
+        self.g, self.buckets, self.pg, self.world, self.rank = flat_grad, buckets, process_group, int(world_size), int(rank)
+        self.comm_dtype, self.pack = comm_dtype, pack
+        self.cuda = flat_grad.is_cuda
+        dev = flat_grad.device
+        for a, b, _ in buckets:
+            if (b - a) % (self.world * ALIGN) != 0:
+                raise ValueError(f"bucket [{a},{b}) does not split into {self.world} {ALIGN}-element-aligned shards")
+        self.shard_len = [(b - a) // self.world for a, b, _ in buckets]
+        self.shard_off = [sum(self.shard_len[:k]) for k in range(len(buckets))]
+        self.shard_total = sum(self.shard_len)
+        self.gs = torch.zeros(self.shard_total, dtype=comm_dtype, device=dev)         # my reduced gradient shards
+        self.gb = torch.zeros(flat_grad.numel(), dtype=comm_dtype, device=dev) if comm_dtype != flat_grad.dtype else None
+        if self.cuda:
+            self.stream = torch.cuda.Stream(device=dev)
+            self.events = [torch.cuda.Event() for _ in buckets]
+            self.gather_events = [torch.cuda.Event() for _ in buckets]
+        self.gather_pending = False
+
+    def shard_range(self, k):
+        """(arena start, arena end) of THIS rank's shard of bucket k."""
+        a, _, _ = self.buckets[k]
+        return a + self.rank * self.shard_len[k], a + (self.rank + 1) * self.shard_len[k]
+
+    def _scatter(self, k):
+        a, b, _ = self.buckets[k]
+        out = self.gs[self.shard_off[k]: self.shard_off[k] + self.shard_len[k]]
+        if self.gb is not None:
+            self.pack(self.g[a:b], self.gb[a:b])
+            torch.distributed.reduce_scatter_tensor(out, self.gb[a:b], group=self.pg)
+        else:
+            torch.distributed.reduce_scatter_tensor(out, self.g[a:b], group=self.pg)
+            self.pack(self.g[a:b], None)
+
+    def ready(self, stage, handles):
+        for k, (a, b, st) in enumerate(self.buckets):
+            if st != stage:
+                continue
+            if self.cuda:
+                self.events[k].record(torch.cuda.current_stream(self.g.device))
+                with torch.cuda.stream(self.stream):
+                    self.stream.wait_event(self.events[k])
+                    self._scatter(k)   # synchronous collective w.r.t. the SIDE stream; the compute stream runs on
+            else:
+                self._scatter(k)
+            handles.append(k)
+
+    def finish(self, handles):
+        if self.cuda and handles:
+            torch.cuda.current_stream(self.g.device).wait_stream(self.stream)
+
+    def gather(self, arena, after=None):
+        """In-place all-gather of every bucket of `arena` from the ranks' shards, forward order (embedding first).
+        after(k, a, b): optional per-bucket follow-up on the same stream (the bf16 shadow cast)."""
+        order = range(len(self.buckets) - 1, -1, -1)
+        if self.cuda:
+            self.stream.wait_stream(torch.cuda.current_stream(arena.device))
+        for k in order:
+            a, b, _ = self.buckets[k]
+            s0, s1 = self.shard_range(k)
+            if self.cuda:
+                with torch.cuda.stream(self.stream):
+                    torch.distributed.all_gather_into_tensor(arena[a:b], arena[s0:s1], group=self.pg)
+                    if after is not None:
+                        after(k, a, b)
+                    self.gather_events[k].record(self.stream)
+            else:
+                torch.distributed.all_gather_into_tensor(arena[a:b], arena[s0:s1].clone(), group=self.pg)
+                if after is not None:
+                    after(k, a, b)
+        self.gather_pending = self.cuda
+
+    def wait_bucket(self, k):
+        if self.cuda and self.gather_pending:
+            torch.cuda.current_stream(self.g.device).wait_event(self.gather_events[k])
+
+    def wait_all(self):
+        if self.cuda and self.gather_pending:
+            torch.cuda.current_stream(self.g.device).wait_stream(self.stream)
+            self.gather_pending = False
+
+
 # ---------------------------------------------------------------------------------------------------- trainer
 class DPTrainer:
     def __init__(self, *, input_channels=3, num_classes=2, image_size=224, patch_size=16, embedding_size=768,
                  num_heads=12, num_blocks=12, batch_size=256, dtype=torch.bfloat16, device=None, lr=1e-4,
                  weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8, dropout_p=eng.DROPOUT_P, process_group=None,
-                 world_size=1, bucket_mb=48, seed=0, last_block_row0=False):
+                 world_size=1, bucket_mb=48, seed=0, last_block_row0=False, zero1=None, grad_comm=None):
         dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         eng.require_cuda(torch.empty(0, device=dev), "trainer device")
         if _C.lib().vitb200_device_ok() != 1:
@@ -143,10 +246,31 @@ class DPTrainer:
         self.layout = param_layout(C=self.C, P=self.P, E=self.E, H=self.H, L=self.L, T=self.T, B=self.B,
                                    classes=self.classes)
         self.offs, self.total = arena_offsets(self.layout)
-        z = lambda dt: torch.zeros(self.total, dtype=dt, device=dev)  # noqa: E731
-        self.p, self.g, self.m, self.v = z(torch.float32), z(torch.float32), z(torch.float32), z(torch.float32)
+        z = lambda dt, n=None: torch.zeros(self.total if n is None else n, dtype=dt, device=dev)  # noqa: E731
+        self.p, self.g = z(torch.float32), z(torch.float32)
         self.shadow = z(torch.bfloat16) if dtype == torch.bfloat16 else None
         self.buckets = make_buckets(self.layout, self.offs, self.total, int(bucket_mb * (1 << 20) / 4))
+        # exchange scheme (module docstring): ZeRO-1 by default when there is more than one rank; gradients travel
+        # in bf16 in bf16 mode and in fp32 in fp32 mode (the DP == single-GPU 1e-5 gate)
+        self.zero1 = (self.world > 1) if zero1 is None else (bool(zero1) and self.world > 1)
+        gc = grad_comm if grad_comm is not None else ("bf16" if dtype == torch.bfloat16 else "fp32")
+        if gc not in ("bf16", "fp32"):
+            raise ValueError(f"grad_comm must be 'bf16' or 'fp32', got {grad_comm!r}")
+        self.comm_dtype = torch.bfloat16 if gc == "bf16" else torch.float32
+        if self.zero1:
+            self.reducer = ShardedReducer(self.g, self.buckets, self.pg, self.world, self.rank, self.comm_dtype,
+                                          self._pack_grads)
+            # Adam moments exist only for this rank's shards (bucket order, back to back)
+            self.m, self.v = z(torch.float32, self.reducer.shard_total), z(torch.float32, self.reducer.shard_total)
+            stage_bucket = {}
+            for k, (a, b, _) in enumerate(self.buckets):
+                for (stage, _, _, _), (o, _) in zip(self.layout, self.offs):
+                    if a <= o < b:
+                        stage_bucket[stage] = k
+            self._stage_bucket = stage_bucket
+        else:
+            self.m, self.v = z(torch.float32), z(torch.float32)
+            self.reducer = None   # BucketReducer, built below once the side streams exist
 
         # pointer tables per stage
         self._views = {}
@@ -191,7 +315,8 @@ class DPTrainer:
 
         # host <-> device staging for step_host()
         self.copy_stream = torch.cuda.Stream(device=dev)
-        self.reducer = BucketReducer(self.g, self.buckets, self.pg, self.world)
+        if self.reducer is None:
+            self.reducer = BucketReducer(self.g, self.buckets, self.pg, self.world)
         self._in = [(torch.empty(self.B, self.C, self.img, self.img, dtype=torch.float32, device=dev),
                      torch.empty(self.B, dtype=torch.int64, device=dev)) for _ in range(2)]
         self._in_u8 = None  # uint8 staging buffers, allocated on the first step_host_u8
@@ -205,6 +330,8 @@ class DPTrainer:
 
     # ------------------------------------------------------------------------------------------ parameters
     def view(self, stage, field, arena=None):
+        if self.zero1:
+            self.reducer.wait_all()
         o, n, shape = self._views[(stage, field)]
         return (self.p if arena is None else arena)[o:o + n].view(shape)
 
@@ -296,13 +423,39 @@ class DPTrainer:
                             t[s_ * E + h * hs: s_ * E + (h + 1) * hs]
         return out
 
+    def _full_moments(self):
+        """(m, v) as full arenas.  ZeRO-1 keeps only this rank's shards: gather them (collective: every rank calls)."""
+        if not self.zero1:
+            return self.m, self.v
+        red, out = self.reducer, []
+        for sh in (self.m, self.v):
+            full = torch.zeros(self.total, dtype=torch.float32, device=self.dev)
+            for k, (a, b, _) in enumerate(self.buckets):
+                torch.distributed.all_gather_into_tensor(full[a:b], sh[red.shard_off[k]: red.shard_off[k] + red.shard_len[k]],
+                                                         group=self.pg)
+            out.append(full)
+        return out
+
+    def _store_moments(self, m_full, v_full):
+        if not self.zero1:
+            self.m.copy_(m_full)
+            self.v.copy_(v_full)
+            return
+        red = self.reducer
+        for k in range(len(self.buckets)):
+            s0, s1 = red.shard_range(k)
+            so, n = red.shard_off[k], red.shard_len[k]
+            self.m[so:so + n].copy_(m_full[s0:s1])
+            self.v[so:so + n].copy_(v_full[s0:s1])
+
     def optimizer_state_dict(self):
         """What `torch.optim.AdamW(reference_model.parameters()).state_dict()` would hold after the same steps:
         state indexed by position in the REFERENCE's parameter list, so a checkpoint written here resumes in the
         unmodified reference (src/train.py:73) and vice versa."""
         from VisionTransformer.checkpoint import reference_param_keys
         keys = reference_param_keys(self.L, self.H)
-        m, v = self._moment_views(self.m), self._moment_views(self.v)
+        m_full, v_full = self._full_moments()
+        m, v = self._moment_views(m_full), self._moment_views(v_full)
         state = {}
         if self.step_no > 0:
             for i, k in enumerate(keys):
@@ -322,11 +475,11 @@ class DPTrainer:
                              f"optimizer's group ({len(keys)} parameters in the reference list)")
         g = sd["param_groups"][0]
         self.lr, self.betas, self.eps, self.wd = g["lr"], tuple(g["betas"]), g["eps"], g["weight_decay"]
-        m, v = self._moment_views(self.m), self._moment_views(self.v)
+        m_full = torch.zeros(self.total, dtype=torch.float32, device=self.dev)
+        v_full = torch.zeros_like(m_full)
+        m, v = self._moment_views(m_full), self._moment_views(v_full)
         steps = set()
         with torch.no_grad():
-            self.m.zero_()
-            self.v.zero_()
             for i, k in enumerate(keys):
                 st = sd["state"].get(i)
                 if st is None:
@@ -337,6 +490,7 @@ class DPTrainer:
                 m[k].copy_(st["exp_avg"].to(self.dev, torch.float32))
                 v[k].copy_(st["exp_avg_sq"].to(self.dev, torch.float32))
                 steps.add(int(float(st["step"])))
+            self._store_moments(m_full, v_full)
         if len(steps) > 1:
             raise ValueError(f"per-parameter step counters differ ({sorted(steps)}); the flat AdamW kernel keeps one")
         self.step_no = steps.pop() if steps else 0
@@ -356,14 +510,28 @@ class DPTrainer:
                 self.rank * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
         return self.plan.dims(self.dropout_p if train else 0.0, seed)
 
+    def _params_ready(self, stage):
+        """ZeRO-1: the all-gather of the previous step's updated parameters runs on the side stream, bucket by bucket
+        in forward order; a stage's kernels wait only for the bucket that holds its parameters."""
+        if self.zero1:
+            self.reducer.wait_bucket(self._stage_bucket[stage])
+
     def forward(self, images, d, u8_layout=0):
         pl = self.plan
+        self._params_ready("embed")
         pl.embed_fwd(d, self.embed_p, images, self.xs[0], self.emb_acts, u8_layout)
         for i in range(self.L):
+            self._params_ready(i)
             pl.block_fwd(d, i, self.block_p[i], self.xs[i], self.xs[i + 1], self.blk_acts[i],
                          row0=self.row0 and i == self.L - 1)
+        self._params_ready("head")
         pl.head_fwd(d, self.head_p, self.xs[self.L], self.logits, self.head_acts, row0=self.row0)
         return self.logits
+
+    def _pack_grads(self, g_slice, out_slice):
+        """Exchange staging of one bucket (ShardedReducer): bf16 copy (if any) + fp32 gradient range cleared."""
+        _C.check(_C.lib().vitb200_grad_pack(g_slice.data_ptr(), None if out_slice is None else out_slice.data_ptr(),
+                                            g_slice.numel(), _C.stream_ptr(self.dev)))
 
     def _bucket_ready(self, stage, handles):
         self.reducer.ready(stage, handles)
@@ -393,9 +561,33 @@ class DPTrainer:
         self._bucket_ready("embed", handles)
         self.reducer.finish(handles)
 
+    def _optimizer_step_sharded(self, h):
+        """ZeRO-1: AdamW on this rank's shard of every bucket (gradients = the reduce-scattered sums, moments exist for
+        the shard only), then the all-gather of the updated parameters (+ bf16 shadow cast) on the side stream."""
+        red, L = self.reducer, _C.lib()
+        red.wait_all()   # a previous step's gathers write the non-owned ranges of p / shadow: finish them first
+        bf = self.comm_dtype == torch.bfloat16
+        for k in range(len(self.buckets)):
+            s0, s1 = red.shard_range(k)
+            so, n = red.shard_off[k], red.shard_len[k]
+            gsk = red.gs[so:so + n]
+            _C.check(L.vitb200_adamw_range(self.p[s0:s1].data_ptr(), None if bf else gsk.data_ptr(),
+                                           gsk.data_ptr() if bf else None, self.m[so:so + n].data_ptr(),
+                                           self.v[so:so + n].data_ptr(),
+                                           None if self.shadow is None else self.shadow[s0:s1].data_ptr(), n, 0, h,
+                                           _C.stream_ptr(self.dev)))
+
+        def shadow_cast(k, a, b):
+            if self.shadow is not None:
+                _C.check(L.vitb200_cast_f32_bf16(self.p[a:b].data_ptr(), self.shadow[a:b].data_ptr(), b - a,
+                                                 _C.stream_ptr(self.dev)))
+        red.gather(self.p, after=shadow_cast)
+
     def optimizer_step(self):
         self.step_no += 1
         h = _C.AdamWHyper(self.lr, self.betas[0], self.betas[1], self.eps, self.wd, self.step_no, 1.0 / self.world)
+        if self.zero1:
+            return self._optimizer_step_sharded(h)
         # one launch: AdamW over the arena, bf16 shadow written, gradient arena cleared for the next backward
         _C.check(_C.lib().vitb200_adamw_range(self.p.data_ptr(), self.g.data_ptr(), None, self.m.data_ptr(),
                                               self.v.data_ptr(),
