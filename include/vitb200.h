@@ -151,6 +151,14 @@ typedef struct {
 } vitb200_adamw_hyper;
 int vitb200_adamw_flat(float* p, const float* g, float* m, float* v, void* shadow_bf16, int64_t n,
                        vitb200_adamw_hyper h, void* stream);
+/* Device-side input pipeline: transforms.Resize((H, W)) of the reference's loader (train.py:151-155)
+ * on uint8 planes [planes = B*C, hin, win] -> [planes, hout, wout], bit-identical to PIL's bilinear ImagingResample
+ * (horizontal then vertical pass, 22-bit fixed-point triangle filter, each pass rounded to uint8).  *_bounds: int32
+ * [out, 2] = (first tap, tap count); *_coeffs: int32 [out, taps] fixed-point weights, built on the host exactly as
+ * PIL does (VisionTransformer/input_pipeline.py).  Feed the result to vitb200_embed_fwd_u8 (the /255 is fused there). */
+int vitb200_resize_bilinear_u8(const uint8_t* src, uint8_t* dst, int planes, int hin, int win, int hout, int wout,
+                               const int32_t* x_bounds, const int32_t* x_coeffs, int x_taps, const int32_t* y_bounds,
+                               const int32_t* y_coeffs, int y_taps, void* stream);
 /* Gradient-exchange staging (data-parallel trainer): out_bf16 = bf16(g) when out_bf16 != NULL, and g = 0, in one
  * pass over n elements — the bf16 copy feeds the reduce-scatter, the cleared arena is optimizer.zero_grad()
  * (train.py:94).  out_bf16 == NULL: clear only. */

@@ -130,6 +130,8 @@ def _declare(L):
         "vitb200_dropout_mask": [c_void_p, c_int64, Dropout, c_void_p],
         "vitb200_mask_cast": [c_void_p, c_void_p, c_int, Dropout, c_int64, c_void_p],
         "vitb200_adamw_flat": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, AdamWHyper, c_void_p],
+        "vitb200_resize_bilinear_u8": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int,
+                                       c_void_p, c_void_p, c_int, c_void_p],
         "vitb200_grad_pack": [c_void_p, c_void_p, c_int64, c_void_p],
         "vitb200_adamw_range": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, AdamWHyper,
                                 c_void_p],
@@ -169,7 +171,7 @@ EXPORTS = (
     "vitb200_prof_begin", "vitb200_prof_end", "vitb200_abi_sizeof", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
     "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
     "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
-    "vitb200_grad_pack", "vitb200_adamw_range", "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_fwd_u8", "vitb200_im2col_u8", "vitb200_embed_bwd",
+    "vitb200_resize_bilinear_u8", "vitb200_grad_pack", "vitb200_adamw_range", "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_fwd_u8", "vitb200_im2col_u8", "vitb200_embed_bwd",
     "vitb200_block_act_bytes", "vitb200_block_scratch_bytes", "vitb200_block_act_offset", "vitb200_block_fwd", "vitb200_block_bwd",
     "vitb200_head_act_bytes", "vitb200_head_fwd", "vitb200_head_bwd", "vitb200_block_fwd_row0",
     "vitb200_block_bwd_row0", "vitb200_head_fwd_row0", "vitb200_head_bwd_row0",

@@ -378,6 +378,51 @@ grad_pack_kernel(float* __restrict__ g, bf16* __restrict__ out, int64_t n) {
     }
 }
 
+// Bilinear resize of uint8 image planes — the arithmetic of PIL's ImagingResample (8 bits per channel), which is what
+// torchvision's transforms.Resize((H, W)) runs on the PIL images of the reference's input pipeline (train.py:151-155):
+// a HORIZONTAL pass then a VERTICAL pass, each a normalised triangle filter (support widened by the scale factor when
+// shrinking) with coefficients in 22-bit fixed point, each pass rounded and clipped to uint8 on its own.  The
+// coefficient tables (bounds = first tap and tap count, k = fixed-point weights) are built on the host in double
+// precision exactly as PIL builds them; here both passes are fused per output pixel (the intermediate uint8 of the
+// horizontal pass is recomputed for each vertical tap), so the result is bit-identical to PIL.
+__device__ __forceinline__ int resize_hpass(const uint8_t* __restrict__ row, int x, int x0, int nx,
+                                            const int32_t* __restrict__ kx, bool skip) {
+  if (skip) return row[x];                 // PIL skips a pass whose size does not change
+  int acc = 1 << 21;
+  for (int c = 0; c < nx; ++c) acc += static_cast<int>(row[x0 + c]) * kx[c];
+  acc >>= 22;
+  return acc < 0 ? 0 : (acc > 255 ? 255 : acc);
+}
+__global__ void __launch_bounds__(256)
+resize_bilinear_u8_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int planes, int hin, int win,
+                          int hout, int wout, const int32_t* __restrict__ xb, const int32_t* __restrict__ xk, int ksx,
+                          const int32_t* __restrict__ yb, const int32_t* __restrict__ yk, int ksy) {
+  const int64_t total = static_cast<int64_t>(planes) * hout * wout;
+  const bool skip_h = win == wout, skip_v = hin == hout;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int x = static_cast<int>(i % wout);
+    const int y = static_cast<int>((i / wout) % hout);
+    const int64_t pl = i / (static_cast<int64_t>(wout) * hout);
+    const uint8_t* sp = src + pl * hin * win;
+    const int x0 = xb[2 * x], nx = xb[2 * x + 1];
+    const int32_t* kx = xk + static_cast<int64_t>(x) * ksx;
+    int v;
+    if (skip_v) {
+      v = resize_hpass(sp + static_cast<int64_t>(y) * win, x, x0, nx, kx, skip_h);
+    } else {
+      const int y0 = yb[2 * y], ny = yb[2 * y + 1];
+      const int32_t* ky = yk + static_cast<int64_t>(y) * ksy;
+      int acc = 1 << 21;
+      for (int r = 0; r < ny; ++r)
+        acc += resize_hpass(sp + static_cast<int64_t>(y0 + r) * win, x, x0, nx, kx, skip_h) * ky[r];
+      v = acc >> 22;
+      v = v < 0 ? 0 : (v > 255 ? 255 : v);
+    }
+    dst[i] = static_cast<uint8_t>(v);
+  }
+}
+
 // keep[i] = 1 if element i of the (seed, stream) dropout stream is kept.  Test/debug export of the mask that the
 // fused epilogues regenerate on the fly.
 __global__ void dropout_mask_kernel(uint8_t* __restrict__ keep, int64_t n, const Dropout drop) {
@@ -560,6 +605,18 @@ int cast_f32_to_bf16(const float* in, bf16* out, int64_t n, cudaStream_t s) {
   ProfScope prof(kProfEltwise, 0.0, 1, s);
   VB_REQUIRE(aligned16(in) && (reinterpret_cast<uintptr_t>(out) & 7u) == 0, "cast: unaligned buffers");
   cast_f32_bf16_kernel<<<grid_for(n / 4 + 1, 256), 256, 0, s>>>(in, out, n);
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int resize_bilinear_u8(const uint8_t* src, uint8_t* dst, int planes, int hin, int win, int hout, int wout,
+                       const int32_t* xb, const int32_t* xk, int ksx, const int32_t* yb, const int32_t* yk, int ksy,
+                       cudaStream_t s) {
+  VB_REQUIRE(planes > 0 && hin > 0 && win > 0 && hout > 0 && wout > 0 && ksx > 0 && ksy > 0, "resize: bad geometry");
+  ProfScope prof(kProfEltwise, 0.0, 1, s);
+  const int64_t total = static_cast<int64_t>(planes) * hout * wout;
+  resize_bilinear_u8_kernel<<<grid_for(total, 256), 256, 0, s>>>(src, dst, planes, hin, win, hout, wout, xb, xk, ksx,
+                                                                  yb, yk, ksy);
   VB_CHECK_LAUNCH();
   return kOk;
 }

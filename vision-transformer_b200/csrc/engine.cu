@@ -603,6 +603,12 @@ int vitb200_adamw_flat(float* p, const float* g, float* m, float* v, void* shado
   VB_REQUIRE(h.step >= 1, "adamw: step must be >= 1");
   return adamw_flat(p, g, m, v, static_cast<bf16*>(shadow_bf16), n, to_hyper(h), static_cast<cudaStream_t>(stream));
 }
+int vitb200_resize_bilinear_u8(const uint8_t* src, uint8_t* dst, int planes, int hin, int win, int hout, int wout,
+                               const int32_t* x_bounds, const int32_t* x_coeffs, int x_taps, const int32_t* y_bounds,
+                               const int32_t* y_coeffs, int y_taps, void* stream) {
+  return resize_bilinear_u8(src, dst, planes, hin, win, hout, wout, x_bounds, x_coeffs, x_taps, y_bounds, y_coeffs,
+                            y_taps, static_cast<cudaStream_t>(stream));
+}
 int vitb200_grad_pack(float* g, void* out_bf16, int64_t n, void* stream) {
   return grad_pack(g, static_cast<bf16*>(out_bf16), n, static_cast<cudaStream_t>(stream));
 }

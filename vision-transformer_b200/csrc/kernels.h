@@ -89,6 +89,9 @@ int dropout_mask(uint8_t* keep, int64_t n, const Dropout& drop, cudaStream_t s);
 int adamw_flat(float* p, const float* g, float* m, float* v, bf16* shadow, int64_t n, const AdamWHyper& h,
                cudaStream_t s);
 int grad_pack(float* g, bf16* out, int64_t n, cudaStream_t s);
+int resize_bilinear_u8(const uint8_t* src, uint8_t* dst, int planes, int hin, int win, int hout, int wout,
+                       const int32_t* xb, const int32_t* xk, int ksx, const int32_t* yb, const int32_t* yk, int ksy,
+                       cudaStream_t s);
 int adamw_range(float* p, float* g, const bf16* gb, float* m, float* v, bf16* shadow, int64_t n, bool zero_grad,
                 const AdamWHyper& h, cudaStream_t s);
 int adamw_multi(const uint64_t* p_ptrs, const uint64_t* g_ptrs, const uint64_t* m_ptrs, const uint64_t* v_ptrs,
