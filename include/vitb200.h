@@ -118,6 +118,17 @@ int vitb200_attn_fwd(const void* qkv, void* out, float* lse, int dtype, int B, i
 /* dqkv [B*T,3E] from d_out; delta is fp32 scratch [B,H,T]. */
 int vitb200_attn_bwd(const void* qkv, const void* out, const void* d_out, const float* lse, float* delta,
                      void* dqkv, int dtype, int B, int T, int H, int hs, float scale, void* stream);
+/* NO COUNTERPART IN THE REFERENCE.  Allocation-free variant of
+ * vitb200_attn_bwd for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it): same inputs and outputs, but the fp32 scratch `delta` [B,H,T] lives in a file-scope
+ * `static __device__` array of VITB200_NOALLOC_MAX_DELTA floats (4 MiB, held by every GPU that loads the library
+ * until exit).  Fails with a clear error when B*H*T exceeds that limit.  Calls no cudaMalloc / cudaFree / allocating
+ * library routine.  All calls share the one array (it keeps the last call's contents; every value a call reads is
+ * written by that call first, so nothing needs clearing): calls that OVERLAP on the GPU (different streams) race —
+ * serialise them.  The calling thread's current device must be the device of `stream` and of the buffers. */
+#define VITB200_NOALLOC_MAX_DELTA (1 << 20)
+int vitb200_attn_bwd_noalloc(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv,
+                             int dtype, int B, int T, int H, int hs, float scale, void* stream);
 /* Debug/export: probs fp32 [B,H,T,T] = MultiHeadAttention.attention_probs (transformer.py:48); fp32 qkv only. */
 int vitb200_attn_probs(const float* qkv, float* probs, int B, int T, int H, int hs, float scale, void* stream);
 

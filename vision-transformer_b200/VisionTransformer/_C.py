@@ -122,6 +122,8 @@ def _declare(L):
         "vitb200_attn_fwd": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p],
         "vitb200_attn_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                              c_float, c_void_p],
+        "vitb200_attn_bwd_noalloc": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                     c_float, c_void_p],
         "vitb200_attn_probs": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p],
         "vitb200_im2col": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
         "vitb200_colsum": [c_void_p, c_int, c_int64, c_void_p, c_int, c_int, c_void_p],
@@ -169,7 +171,7 @@ def _declare(L):
 EXPORTS = (
     "vitb200_last_error", "vitb200_version", "vitb200_device_ok", "vitb200_launch_count", "vitb200_prof_class_name",
     "vitb200_prof_begin", "vitb200_prof_end", "vitb200_abi_sizeof", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
-    "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
+    "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_bwd_noalloc", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
     "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
     "vitb200_resize_bilinear_u8", "vitb200_grad_pack", "vitb200_adamw_range", "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_fwd_u8", "vitb200_im2col_u8", "vitb200_embed_bwd",
     "vitb200_block_act_bytes", "vitb200_block_scratch_bytes", "vitb200_block_act_offset", "vitb200_block_fwd", "vitb200_block_bwd",
@@ -201,6 +203,7 @@ def check(rc):
 
 
 ACT_QKV, ACT_ATTN, ACT_LSE, ACT_XMID = 0, 1, 2, 3
+NOALLOC_MAX_DELTA = 1 << 20   # VITB200_NOALLOC_MAX_DELTA
 
 
 def stream_ptr(device=None):

@@ -2,6 +2,7 @@
 // enqueues its kernels on the caller's stream.  No allocation, no synchronisation: every buffer (parameters,
 // gradients, saved activations, scratch) is carved from caller-owned memory with the layouts defined here.
 #include <cmath>
+#include <mutex>
 
 #include "../../include/vitb200.h"
 #include "kernels.h"
@@ -560,6 +561,46 @@ int vitb200_attn_bwd(const void* qkv, const void* out, const void* d_out, const 
                               lse, delta, static_cast<bf16*>(dqkv), B, T, H, hs, scale, s);
   return attn_f32_backward(static_cast<const float*>(qkv), static_cast<const float*>(out), static_cast<const float*>(d_out),
                            lse, delta, static_cast<float*>(dqkv), B, T, H, hs, scale, s);
+}
+// ---- allocation-free variant of vitb200_attn_bwd (see include/vitb200.h) --
+// The backward attention kernels need one fp32 scratch value per (image, head, query): delta = rowsum(dO o O).  The
+// regular entry point takes that buffer from the caller; this one keeps it in a file-scope device array, so callers
+// that may not allocate (CUDA graph capture, serving loops) pass inputs and outputs only.  In HOST code the array's
+// name is only a host-side stand-in: its device address is fetched once per device with cudaGetSymbolAddress (with
+// that device current) and that pointer is what the kernels receive.
+static __device__ __align__(256) float g_noalloc_delta[VITB200_NOALLOC_MAX_DELTA];
+
+static int noalloc_delta_ptr(float** out) {
+  constexpr int kMaxDev = 64;
+  static float* ptrs[kMaxDev] = {};
+  static std::mutex mu;
+  int dev = -1;
+  VB_CHECK_CUDA(cudaGetDevice(&dev));
+  VB_REQUIRE(dev >= 0 && dev < kMaxDev, "attn_bwd_noalloc: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    VB_CHECK_CUDA(cudaGetSymbolAddress(&p, g_noalloc_delta));   // set-up, once per device, that device current
+    VB_REQUIRE(p != nullptr, "attn_bwd_noalloc: cudaGetSymbolAddress returned a null address");
+    ptrs[dev] = static_cast<float*>(p);
+  }
+  *out = ptrs[dev];
+  return kOk;
+}
+
+int vitb200_attn_bwd_noalloc(const void* qkv, const void* out, const void* d_out, const float* lse, void* dqkv,
+                             int dtype, int B, int T, int H, int hs, float scale, void* stream) {
+  VB_REQUIRE(B > 0 && T > 0 && H > 0 && hs > 0, "attn_bwd_noalloc: empty problem B=%d T=%d H=%d hs=%d", B, T, H, hs);
+  const int64_t need = static_cast<int64_t>(B) * H * T;
+  VB_REQUIRE(need <= static_cast<int64_t>(VITB200_NOALLOC_MAX_DELTA),
+             "attn_bwd_noalloc: B*H*T = %lld scratch values exceed the static limit VITB200_NOALLOC_MAX_DELTA = %d; "
+             "use vitb200_attn_bwd with a caller-provided delta buffer", static_cast<long long>(need),
+             VITB200_NOALLOC_MAX_DELTA);
+  float* delta = nullptr;
+  VB_PROPAGATE(noalloc_delta_ptr(&delta));
+  // every one of the B*H*T values is written by the delta kernel before the backward kernels read it: nothing in the
+  // shared array has to start at zero, and stale contents of an earlier (larger) call are never read
+  return vitb200_attn_bwd(qkv, out, d_out, lse, delta, dqkv, dtype, B, T, H, hs, scale, stream);
 }
 int vitb200_attn_probs(const float* qkv, float* probs, int B, int T, int H, int hs, float scale, void* stream) {
   VB_REQUIRE(static_cast<int64_t>(B) * H <= 65535, "attention: B*H exceeds 65535");
