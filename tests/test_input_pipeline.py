@@ -78,7 +78,8 @@ def test_gpu_resize_plus_model_equals_torchvision_loader(lib):
     tf = T.Compose([T.Resize((img, img)), T.ToTensor()])                      # reference train.py:151-155
     x_ref = torch.stack([tf(Image.fromarray(r)) for r in raw]).cuda()
     x_u8 = ip.Resize(img)(torch.from_numpy(raw).permute(0, 3, 1, 2).contiguous().cuda())
-    assert torch.equal(x_u8.float() / 255, x_ref)
+    # ToTensor divides by 255 on the CPU (true division; a CUDA `x / 255` multiplies by a reciprocal and differs by 1 ulp)
+    assert torch.equal(x_u8.cpu().float() / 255, x_ref.cpu())
     torch.manual_seed(0)
     m = vit.VisionTransformer(config.ViTConfig(3, 10, (img // 16) ** 2, 64, 16, 4, 2, "cuda", B)).cuda().eval()
     assert torch.equal(m(x_u8), m(x_ref))

@@ -286,11 +286,25 @@ def _zero1_worker(rank, world, port, backend, out):
                 y = torch.randint(0, classes, (world * B,), generator=gen)
                 xs, ys = x[rank * B:(rank + 1) * B].to(dev), y[rank * B:(rank + 1) * B].to(dev)
                 la, lb = tr.step(xs, ys, train=False).item(), ar.step(xs, ys, train=False).item()
-                assert abs(la - lb) < (1e-6 if comm == "fp32" else 5e-3), (step, la, lb)
+                # bf16 exchange: Adam's first steps move every weight by ~lr whatever the gradient's size, so a
+                # gradient entry whose sign flips under bf16 rounding moves that weight the other way: loss to 2 %
+                assert abs(la - lb) < (1e-6 if comm == "fp32" else 2e-2 * abs(lb)), (step, la, lb)
+                if step == 0:
+                    # after ONE step the first moment is 0.1 x the exchanged mean gradient: this isolates the exchange
+                    # itself (bf16 rounding of each rank's contribution, 2^-9 relative) from trajectory divergence
+                    o1, o2 = tr.optimizer_state_dict(), ar.optimizer_state_dict()
+                    first = 1.0 - min(cosine(o1["state"][i]["exp_avg"], o2["state"][i]["exp_avg"]) for i in o1["state"])
+                    assert first < (1e-10 if comm == "fp32" else 1e-4), (comm, first)
             a, b = tr.state_dict(), ar.state_dict()
-            worst = max(rel_err(a[k], b[k]) for k in a)
+            if comm == "fp32":
+                worst = max(rel_err(a[k], b[k]) for k in a)
+            else:   # absolute: at most 2 lr per step on any one weight (3 steps, lr 1e-3), and nearly all agree
+                worst = max(float((a[k] - b[k]).abs().max()) for k in a)
             oa, ob = tr.optimizer_state_dict(), ar.optimizer_state_dict()
-            worst_m = max(rel_err(oa["state"][i]["exp_avg"], ob["state"][i]["exp_avg"]) for i in oa["state"])
+            if comm == "fp32":
+                worst_m = max(rel_err(oa["state"][i]["exp_avg"], ob["state"][i]["exp_avg"]) for i in oa["state"])
+            else:
+                worst_m = 1.0 - min(cosine(oa["state"][i]["exp_avg"], ob["state"][i]["exp_avg"]) for i in oa["state"])
             steps_ok = all(float(oa["state"][i]["step"]) == 3.0 for i in oa["state"])
             # resume: the gathered state loads back into shards
             tr.load_optimizer_state_dict(ob)
@@ -319,9 +333,10 @@ def test_two_rank_zero1_matches_allreduce_trainer(lib):
         worst, worst_m, steps_ok, resume, g_nz = by_comm["fp32"]
         assert worst < 1e-5 and worst_m < 1e-5 and steps_ok and resume == 0.0 and g_nz == 0, (r, by_comm["fp32"])
         worst, worst_m, steps_ok, resume, g_nz = by_comm["bf16"]
-        # bf16 gradient exchange: the first Adam steps move every weight by ~lr regardless of gradient magnitude, so
-        # parameters agree to a few 1e-3 of lr-sized steps; moments to bf16 precision
-        assert worst < 2e-3 and worst_m < 2e-2 and steps_ok and g_nz == 0, (r, by_comm["bf16"])
+        # bf16 gradient exchange: the exchange itself is checked after the first step (inside the worker); after three
+        # steps the trajectories have separated by sign flips of near-zero gradient entries: parameters within 2 lr per
+        # step (absolute), first moments still cosine >= 0.98
+        assert worst <= 2.1 * 3 * 1e-3 and worst_m < 2e-2 and steps_ok and g_nz == 0, (r, by_comm["bf16"])
 
 
 def test_trainer_rejects_bad_labels_and_out_of_range_targets(lib):
