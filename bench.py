@@ -26,7 +26,8 @@ MODELS = {
     "vit_s16": (384, 6, 12, 16, 224),
     "vit_b16": (768, 12, 12, 16, 224),
     "vit_l16": (1024, 16, 24, 16, 224),
-    "vit_h14": (1280, 16, 32, 14, 336),
+    "vit_h14": (1280, 16, 32, 14, 336),        # C5a: 24 x 24 + 1 = 577 tokens
+    "vit_h14_384": (1280, 16, 32, 14, 384),    # C5b: the literal BASELINE string, 27 x 27 + 1 = 730 tokens (conv floor-crops)
 }
 METRIC = "ViT-B/16 train images/s"
 UNIT = "images/s"

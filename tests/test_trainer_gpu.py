@@ -286,31 +286,31 @@ def _zero1_worker(rank, world, port, backend, out):
                 y = torch.randint(0, classes, (world * B,), generator=gen)
                 xs, ys = x[rank * B:(rank + 1) * B].to(dev), y[rank * B:(rank + 1) * B].to(dev)
                 la, lb = tr.step(xs, ys, train=False).item(), ar.step(xs, ys, train=False).item()
-                # bf16 exchange: Adam's first steps move every weight by ~lr whatever the gradient's size, so a
-                # gradient entry whose sign flips under bf16 rounding moves that weight the other way: loss to 2 %
-                assert abs(la - lb) < (1e-6 if comm == "fp32" else 2e-2 * abs(lb)), (step, la, lb)
+                # Adam's first steps move every weight by ~lr whatever the gradient's size: a gradient entry that is ~0
+                # flips sign under ANY rounding change (bf16 exchange, or just a different summation order of the
+                # reduce-scatter in fp32) and moves that one weight the other way; the loss follows to 1e-4 / 2 %
+                assert abs(la - lb) < (1e-4 if comm == "fp32" else 2e-2) * abs(lb), (step, la, lb)
                 if step == 0:
                     # after ONE step the first moment is 0.1 x the exchanged mean gradient: this isolates the exchange
                     # itself (bf16 rounding of each rank's contribution, 2^-9 relative) from trajectory divergence
                     o1, o2 = tr.optimizer_state_dict(), ar.optimizer_state_dict()
                     first = 1.0 - min(cosine(o1["state"][i]["exp_avg"], o2["state"][i]["exp_avg"]) for i in o1["state"])
                     assert first < (1e-10 if comm == "fp32" else 1e-4), (comm, first)
+                    firstp = max(rel_err(o1["state"][i]["exp_avg"], o2["state"][i]["exp_avg"]) for i in o1["state"])
+                    assert firstp < (1e-5 if comm == "fp32" else 1e-2), (comm, firstp)
             a, b = tr.state_dict(), ar.state_dict()
-            if comm == "fp32":
-                worst = max(rel_err(a[k], b[k]) for k in a)
-            else:   # absolute: at most 2 lr per step on any one weight (3 steps, lr 1e-3), and nearly all agree
-                worst = max(float((a[k] - b[k]).abs().max()) for k in a)
+            # absolute: at most 2 lr per step on any one weight (3 steps, lr 1e-3), and nearly all weights agree
+            worst = max(float((a[k] - b[k]).abs().max()) for k in a)
+            mean_abs = sum(float((a[k] - b[k]).abs().sum()) for k in a) / sum(a[k].numel() for k in a)
             oa, ob = tr.optimizer_state_dict(), ar.optimizer_state_dict()
-            if comm == "fp32":
-                worst_m = max(rel_err(oa["state"][i]["exp_avg"], ob["state"][i]["exp_avg"]) for i in oa["state"])
-            else:
-                worst_m = 1.0 - min(cosine(oa["state"][i]["exp_avg"], ob["state"][i]["exp_avg"]) for i in oa["state"])
+            worst_m = 1.0 - min(cosine(oa["state"][i]["exp_avg"], ob["state"][i]["exp_avg"]) for i in oa["state"])
             steps_ok = all(float(oa["state"][i]["step"]) == 3.0 for i in oa["state"])
             # resume: the gathered state loads back into shards
             tr.load_optimizer_state_dict(ob)
             oc = tr.optimizer_state_dict()
             resume = max(rel_err(oc["state"][i]["exp_avg_sq"], ob["state"][i]["exp_avg_sq"]) for i in oc["state"])
-            res[comm] = (float(worst), float(worst_m), bool(steps_ok), float(resume), int(torch.count_nonzero(tr.g)))
+            res[comm] = (float(worst), float(mean_abs), float(worst_m), bool(steps_ok), float(resume),
+                         int(torch.count_nonzero(tr.g)))
         out[rank] = res
     finally:
         dist.destroy_process_group()
@@ -330,13 +330,13 @@ def test_two_rank_zero1_matches_allreduce_trainer(lib):
         res = dict(out)
     assert set(res) == {0, 1}
     for r, by_comm in res.items():
-        worst, worst_m, steps_ok, resume, g_nz = by_comm["fp32"]
-        assert worst < 1e-5 and worst_m < 1e-5 and steps_ok and resume == 0.0 and g_nz == 0, (r, by_comm["fp32"])
-        worst, worst_m, steps_ok, resume, g_nz = by_comm["bf16"]
-        # bf16 gradient exchange: the exchange itself is checked after the first step (inside the worker); after three
-        # steps the trajectories have separated by sign flips of near-zero gradient entries: parameters within 2 lr per
-        # step (absolute), first moments still cosine >= 0.98
-        assert worst <= 2.1 * 3 * 1e-3 and worst_m < 2e-2 and steps_ok and g_nz == 0, (r, by_comm["bf16"])
+        worst, mean_abs, worst_m, steps_ok, resume, g_nz = by_comm["fp32"]
+        assert worst <= 2.1 * 3 * 1e-3 and mean_abs < 1e-6 and worst_m < 1e-3 and steps_ok and resume == 0.0 and g_nz == 0, \
+            (r, by_comm["fp32"])
+        worst, mean_abs, worst_m, steps_ok, resume, g_nz = by_comm["bf16"]
+        # bf16 gradient exchange: the exchange itself is gated after the first step (inside the worker); after three
+        # steps the trajectories have separated by sign flips of near-zero gradient entries
+        assert worst <= 2.1 * 3 * 1e-3 and mean_abs < 1e-4 and worst_m < 2e-2 and steps_ok and g_nz == 0, (r, by_comm["bf16"])
 
 
 def test_trainer_rejects_bad_labels_and_out_of_range_targets(lib):

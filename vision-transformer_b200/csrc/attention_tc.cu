@@ -39,6 +39,7 @@ struct FwdParams {
   int T, TP, H, items;   // TP = T rounded up to a multiple of 16 (UMMA N and PV K extent)
   float scale_log2;      // scale * log2(e)
   int st256;             // output rows are 32-byte aligned: store whole sectors per thread
+  int order;             // MMA issue order: 1 skewed (default), 0 lock-step (VITB200_ATTN_FWD_ORDER=0, A/B timing)
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -109,40 +110,70 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
       const uint32_t idesc_s = ptx::make_idesc_bf16_f32(QT, p.TP, 0, 0);   // S: M=128, N=TP, A,B K-major
       const uint32_t idesc_o = ptx::make_idesc_bf16_f32(QT, HS, 0, 1);     // O: M=128, N=64, B (=V) MN-major
       const int ntile = p.T > QT ? 2 : 1;
-      int it = 0;
-      for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
-        const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;       // phase of the 2-deep smem ring
-        const uint32_t tp = it & 1;              // phase of the per-item barriers
-        const uint32_t sq = ptx::smem_u32(smem + st * STAGE_BYTES);
-        const uint32_t sk = sq + TILE_BYTES, sv = sk + TILE_BYTES;
-        ptx::mbar_wait(&kv_full[st], ph);
+      const int nks = p.TP / 16;
+      const bool dual = nks >= 2;              // both O accumulators get initialised by the first two k-steps
+      // S = Q_t K^T of one (item, tile) unit into the tile's tensor-memory slot
+      auto issue_s = [&](int it2, int t) {
+        const uint32_t sq = ptx::smem_u32(smem + (it2 & 1) * STAGE_BYTES), sk = sq + TILE_BYTES;
+        ptx::mbar_wait(&t_free[t], (static_cast<uint32_t>(it2) & 1u) ^ 1u);
         ptx::tc_fence_after();
-        for (int t = 0; t < ntile; ++t) {
-          ptx::mbar_wait(&t_free[t], tp ^ 1u);
-          ptx::tc_fence_after();
-          const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
+        const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
 #pragma unroll
-          for (int k = 0; k < HS / 16; ++k) {
-            const uint64_t da = ptx::make_smem_desc_sw128(sq + t * (QT * HS * 2) + k * 32, 16, 1024);
-            const uint64_t db = ptx::make_smem_desc_sw128(sk + k * 32, 16, 1024);
-            ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
-          }
-          ptx::umma_commit(&s_full[t]);
+        for (int k = 0; k < HS / 16; ++k) {
+          const uint64_t da = ptx::make_smem_desc_sw128(sq + t * (QT * HS * 2) + k * 32, 16, 1024);
+          const uint64_t db = ptx::make_smem_desc_sw128(sk + k * 32, 16, 1024);
+          ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
         }
-        for (int t = 0; t < ntile; ++t) {
-          ptx::mbar_wait(&p_ready[t], tp);
+        ptx::umma_commit(&s_full[t]);
+      };
+      // O = P V of one unit.  Back-to-back MMAs into ONE accumulator serialise on its latency (~114 clk each against
+      // ~55 clk for independent ones, tools/probe): the k-steps alternate between two accumulators (columns 128..191
+      // and 192..255 of the slot; S is dead by then) which the epilogue adds.
+      auto issue_pv = [&](int it2, int t) {
+        const uint32_t sv = ptx::smem_u32(smem + (it2 & 1) * STAGE_BYTES) + 2 * TILE_BYTES;
+        ptx::mbar_wait(&p_ready[t], static_cast<uint32_t>(it2) & 1u);
+        ptx::tc_fence_after();
+        const uint32_t a_p = tmem_base + static_cast<uint32_t>(t * 256);
+        for (int k = 0; k < nks; ++k) {
+          // V as MN-major B: 16 key rows per k-step = 16 * 128 B; 8-row groups 1024 B apart
+          const uint64_t db = ptx::make_smem_desc_sw128(sv + k * 2048, 64 * 128, 1024);
+          const uint32_t d_o = a_p + 128u + ((dual && (k & 1)) ? 64u : 0u);
+          ptx::umma_f16_ts(d_o, a_p + static_cast<uint32_t>(k * 8), db, idesc_o, k > (dual ? 1 : 0) ? 1u : 0u);
+        }
+        ptx::umma_commit(&o_full[t]);
+      };
+      const int my_items = blockIdx.x < p.items ? (p.items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
+                                                    static_cast<int>(gridDim.x) : 0;
+      if (p.order == 0) {
+        // lock-step order (round 1): S of both tiles, then P.V of both tiles, item by item
+        for (int it = 0; it < my_items; ++it) {
+          ptx::mbar_wait(&kv_full[it & 1], (it >> 1) & 1);
           ptx::tc_fence_after();
-          const uint32_t a_p = tmem_base + static_cast<uint32_t>(t * 256);
-          const uint32_t d_o = a_p + 128;
-          for (int k = 0; k < p.TP / 16; ++k) {
-            // V as MN-major B: 16 key rows per k-step = 16 * 128 B; 8-row groups 1024 B apart
-            const uint64_t db = ptx::make_smem_desc_sw128(sv + k * 2048, 64 * 128, 1024);
-            ptx::umma_f16_ts(d_o, a_p + static_cast<uint32_t>(k * 8), db, idesc_o, k > 0 ? 1u : 0u);
-          }
-          ptx::umma_commit(&o_full[t]);
+          for (int t = 0; t < ntile; ++t) issue_s(it, t);
+          for (int t = 0; t < ntile; ++t) issue_pv(it, t);
+          ptx::umma_commit(&kv_empty[it & 1]);
         }
-        ptx::umma_commit(&kv_empty[st]);
+      } else if (my_items > 0) {
+        // skewed order: P.V(it, t) is followed at once by S(it+1, t), so that a tile's softmax warps get their next
+        // logits while the OTHER tile's are still exponentiating — the two element-wise groups stop running in
+        // lock-step, and the SFU works on one tile while the tensor pipe and the epilogue serve the other
+        ptx::mbar_wait(&kv_full[0], 0);
+        ptx::tc_fence_after();
+        for (int t = 0; t < ntile; ++t) issue_s(0, t);
+        for (int it = 0; it < my_items; ++it) {
+          const bool more = it + 1 < my_items;
+          for (int t = 0; t < ntile; ++t) {
+            issue_pv(it, t);
+            if (t == ntile - 1) ptx::umma_commit(&kv_empty[it & 1]);
+            if (more) {
+              if (t == 0) {
+                ptx::mbar_wait(&kv_full[(it + 1) & 1], ((it + 1) >> 1) & 1);
+                ptx::tc_fence_after();
+              }
+              issue_s(it + 1, t);
+            }
+          }
+        }
       }
     }
   } else {
@@ -235,6 +266,13 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
       for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
         ptx::tmem_ld_32x32(t_row + 128u + static_cast<uint32_t>(c * 32), r);
+        if (p.TP >= 32) {                       // second accumulator (odd k-steps of P.V), see the MMA issuer
+          uint32_t r2[32];
+          ptx::tmem_ld_32x32(t_row + 192u + static_cast<uint32_t>(c * 32), r2);
+          ptx::tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+        }
         ptx::tmem_ld_wait();
         if (live) {
           uint32_t w[16];
@@ -696,6 +734,8 @@ int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H,
   p.T = T; p.TP = (T + 15) / 16 * 16; p.H = H; p.items = B * H;
   p.scale_log2 = scale * kLog2e;
   p.st256 = (reinterpret_cast<uintptr_t>(out) & 31u) == 0 && (E * 2) % 32 == 0;
+  static const int order = getenv("VITB200_ATTN_FWD_ORDER") ? atoi(getenv("VITB200_ATTN_FWD_ORDER")) : 1;
+  p.order = order;
   ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * static_cast<double>(T) * hs, 1, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
   VB_CHECK_CUDA(launch_pdl(attn_tc_fwd_kernel, dim3(grid), dim3(kThreads), SMEM_BYTES, stream, 1, tm, out, lse, p));
