@@ -333,6 +333,9 @@ struct BwdParams {
   int tile_bytes, stage_bytes;              // TP*128, 4*tile_bytes + kStatBytes
   float scale, scale_log2;
   int st256;                                // dqkv rows are 32-byte aligned: drain with 32-byte stores
+  int full;                                 // 1: ONE full-width chunk per unit in ONE slot (see attn_tc_backward), 0: chunked, 2 slots
+  int hc;                                   // full: column split between the two element-wise groups (0: balanced)
+  int acc0, acc1;                           // tensor-memory columns of the two accumulators
   int dbg;                                  // timing experiments only (VITB200_ATTN_DBG), 0 in production
   long long* trace;                         // optional event trace of CTA 0 (tools/attn_trace.py), else nullptr
 };
@@ -352,7 +355,9 @@ __device__ __forceinline__ void tmem_st_n(uint32_t taddr, const uint32_t (&r)[N]
 }
 
 // Column split of a chunk of wc columns (a multiple of 16) between the two element-wise groups, in whole k-steps.
-__device__ __forceinline__ int bwd_split(int wc) { return ((wc >> 4) + 1) >> 1 << 4; }
+__device__ __forceinline__ int bwd_split(int wc, int hc = 0) {
+  return hc > 0 ? (hc < wc ? hc : wc) : ((wc >> 4) + 1) >> 1 << 4;
+}
 
 // N columns [c0, c0+N) of one chunk (global column index gcol0 .. gcol0+N-1) for this thread's row.
 template <int MODE, int N>
@@ -428,8 +433,9 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
   const int ntile = p.T > QT ? 2 : 1;
   const int nchk = p.nchk, W = p.W;
   const bool dual = p.TP >= 32;      // MODE 0: a unit's first chunk then has >= 2 k-steps, so both accumulators get initialised
-  constexpr uint32_t kAcc0 = 384u;   // MODE 0: dQ (even k-steps) | MODE 1: dV
-  constexpr uint32_t kAcc1 = 448u;   // MODE 0: dQ (odd k-steps)  | MODE 1: dK
+  const uint32_t kAcc0 = static_cast<uint32_t>(p.acc0);   // MODE 0: dQ (even k-steps) | MODE 1: dV
+  const uint32_t kAcc1 = static_cast<uint32_t>(p.acc1);   // MODE 0: dQ (odd k-steps)  | MODE 1: dK
+  const bool full = p.full != 0;
 
   if (threadIdx.x == 0) {
     ptx::tma_prefetch_desc(&tm_qkv);
@@ -512,14 +518,17 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         for (int t = 0; t < ntile; ++t) {
           const uint32_t a1t = a1 + static_cast<uint32_t>(t * (QT * 128 / 16)), a2t = a2 + static_cast<uint32_t>(t * (QT * 128 / 16));
           for (int j = 0; j < nchk; ++j, ++g) {
-            const int slot = g & 1;
-            const uint32_t gph = (static_cast<uint32_t>(g) >> 1) & 1u;
+            const int slot = full ? 0 : (g & 1);
+            const uint32_t gph = full ? (static_cast<uint32_t>(g) & 1u) : ((static_cast<uint32_t>(g) >> 1) & 1u);
             const int col0 = j * W, wc = min(W, p.TP - col0);
             const uint32_t idesc_s = kIdescS0 | (static_cast<uint32_t>(wc >> 3) << 17);
             const uint32_t tS = tmem_base + static_cast<uint32_t>(slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
             const uint32_t b1c = b1 + static_cast<uint32_t>(col0 * 8), b2c = b2 + static_cast<uint32_t>(col0 * 8);
             VB_TR(1);
             ptx::mbar_wait(&slot_free[slot], gph ^ 1u);
+            // full width: the accumulators live INSIDE the slot (columns the packed operands do not need), so the
+            // previous unit must have been drained before its slot is overwritten
+            if (full) ptx::mbar_wait(acc_free, (static_cast<uint32_t>(g) & 1u) ^ 1u);
             ptx::tc_fence_after();
             VB_TR(2);
 #pragma unroll
@@ -550,15 +559,15 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         const uint32_t o0 = ptx::smem_desc_lo(MODE == 0 ? sk : sdo, 64 * 128), o1 = ptx::smem_desc_lo(sq, 64 * 128);
         for (int t = 0; t < ntile; ++t, ++u) {
           for (int j = 0; j < nchk; ++j, ++g) {
-            const int slot = g & 1;
-            const uint32_t gph = (static_cast<uint32_t>(g) >> 1) & 1u;
+            const int slot = full ? 0 : (g & 1);
+            const uint32_t gph = full ? (static_cast<uint32_t>(g) & 1u) : ((static_cast<uint32_t>(g) >> 1) & 1u);
             const int col0 = j * W, nk = min(W, p.TP - col0) >> 4;
             const uint32_t tS = tmem_base + static_cast<uint32_t>(slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
             const uint32_t b0 = o0 + static_cast<uint32_t>(col0 * 8), b1 = o1 + static_cast<uint32_t>(col0 * 8);
             const uint32_t keep = j == 0 ? 0u : 1u;                    // first chunk of a unit overwrites the accumulators
             // bf16 operand of k-step k: columns 8k.. of the region for the first group's k-steps, shifted by hc/2 for
             // the second group's (it packs in place from column hc on)
-            const int kh = bwd_split(nk << 4) >> 4;
+            const int kh = bwd_split(nk << 4, p.hc) >> 4;
             const uint32_t sh = static_cast<uint32_t>(kh * 8);
             VB_TR(4);
             ptx::mbar_wait(&ew_done[2 * slot], gph);
@@ -570,7 +579,7 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
             // accumulators by k-step parity (summed in the drain); MODE 1 alternates dV and dK.
             const uint32_t keep1 = dual ? keep : 1u;
 #pragma unroll
-            for (int k = 0; k < 6; ++k) {
+            for (int k = 0; k < 16; ++k) {
               if (k < nk) {
                 if (k == kh) {
                   ptx::mbar_wait(&ew_done[2 * slot + 1], gph);
@@ -671,13 +680,13 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
           // S/dP -> operand latency of a chunk, which is what bounds the slot cycle (S/dP MMAs -> element-wise ->
           // output MMAs -> slot free).  Each group packs its bf16 results in place at the start of ITS OWN column
           // range (ascending, so it only overwrites what it has already read); the output-MMA issuer knows the layout.
-          const int slot = g & 1;
+          const int slot = full ? 0 : (g & 1);
           const int col0 = j * W, wc = min(W, p.TP - col0);
-          const int hc = bwd_split(wc);
+          const int hc = bwd_split(wc, p.hc);
           const int cbeg = grp == 0 ? 0 : hc, cend = grp == 0 ? hc : wc;
           const uint32_t tS = lane_base + static_cast<uint32_t>(slot * 2 * W), tP = tS + static_cast<uint32_t>(W);
           VB_TR(10);
-          ptx::mbar_wait(&sd_full[slot], (static_cast<uint32_t>(g) >> 1) & 1u);
+          ptx::mbar_wait(&sd_full[slot], full ? (static_cast<uint32_t>(g) & 1u) : ((static_cast<uint32_t>(g) >> 1) & 1u));
           ptx::tc_fence_after();
           VB_TR(11);
           int c0 = cbeg;
@@ -693,7 +702,8 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
           VB_TR(12);
           // Drain a unit's accumulators one chunk LATE (after the first chunk of the next unit): right after the unit's
           // own last chunk its output MMAs have only just been issued and both groups would sit on acc_full.
-          while (next_drain < total_units && (next_drain + 1) * nchk - 1 < g) drain(next_drain++);
+          // (full width: at once — the next unit's S/dP cannot be issued before this unit's accumulators are drained)
+          while (next_drain < total_units && (next_drain + 1) * nchk - 1 < g + (full ? 1 : 0)) drain(next_drain++);
         }
       }
     }
@@ -778,9 +788,30 @@ int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const f
   VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * static_cast<double>(T) * hs, 2, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
-  chunking(96);    // two slots of 2W columns + two 64-column accumulators: 4W + 128 <= 512
+  // Two tensor-memory plans.  CHUNKED (round 1): chunks of W <= 96 columns flow through two [S | dP] slots, accumulators
+  // at columns 384 / 448 (4W + 128 <= 512).  FULL WIDTH (round 2): ONE chunk of all TP columns per unit in ONE slot
+  // (S at 0, dP at TP), the accumulators inside columns that are dead by the time the output MMAs start.  These
+  // kernels are bound by the NUMBER of MMAs (each 128 x N x 16 instruction costs 55-110 clk whatever N <= 112 is:
+  // profiles/r02_attn_bwd_bound_experiments.txt — without any element-wise work the two kernels still take 190 of
+  // 290 us), and full width needs 8 instead of 24 S/dP MMAs per 128-row tile at T = 197, at the price of no overlap
+  // between a unit's element-wise pass and the next unit's MMAs.  VITB200_ATTN_BWD_FULL: bit 0 = dQ kernel, bit 1 =
+  // dK/dV kernel (A/B switch; default set from the measurement).
+  static const int full_mask = getenv("VITB200_ATTN_BWD_FULL") ? atoi(getenv("VITB200_ATTN_BWD_FULL")) : 0;
+  const bool can_full = p.TP >= 144 && p.TP <= 224;
+  auto plan = [&](int mode) {
+    if (can_full && ((full_mask >> mode) & 1)) {
+      p.full = 1; p.nchk = 1; p.W = p.TP;
+      if (mode == 0) { p.hc = 0; p.acc0 = 2 * p.TP; p.acc1 = p.TP; }      // dQ halves: spare columns | group 0's dP columns
+      else { p.hc = 128; p.acc0 = 64; p.acc1 = p.TP + 64; }              // dV | dK: the unpacked upper half of group 0's columns
+    } else {
+      p.full = 0; p.hc = 0; p.acc0 = 384; p.acc1 = 448;
+      chunking(96);    // two slots of 2W columns + two 64-column accumulators: 4W + 128 <= 512
+    }
+  };
+  plan(1);
   VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<1>, dim3(grid), dim3(kBwdThreads), smem, stream, 1, tq, td, lse, delta, dqkv, p));
   VB_CHECK_LAUNCH();
+  plan(0);
   VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<0>, dim3(grid), dim3(kBwdThreads), smem, stream, 1, tq, td, lse, delta, dqkv, p));
   VB_CHECK_LAUNCH();
   return kOk;
