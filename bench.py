@@ -48,6 +48,7 @@ def parse():
     ap.add_argument("--no-module-path", action="store_true", help="skip the drop-in nn.Module side number")
     ap.add_argument("--no-row0", action="store_true", help="skip the last-block dead-row-elimination side number")
     ap.add_argument("--no-ref-eager", action="store_true", help="skip the reference-eager-on-this-GPU side number")
+    ap.add_argument("--no-graph", action="store_true", help="skip the CUDA-graph replay side number")
     ap.add_argument("--bucket-mb", type=float, default=0,
                     help="gradient bucket size in MB of fp32 gradient; 0 = auto: ONE bucket (exchange after backward, nothing "
                          "co-runs with the persistent GEMMs) when the arena is <= 400 MB, else 48 MB buckets overlapped "
@@ -363,6 +364,19 @@ def run_b200(args):
                                   "patch gather"}
         del x8
 
+    # ---- side number: the same step captured into ONE CUDA graph and replayed
+    graph_line = None
+    if world == 1 and not args.no_graph:
+        try:
+            tr.capture_graph()
+            g_ms, _ = timed(lambda i: tr.step_graph(xd[i % n_host], yd[i % n_host]), args.steps, 3)
+            graph_line = {"value": gb / (g_ms / args.steps * 1e-3), "unit": UNIT, "ms_per_step": g_ms / args.steps,
+                          "loss_after": float(tr.loss.item()),
+                          "what": "DPTrainer.step_graph: fwd+CE+bwd+AdamW as one cudaGraphLaunch per step; dropout seed and "
+                                  "Adam bias corrections advance in device memory inside the graph"}
+        except Exception as e:  # a side number must never fail the bench
+            graph_line = {"error": repr(e)[:200]}
+
     # ---- live per-kernel-class timing (CUDA events on the launching stream) over 2 more steps: `roofline`
     pk = peaks()
     barrier()
@@ -497,7 +511,7 @@ def run_b200(args):
         "mfu": {"algorithmic_tflops_per_gpu": step_tflops, "of_measured_sustained": step_tflops / pk["tflops_sustained"],
                 "of_measured_burst": step_tflops / pk["tflops_burst"], "of_datasheet_2250": step_tflops / 2250.0},
         "kernels": kern, "loss_after": loss_after, "last_block_row0": row0,
-        "module_path": module_path, "reference_gpu_eager": ref_eager,
+        "module_path": module_path, "reference_gpu_eager": ref_eager, "cuda_graph": graph_line,
     }
     emit(line)
     if world > 1:

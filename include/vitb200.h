@@ -180,6 +180,15 @@ int vitb200_grad_pack(float* g, void* out_bf16, int64_t n, void* stream);
  * (optimizer.zero_grad(), train.py:94 — the backward kernels accumulate into it). */
 int vitb200_adamw_range(float* p, float* g, const void* g_bf16, float* m, float* v, void* shadow_bf16, int64_t n,
                         int zero_grad, vitb200_adamw_hyper h, void* stream);
+/* Per-step scalars for a training step captured into a CUDA graph (the reference has no counterpart):
+ * a 32-byte device struct { uint64 seed_add; int32 step; float bias_corr1; float inv_sqrt_bc2; pad }.
+ * vitb200_step_state_advance (one tiny kernel, capturable): step += 1, seed_add = (step - 1) * seed_stride, Adam bias
+ * corrections of the new step (double precision, as the host computes them).  Point vitb200_dims.seed_dev at the
+ * struct and pass it to vitb200_adamw_range_dev, which is vitb200_adamw_range with the two corrections read from it. */
+#define VITB200_STEP_STATE_BYTES 32
+int vitb200_step_state_advance(void* step_state, float beta1, float beta2, uint64_t seed_stride, void* stream);
+int vitb200_adamw_range_dev(float* p, float* g, const void* g_bf16, float* m, float* v, void* shadow_bf16, int64_t n,
+                            int zero_grad, vitb200_adamw_hyper h, const void* step_state, void* stream);
 /* Multi-tensor form: device arrays of tensor addresses / sizes and a (block -> tensor, chunk of 65536) table. */
 int vitb200_adamw_multi(const uint64_t* p_ptrs, const uint64_t* g_ptrs, const uint64_t* m_ptrs,
                         const uint64_t* v_ptrs, const uint64_t* shadow_ptrs, const int64_t* sizes,
@@ -199,6 +208,9 @@ typedef struct {
   float dropout_p;      /* 0 in eval mode; the reference hard-codes 0.2 when training (transformer.py:35,53) */
   uint64_t seed;        /* dropout seed for this step */
   float ln_eps;
+  const uint64_t* seed_dev;  /* optional DEVICE word added to `seed` when a mask is drawn (NULL: none).  Kernel arguments
+                              * are frozen when a step is captured into a CUDA graph; the per-step part of the seed then
+                              * lives in a vitb200 step state (below) that the graph itself advances. */
 } vitb200_dims;
 
 /* PatchEmbedding (vit.py:9-43).  w_lp is the dtype copy of w_f32 ([E, C*P*P]); used when dtype == BF16 and

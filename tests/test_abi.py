@@ -34,7 +34,7 @@ def test_python_binding_table_covers_header():
 def test_struct_layouts_match_header_sizes():
     # sizes computed from the C declarations (LP64): guards against silent ctypes / header drift
     assert ctypes.sizeof(_C.Dropout) == 24
-    assert ctypes.sizeof(_C.Dims) == 64
+    assert ctypes.sizeof(_C.Dims) == 72
     assert ctypes.sizeof(_C.AdamWHyper) == 28
     assert ctypes.sizeof(_C.BlockParams) == 11 * 8
     assert ctypes.sizeof(_C.GemmArgs) == 192

@@ -339,6 +339,37 @@ def test_two_rank_zero1_matches_allreduce_trainer(lib):
         assert worst <= 2.1 * 3 * 1e-3 and mean_abs < 1e-4 and worst_m < 2e-2 and steps_ok and g_nz == 0, (r, by_comm["bf16"])
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_graph_replay_equals_eager_steps_with_live_dropout(lib, dtype):
+    """the whole step captured into ONE CUDA graph.  With dropout LIVE, replays must draw the masks and
+    apply the AdamW update of the eager step with the same step number (the per-step seed term and the bias
+    corrections live in device memory that the graph advances), also when eager steps are interleaved."""
+    E = 128 if dtype == torch.bfloat16 else 64
+    ta, cfg, sd, x, y = _make(dtype, E=E, H=2, L=2, B=8, dropout_p=0.2, seed=3)
+    tb, *_ = _make(dtype, E=E, H=2, L=2, B=8, dropout_p=0.2, seed=3)
+    gen = torch.Generator().manual_seed(5)
+    xs = [torch.rand(x.shape, generator=gen).cuda() for _ in range(6)]
+    ys = [torch.randint(0, 3, y.shape, generator=gen).cuda() for _ in range(6)]
+    with pytest.raises(RuntimeError, match="at least one eager step"):
+        tb.capture_graph()
+    plan = ["eager", "graph", "graph", "eager", "graph", "graph"]
+    for i, how in enumerate(plan):
+        la = ta.step(xs[i], ys[i]).item()
+        lb = (tb.step(xs[i], ys[i]) if how == "eager" else tb.step_graph(xs[i], ys[i])).item()
+        # same masks, same update: only the fp32 summation order of the split-K dW atomics differs between two runs
+        assert abs(la - lb) <= 2e-4 * abs(la), (i, how, la, lb)
+    assert ta.step_no == tb.step_no == 6
+    a, b = ta.state_dict(), tb.state_dict()
+    mean_abs = sum(float((a[k] - b[k]).abs().sum()) for k in a) / sum(a[k].numel() for k in a)
+    assert mean_abs < 2e-6, mean_abs
+    # and a replay with the SAME inputs draws different masks each time (the seed really advances)
+    l1 = tb.step_graph(xs[0], ys[0]).item()
+    l2 = tb.step_graph(xs[0], ys[0]).item()
+    assert l1 != l2
+    oa, ob = ta.optimizer_state_dict(), tb.optimizer_state_dict()
+    assert float(ob["state"][0]["step"]) == 8.0 and float(oa["state"][0]["step"]) == 6.0
+
+
 def test_trainer_rejects_bad_labels_and_out_of_range_targets(lib):
     tr, cfg, sd, x, y = _make(torch.float32)
     with pytest.raises(RuntimeError, match="int64"):

@@ -56,7 +56,7 @@ class Dims(ctypes.Structure):
     _fields_ = [("B", c_int), ("T", c_int), ("E", c_int), ("H", c_int),
                 ("C", c_int), ("P", c_int), ("Hi", c_int), ("Wi", c_int),
                 ("classes", c_int), ("dtype", c_int), ("dropout_p", c_float), ("seed", c_uint64),
-                ("ln_eps", c_float)]
+                ("ln_eps", c_float), ("seed_dev", c_void_p)]
 
 
 class ProfEntry(ctypes.Structure):
@@ -137,6 +137,9 @@ def _declare(L):
         "vitb200_grad_pack": [c_void_p, c_void_p, c_int64, c_void_p],
         "vitb200_adamw_range": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, AdamWHyper,
                                 c_void_p],
+        "vitb200_adamw_range_dev": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                                    AdamWHyper, c_void_p, c_void_p],
+        "vitb200_step_state_advance": [c_void_p, c_float, c_float, c_uint64, c_void_p],
         "vitb200_adamw_multi": [c_void_p] * 8 + [c_int, AdamWHyper, c_void_p],
         "vitb200_embed_fwd": [P(Dims), P(EmbedParams), c_void_p, c_void_p, c_void_p, c_void_p],
         "vitb200_embed_fwd_u8": [P(Dims), P(EmbedParams), c_void_p, c_int, c_void_p, c_void_p, c_void_p],
@@ -173,7 +176,8 @@ EXPORTS = (
     "vitb200_prof_begin", "vitb200_prof_end", "vitb200_abi_sizeof", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
     "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_bwd_noalloc", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
     "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
-    "vitb200_resize_bilinear_u8", "vitb200_grad_pack", "vitb200_adamw_range", "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_fwd_u8", "vitb200_im2col_u8", "vitb200_embed_bwd",
+    "vitb200_resize_bilinear_u8", "vitb200_grad_pack", "vitb200_adamw_range", "vitb200_adamw_range_dev",
+    "vitb200_step_state_advance", "vitb200_adamw_multi", "vitb200_embed_act_bytes", "vitb200_embed_fwd", "vitb200_embed_fwd_u8", "vitb200_im2col_u8", "vitb200_embed_bwd",
     "vitb200_block_act_bytes", "vitb200_block_scratch_bytes", "vitb200_block_act_offset", "vitb200_block_fwd", "vitb200_block_bwd",
     "vitb200_head_act_bytes", "vitb200_head_fwd", "vitb200_head_bwd", "vitb200_block_fwd_row0",
     "vitb200_block_bwd_row0", "vitb200_head_fwd_row0", "vitb200_head_bwd_row0",
@@ -204,6 +208,7 @@ def check(rc):
 
 ACT_QKV, ACT_ATTN, ACT_LSE, ACT_XMID = 0, 1, 2, 3
 NOALLOC_MAX_DELTA = 1 << 20   # VITB200_NOALLOC_MAX_DELTA
+STEP_STATE_BYTES = 32         # VITB200_STEP_STATE_BYTES
 
 
 def stream_ptr(device=None):

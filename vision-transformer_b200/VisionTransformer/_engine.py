@@ -31,9 +31,10 @@ class Plan:
         self.block_scratch_bytes = L_.vitb200_block_scratch_bytes(ctypes.byref(d))
         self.head_act_bytes = L_.vitb200_head_act_bytes(ctypes.byref(d))
 
-    def dims(self, dropout_p, seed):
+    def dims(self, dropout_p, seed, seed_dev=None):
+        """seed_dev: optional device address of a uint64 added to `seed` on the device (captured steps)."""
         return _C.Dims(self.B, self.T, self.E, self.H, self.C, self.P, self.Hi, self.Wi, self.classes, self.code,
-                       float(dropout_p), int(seed) & 0xFFFFFFFFFFFFFFFF, 1e-5)
+                       float(dropout_p), int(seed) & 0xFFFFFFFFFFFFFFFF, 1e-5, seed_dev)
 
     # ---- raw stage calls (tensors in, nothing returned; all async on the current stream) -------------------
     @staticmethod

@@ -66,7 +66,12 @@ adamw_flat_kernel(float* __restrict__ p, const float* __restrict__ g, float* __r
 template <bool GB, bool ZERO>
 __global__ void __launch_bounds__(256)
 adamw_range_kernel(float* __restrict__ p, float* __restrict__ g, const bf16* __restrict__ gb, float* __restrict__ m,
-                   float* __restrict__ v, bf16* __restrict__ shadow, int64_t n, const AdamWHyper h) {
+                   float* __restrict__ v, bf16* __restrict__ shadow, int64_t n, const AdamWHyper h_in) {
+  AdamWHyper h = h_in;
+  if (h.corr_dev != nullptr) {          // captured CUDA graph: the step-dependent corrections come from device memory
+    h.bias_corr1 = __ldg(h.corr_dev);
+    h.inv_sqrt_bc2 = __ldg(h.corr_dev + 1);
+  }
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x * 4;
   const int64_t n4 = n & ~int64_t(3);
   for (int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4; i < n4; i += stride) {
@@ -105,6 +110,20 @@ adamw_range_kernel(float* __restrict__ p, float* __restrict__ g, const bf16* __r
     if (ZERO) g[i] = 0.f;
     if (shadow != nullptr) shadow[i] = __float2bfloat16_rn(pp);
   }
+}
+
+// Per-step scalars of a CAPTURED step (CUDA graph: kernel arguments are frozen at capture, so whatever changes from
+// step to step lives here).  Layout (32 bytes): uint64 seed_add | int32 step | float bias_corr1 | float inv_sqrt_bc2.
+// One thread: step += 1, seed_add = (step - 1) * seed_stride (the per-step term of DPTrainer's dropout seed), corrections
+// recomputed in double precision exactly as the host does (to_hyper in engine.cu).
+struct StepState { unsigned long long seed_add; int step; float bias_corr1; float inv_sqrt_bc2; int pad[3]; };
+__global__ void step_state_advance_kernel(StepState* st, float beta1, float beta2, unsigned long long seed_stride) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const int step = st->step + 1;
+  st->step = step;
+  st->seed_add = static_cast<unsigned long long>(step - 1) * seed_stride;   // the step being run, 0-based, as the host counts it
+  st->bias_corr1 = static_cast<float>(1.0 - pow(static_cast<double>(beta1), static_cast<double>(step)));
+  st->inv_sqrt_bc2 = static_cast<float>(1.0 / sqrt(1.0 - pow(static_cast<double>(beta2), static_cast<double>(step))));
 }
 
 // Multi-tensor form: block -> (tensor, chunk) through a device-resident table.
@@ -153,6 +172,15 @@ int adamw_range(float* p, float* g, const bf16* gb, float* m, float* v, bf16* sh
     if (zero_grad) adamw_range_kernel<false, true><<<grid, 256, 0, s>>>(p, g, gb, m, v, shadow, n, h);
     else adamw_range_kernel<false, false><<<grid, 256, 0, s>>>(p, g, gb, m, v, shadow, n, h);
   }
+  VB_CHECK_LAUNCH();
+  return kOk;
+}
+
+int step_state_advance(void* state, float beta1, float beta2, uint64_t seed_stride, cudaStream_t s) {
+  static_assert(sizeof(StepState) == 32, "step state layout is part of the C ABI (VITB200_STEP_STATE_BYTES)");
+  ProfScope prof(kProfAdamW, 0.0, 1, s);
+  step_state_advance_kernel<<<1, 32, 0, s>>>(static_cast<StepState*>(state), beta1, beta2,
+                                             static_cast<unsigned long long>(seed_stride));
   VB_CHECK_LAUNCH();
   return kOk;
 }

@@ -151,20 +151,27 @@ struct Dropout {
   uint32_t thresh;    // keep iff 16-bit lane < thresh
   uint64_t seed;
   uint64_t stream;    // distinguishes call sites (layer id * 2 + {proj, fc2})
+  const uint64_t* seed_dev;   // optional DEVICE word added to `seed` when the mask is drawn: lets a captured CUDA graph
+                              // draw fresh masks on every replay (the per-step part of the seed lives in device memory)
 };
-inline Dropout make_dropout(float p, uint64_t seed, uint64_t stream) {
+inline Dropout make_dropout(float p, uint64_t seed, uint64_t stream, const uint64_t* seed_dev = nullptr) {
   Dropout d;
   d.p = p;
   d.scale = p > 0.f ? 1.f / (1.f - p) : 1.f;
   d.thresh = keep_threshold(p);
   d.seed = seed;
   d.stream = stream;
+  d.seed_dev = seed_dev;
   return d;
 }
 // Element `lin` of a (seed, stream) mask lives in lane lin & 7 of Philox counter lin >> 3; lanes are the 16-bit halves
 // of the four output words in order (x.lo, x.hi, y.lo, y.hi, z.lo, z.hi, w.lo, w.hi).
 __host__ __device__ __forceinline__ uint32_t dropout_keep8(const Dropout& d, uint64_t idx8) {
-  const Philox4 r = philox4x32<7>(d.seed, d.stream, idx8);
+  uint64_t seed = d.seed;
+#ifdef __CUDA_ARCH__
+  if (d.seed_dev != nullptr) seed += __ldg(reinterpret_cast<const unsigned long long*>(d.seed_dev));
+#endif
+  const Philox4 r = philox4x32<7>(seed, d.stream, idx8);
   const uint32_t w[4] = {r.x, r.y, r.z, r.w};
   uint32_t bits = 0;
 #pragma unroll

@@ -331,7 +331,7 @@ static int head_backward(const vitb200_dims* d, int n_layers, const vitb200_head
     VB_PROPAGATE(gemm_f32(B, E, F, 0, 1, dn, F, p->w1, E, -1, e, s));  // few tiles, K = 4E: atomic split-K allowed
   }
   // scatter into the residual-stream gradient (token 0 only) + masked low-precision copy for the last fc2
-  const Dropout dr = make_dropout(d->dropout_p, d->seed, drop_stream(n_layers - 1, 1));
+  const Dropout dr = make_dropout(d->dropout_p, d->seed, drop_stream(n_layers - 1, 1), d->seed_dev);
   return head_scatter(dx0, g, dy_out, is_bf16(d), dr, B, Tx, E, s);
 }
 
@@ -410,7 +410,7 @@ static int block_forward(const vitb200_dims* d, int layer, const vitb200_block_p
   l = Lin();
   l.M = Mt; l.N = E; l.K = E; l.A = a.attn; l.lda = attn_ld; l.B = p->w_proj; l.ldb = E;
   l.ep = make_ep(a.x_mid, E); l.ep.bias = p->b_proj; l.ep.residual = res_in;
-  l.ep.drop = make_dropout(d->dropout_p, d->seed, drop_stream(layer, 0));
+  l.ep.drop = make_dropout(d->dropout_p, d->seed, drop_stream(layer, 0), d->seed_dev);
   l.out_f32 = true;
   VB_PROPAGATE(run_lin(bf, l, s));
 
@@ -424,7 +424,7 @@ static int block_forward(const vitb200_dims* d, int layer, const vitb200_block_p
   l = Lin();
   l.M = Mt; l.N = E; l.K = 4 * E; l.A = a.h; l.lda = 4 * E; l.B = p->w_fc2; l.ldb = 4 * E;
   l.ep = make_ep(x_out, E); l.ep.bias = p->b_fc2; l.ep.residual = a.x_mid;
-  l.ep.drop = make_dropout(d->dropout_p, d->seed, drop_stream(layer, 1));
+  l.ep.drop = make_dropout(d->dropout_p, d->seed, drop_stream(layer, 1), d->seed_dev);
   l.out_f32 = true;
   return run_lin(bf, l, s);
 }
@@ -481,7 +481,7 @@ static int block_backward(const vitb200_dims* d, int layer, const vitb200_block_
   VB_PROPAGATE(run_lin(bf, l, s));
   // LN2 backward: g += dx ; emits s3 = cast(g * proj-dropout mask)
   VB_PROPAGATE(ln_backward(sc.s2, bf, a.x_mid, a.mean2, a.rstd2, p->ln2_w, g, 1, gr->ln2_w, gr->ln2_b, sc.s3,
-                           gr->b_proj, make_dropout(d->dropout_p, d->seed, drop_stream(layer, 0)), M, E, s));
+                           gr->b_proj, make_dropout(d->dropout_p, d->seed, drop_stream(layer, 0), d->seed_dev), M, E, s));
 
   // ---- attention branch
   // dWproj[E,E] += s3^T attn  (dbproj += colsum(s3) came out of the LN2 backward above)
@@ -515,7 +515,7 @@ static int block_backward(const vitb200_dims* d, int layer, const vitb200_block_
   l.ep = make_ep(sc.s2, E); l.out_f32 = !bf;
   VB_PROPAGATE(run_lin(bf, l, s));
   // LN1 backward: g += dx ; emits dy_out = cast(g * fc2-dropout mask of layer-1) for the previous block
-  const Dropout prev = make_dropout(layer > 0 ? d->dropout_p : 0.f, d->seed, drop_stream(layer - 1, 1));
+  const Dropout prev = make_dropout(layer > 0 ? d->dropout_p : 0.f, d->seed, drop_stream(layer - 1, 1), d->seed_dev);
   return ln_backward(sc.s2, bf, x_in, a.mean1, a.rstd1, p->ln1_w, g, 1, gr->ln1_w, gr->ln1_b,
                      layer > 0 ? dy_out : nullptr, layer > 0 ? gr->b_fc2_prev : nullptr, prev, M, E, s);
 }
@@ -637,6 +637,7 @@ static AdamWHyper to_hyper(const vitb200_adamw_hyper& h) {
   k.bias_corr1 = static_cast<float>(1.0 - std::pow(static_cast<double>(h.beta1), h.step));
   k.inv_sqrt_bc2 = static_cast<float>(1.0 / std::sqrt(1.0 - std::pow(static_cast<double>(h.beta2), h.step)));
   k.grad_scale = h.grad_scale;
+  k.corr_dev = nullptr;
   return k;
 }
 int vitb200_adamw_flat(float* p, const float* g, float* m, float* v, void* shadow_bf16, int64_t n,
@@ -658,6 +659,18 @@ int vitb200_adamw_range(float* p, float* g, const void* g_bf16, float* m, float*
   VB_REQUIRE(h.step >= 1, "adamw: step must be >= 1");
   return adamw_range(p, g, static_cast<const bf16*>(g_bf16), m, v, static_cast<bf16*>(shadow_bf16), n, zero_grad != 0,
                      to_hyper(h), static_cast<cudaStream_t>(stream));
+}
+int vitb200_adamw_range_dev(float* p, float* g, const void* g_bf16, float* m, float* v, void* shadow_bf16, int64_t n,
+                            int zero_grad, vitb200_adamw_hyper h, const void* step_state, void* stream) {
+  VB_REQUIRE(step_state != nullptr, "adamw_range_dev: null step state");
+  AdamWHyper k = to_hyper(vitb200_adamw_hyper{h.lr, h.beta1, h.beta2, h.eps, h.weight_decay, 1, h.grad_scale});
+  k.corr_dev = reinterpret_cast<const float*>(static_cast<const uint8_t*>(step_state) + 12);   // {bias_corr1, inv_sqrt_bc2}
+  return adamw_range(p, g, static_cast<const bf16*>(g_bf16), m, v, static_cast<bf16*>(shadow_bf16), n, zero_grad != 0, k,
+                     static_cast<cudaStream_t>(stream));
+}
+int vitb200_step_state_advance(void* step_state, float beta1, float beta2, uint64_t seed_stride, void* stream) {
+  VB_REQUIRE(step_state != nullptr, "step_state_advance: null step state");
+  return step_state_advance(step_state, beta1, beta2, seed_stride, static_cast<cudaStream_t>(stream));
 }
 int vitb200_adamw_multi(const uint64_t* p_ptrs, const uint64_t* g_ptrs, const uint64_t* m_ptrs,
                         const uint64_t* v_ptrs, const uint64_t* shadow_ptrs, const int64_t* sizes,

@@ -10,6 +10,7 @@ struct AdamWHyper {
   float bias_corr1;      // 1 - beta1^step
   float inv_sqrt_bc2;    // 1 / sqrt(1 - beta2^step)
   float grad_scale;      // multiply gradients (1/world_size for the data-parallel mean)
+  const float* corr_dev; // optional DEVICE pair {bias_corr1, inv_sqrt_bc2} overriding the two fields above (CUDA graphs)
 };
 
 // contractions
@@ -89,6 +90,7 @@ int dropout_mask(uint8_t* keep, int64_t n, const Dropout& drop, cudaStream_t s);
 int adamw_flat(float* p, const float* g, float* m, float* v, bf16* shadow, int64_t n, const AdamWHyper& h,
                cudaStream_t s);
 int grad_pack(float* g, bf16* out, int64_t n, cudaStream_t s);
+int step_state_advance(void* state, float beta1, float beta2, uint64_t seed_stride, cudaStream_t s);
 int resize_bilinear_u8(const uint8_t* src, uint8_t* dst, int planes, int hin, int win, int hout, int wout,
                        const int32_t* xb, const int32_t* xk, int ksx, const int32_t* yb, const int32_t* yk, int ksy,
                        cudaStream_t s);

@@ -671,6 +671,62 @@ class DPTrainer:
         self._loss_ev[li].record(cur)
         return li
 
+    # ------------------------------------------------------------------------------------------ CUDA graph
+    _SEED_STRIDE = 0xD1B54A32D192ED03       # per-step term of the dropout seed (see _dims)
+
+    def capture_graph(self):
+        """Capture one whole training step (fwd + CE + bwd + AdamW with fused zero_grad) into a CUDA graph — SURVEY
+        8f-3 / reference train.py:92-96 as ONE graph launch.  Kernel arguments are frozen at capture, so everything
+        that changes from step to step lives in a 32-byte device "step state" that the graph itself advances with its
+        first node: the step counter, the per-step term of the dropout seed (kernels add it to their seed when they
+        draw a mask) and AdamW's bias corrections.  A replay draws exactly the masks, and applies exactly the update,
+        that the eager `step()` with the same step number would.  Single GPU only (the multi-GPU exchange lives on
+        side streams); call it after at least one eager step, so that no first-use set-up lands inside the capture."""
+        if self.world != 1:
+            raise RuntimeError("capture_graph: single-GPU only (the data-parallel exchange runs on side streams)")
+        if self.step_no < 1:
+            raise RuntimeError("capture_graph: run at least one eager step() first")
+        with torch.cuda.device(self.dev):
+            self._gstate = torch.zeros(_C.STEP_STATE_BYTES, dtype=torch.uint8, device=self.dev)
+            self._gx, self._gy = torch.empty_like(self._in[0][0]), torch.empty_like(self._in[0][1])   # static inputs
+            base_seed = (self.seed * 0x9E3779B97F4A7C15 + self.rank * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+            d = self.plan.dims(self.dropout_p, base_seed, seed_dev=self._gstate.data_ptr())
+            side = torch.cuda.Stream(device=self.dev)
+            side.wait_stream(torch.cuda.current_stream(self.dev))
+            graph = torch.cuda.CUDAGraph()
+            # "relaxed": the C ABI calls cudaFuncSetAttribute / cuTensorMapEncodeTiled (host-only, no stream work) while
+            # it enqueues; nothing in it allocates or synchronises
+            with torch.cuda.graph(graph, stream=side, capture_error_mode="relaxed"):
+                L = _C.lib()
+                _C.check(L.vitb200_step_state_advance(self._gstate.data_ptr(), self.betas[0], self.betas[1],
+                                                      self._SEED_STRIDE, _C.stream_ptr(self.dev)))
+                self.forward(self._gx, d)
+                self.backward(self._gy, d)
+                h = _C.AdamWHyper(self.lr, self.betas[0], self.betas[1], self.eps, self.wd, 1, 1.0)
+                _C.check(L.vitb200_adamw_range_dev(self.p.data_ptr(), self.g.data_ptr(), None, self.m.data_ptr(),
+                                                   self.v.data_ptr(),
+                                                   None if self.shadow is None else self.shadow.data_ptr(), self.total,
+                                                   1, h, self._gstate.data_ptr(), _C.stream_ptr(self.dev)))
+            torch.cuda.current_stream(self.dev).wait_stream(side)
+            self._graph, self._graph_step = graph, -1
+        return graph
+
+    @_on_device
+    def step_graph(self, images, labels):
+        """Replay the captured step on device-resident inputs (copied into the graph's static buffers).  Interleaves
+        freely with step(): the device step counter is re-synchronised whenever the host's moved in between."""
+        if getattr(self, "_graph", None) is None:
+            self.capture_graph()
+        self._check_labels(labels)
+        if self._graph_step != self.step_no:
+            self._gstate[8:12].view(torch.int32).fill_(self.step_no)
+        self._gx.copy_(images, non_blocking=True)
+        self._gy.copy_(labels, non_blocking=True)
+        self._graph.replay()
+        self.step_no += 1
+        self._graph_step = self.step_no
+        return self.loss
+
     def read_loss(self, li):
         self._loss_ev[li].synchronize()
         return float(self.loss_host[li])
