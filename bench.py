@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--no-row0", action="store_true", help="skip the last-block dead-row-elimination side number")
     ap.add_argument("--no-ref-eager", action="store_true", help="skip the reference-eager-on-this-GPU side number")
     ap.add_argument("--no-graph", action="store_true", help="skip the CUDA-graph replay side number")
+    ap.add_argument("--dropout", type=float, default=0.2,
+                    help="EXPERIMENTS ONLY: the reference hard-codes 0.2 (transformer.py:35,53); the line says so if changed")
     ap.add_argument("--bucket-mb", type=float, default=0,
                     help="gradient bucket size in MB of fp32 gradient; 0 = auto: ONE bucket (exchange after backward, nothing "
                          "co-runs with the persistent GEMMs) when the arena is <= 400 MB, else 48 MB buckets overlapped "
@@ -301,7 +303,7 @@ def run_b200(args):
     zero1 = None if args.zero1 == "auto" else args.zero1 == "1"
     grad_comm = None if args.grad_comm == "auto" else args.grad_comm
     tr = train_dp.DPTrainer(batch_size=args.batch, dtype=dtype, device=dev, process_group=pg, world_size=world,
-                            bucket_mb=args.bucket_mb, seed=0, zero1=zero1, grad_comm=grad_comm, **wl)
+                            bucket_mb=args.bucket_mb, seed=0, zero1=zero1, grad_comm=grad_comm, dropout_p=args.dropout, **wl)
     tr.init_parameters(seed=0)  # random-init weights of the architecture (no checkpoints offline)
     tr.broadcast_parameters()
 
@@ -497,7 +499,7 @@ def run_b200(args):
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": args.dtype, "data": "synthetic",
         "config": {"workload": f"{args.model} B={args.batch}/GPU train step (fwd+CE+bwd+allreduce+AdamW), {img}x{img}x3, "
-                               f"{args.classes} cls, dropout on",
+                               f"{args.classes} cls, dropout " + ("on" if args.dropout == 0.2 else f"p={args.dropout} (EXPERIMENT, not the reference's 0.2)"),
                    "global_batch": gb, "tokens_per_image": tr.T, "parallelism": f"dp{world}",
                    "exchange": ("none (1 GPU)" if world == 1 else
                                 (f"ZeRO-1: reduce-scatter {str(tr.comm_dtype).split('.')[-1]} gradients, sharded AdamW, "

@@ -1,7 +1,10 @@
 """GPU: BASELINE.json's full bench configuration (ViT-B/16, 12 blocks, 256 images of 224x224x3 per GPU, bf16) through
-size-independent properties — the oracle cannot run this size in seconds, so parity at full size is pinned by
-invariants the reference's arithmetic has: images are independent (permutation equivariance of logits), the loss is a
-batch mean (gradients of the full batch = mean of the half-batch gradients), and the forward is deterministic."""
+size-independent properties of the reference's arithmetic: images are independent (permutation equivariance of logits),
+the loss is a batch mean (gradients of the full batch = mean of the half-batch gradients), and the forward is
+deterministic.  These complement — they do not replace — the direct comparison with the real reference modules on the
+same B200 at full depth (12 / 24 / 32 blocks, batch 16-32), which lives in tests/test_reference_gpu.py; here the point
+is the full BATCH of the bench line (M = 50 432 rows: every tile of every persistent kernel, the arenas, the 2-tile
+attention items of all 3 072 (image, head) pairs)."""
 import pytest
 import torch
 
