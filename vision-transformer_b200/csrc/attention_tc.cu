@@ -32,17 +32,30 @@ constexpr int STAGE_BYTES = 3 * TILE_BYTES;         // Q | K | V
 constexpr int kStages = 2;
 constexpr int kThreads = 64 + 8 * 32;
 constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 256 + 1024;
+// EWG = 2 (round 2, T in 193..256): TWO softmax groups per query tile, each owning half of the key columns of every row
+// (chunks 0-3 | 4-7) — the per-row chain of tcgen05.ld -> ex2 -> tcgen05.st, which bounds the kernel, is half as long.
+// The groups exchange their partial row maxima / sums through 4 KB of shared memory and a 256-thread named barrier.
+constexpr int kThreads2 = 64 + 16 * 32;
+constexpr int XCH_BYTES = 2 * 2 * 2 * 128 * 4;      // [max | sum][tile][group][row]
+constexpr int SMEM_BYTES2 = SMEM_BYTES + XCH_BYTES;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
+
+#define VB_TR(tag)                                                                      \
+  do {                                                                                  \
+    if (trbuf != nullptr && trn < 512) trbuf[trn++] = (clock64() << 8) | (tag);         \
+  } while (0)
 
 struct FwdParams {
   int T, TP, H, items;   // TP = T rounded up to a multiple of 16 (UMMA N and PV K extent)
   float scale_log2;      // scale * log2(e)
   int st256;             // output rows are 32-byte aligned: store whole sectors per thread
   int order;             // MMA issue order: 1 skewed (default), 0 lock-step (VITB200_ATTN_FWD_ORDER=0, A/B timing)
+  long long* trace;      // optional event trace of CTA 0 (tools/attn_trace.py fwd), else nullptr
 };
 
-__global__ void __launch_bounds__(kThreads, 1)
+template <int EWG>
+__global__ void __launch_bounds__(EWG == 2 ? kThreads2 : kThreads, 1)
 attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict__ out, float* __restrict__ lse,
                    const FwdParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -65,9 +78,9 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
       ptx::mbar_init(&kv_full[s], 1);
       ptx::mbar_init(&kv_empty[s], 1);
       ptx::mbar_init(&s_full[s], 1);
-      ptx::mbar_init(&p_ready[s], 4);
+      ptx::mbar_init(&p_ready[s], 4 * EWG);
       ptx::mbar_init(&o_full[s], 1);
-      ptx::mbar_init(&t_free[s], 4);
+      ptx::mbar_init(&t_free[s], 4 * EWG);
     }
     ptx::fence_barrier_init();
   }
@@ -81,6 +94,12 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
   const uint32_t tmem_base = *tmem_ptr;
   pdl_wait();
   pdl_trigger();
+  // EWG = 2: group 0 packs its P (keys 0..127) at columns [0,64), group 1 (keys 128..) at [128, ...): each group only
+  // overwrites columns it has already read.  The O accumulators sit in columns that are dead once P is complete:
+  // [64,128) and the 64 columns behind group 1's P.
+  const int nchunk_all = (p.TP + 31) / 32;
+  const uint32_t kO0 = EWG == 2 ? 64u : 128u;
+  const uint32_t kO1 = EWG == 2 ? static_cast<uint32_t>(128 + 16 * (nchunk_all - 4)) : 192u;
   // tensor-memory map per query tile t: [t*256, t*256+TP) S (fp32) -> [t*256, +TP/2) P (bf16 pairs), O at t*256+128
   // (TP <= 256: P needs <= 128 columns, O 64 columns; S is dead once P is written)
 
@@ -113,10 +132,14 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
       const int nks = p.TP / 16;
       const bool dual = nks >= 2;              // both O accumulators get initialised by the first two k-steps
       // S = Q_t K^T of one (item, tile) unit into the tile's tensor-memory slot
+      long long* trbuf = (p.trace != nullptr && blockIdx.x == 0) ? p.trace : nullptr;
+      int trn = 0;
       auto issue_s = [&](int it2, int t) {
         const uint32_t sq = ptx::smem_u32(smem + (it2 & 1) * STAGE_BYTES), sk = sq + TILE_BYTES;
+        VB_TR(1);
         ptx::mbar_wait(&t_free[t], (static_cast<uint32_t>(it2) & 1u) ^ 1u);
         ptx::tc_fence_after();
+        VB_TR(2);
         const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
 #pragma unroll
         for (int k = 0; k < HS / 16; ++k) {
@@ -125,22 +148,28 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
           ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
         }
         ptx::umma_commit(&s_full[t]);
+        VB_TR(3);
       };
       // O = P V of one unit.  Back-to-back MMAs into ONE accumulator serialise on its latency (~114 clk each against
       // ~55 clk for independent ones, tools/probe): the k-steps alternate between two accumulators (columns 128..191
       // and 192..255 of the slot; S is dead by then) which the epilogue adds.
       auto issue_pv = [&](int it2, int t) {
         const uint32_t sv = ptx::smem_u32(smem + (it2 & 1) * STAGE_BYTES) + 2 * TILE_BYTES;
+        VB_TR(4);
         ptx::mbar_wait(&p_ready[t], static_cast<uint32_t>(it2) & 1u);
         ptx::tc_fence_after();
+        VB_TR(5);
         const uint32_t a_p = tmem_base + static_cast<uint32_t>(t * 256);
         for (int k = 0; k < nks; ++k) {
           // V as MN-major B: 16 key rows per k-step = 16 * 128 B; 8-row groups 1024 B apart
           const uint64_t db = ptx::make_smem_desc_sw128(sv + k * 2048, 64 * 128, 1024);
-          const uint32_t d_o = a_p + 128u + ((dual && (k & 1)) ? 64u : 0u);
-          ptx::umma_f16_ts(d_o, a_p + static_cast<uint32_t>(k * 8), db, idesc_o, k > (dual ? 1 : 0) ? 1u : 0u);
+          const uint32_t d_o = a_p + ((dual && (k & 1)) ? kO1 : kO0);
+          const uint32_t a_k = (EWG == 2 && k >= 8) ? a_p + 128u + static_cast<uint32_t>((k - 8) * 8)
+                                                    : a_p + static_cast<uint32_t>(k * 8);
+          ptx::umma_f16_ts(d_o, a_k, db, idesc_o, k > (dual ? 1 : 0) ? 1u : 0u);
         }
         ptx::umma_commit(&o_full[t]);
+        VB_TR(6);
       };
       const int my_items = blockIdx.x < p.items ? (p.items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) /
                                                     static_cast<int>(gridDim.x) : 0;
@@ -167,8 +196,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
             if (t == ntile - 1) ptx::umma_commit(&kv_empty[it & 1]);
             if (more) {
               if (t == 0) {
+                VB_TR(7);
                 ptx::mbar_wait(&kv_full[(it + 1) & 1], ((it + 1) >> 1) & 1);
                 ptx::tc_fence_after();
+                VB_TR(8);
               }
               issue_s(it + 1, t);
             }
@@ -178,97 +209,116 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
     }
   } else {
     // ------------------------------------------------------------------ softmax + epilogue: one thread per query row
-    const int t = (warp - 2) >> 2;               // query tile of this warp
+    // (EWG = 2: per row TWO threads in two warps of the same lane quarter, each owning half of the key columns)
+    const int grp4 = (warp - 2) >> 2;            // group of four warps covering the four tensor-memory lane quarters
+    const int t = EWG == 2 ? grp4 >> 1 : grp4;   // query tile of this warp
+    const int hg = EWG == 2 ? grp4 & 1 : 0;      // column half owned by this warp
     const int q = warp & 3;                      // tensor-memory lane quarter
     const int row = t * QT + q * 32 + lane;      // query index inside the item
     const bool tile_live = t * QT < p.T;
     const uint32_t t_row = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(t * 256);
-    const int nchunk = (p.TP + 31) / 32;
+    const int nchunk = nchunk_all;
+    const int cb = EWG == 2 ? (hg == 0 ? 0 : 4) : 0;                    // my chunks of 32 key columns: [cb, ce)
+    const int ce = EWG == 2 ? (hg == 0 ? 4 : nchunk) : nchunk;
+    // packed bf16 P of chunk c lands at column pdst(c): always at or below the chunk's own first column
+    auto pdst = [&](int c) { return EWG == 2 && hg == 1 ? 128 + 16 * (c - 4) : 16 * c; };
+    float* xch = reinterpret_cast<float*>(smem + kStages * STAGE_BYTES + 256);   // EWG = 2 only (SMEM_BYTES2)
+    const int xi = (t * 2 + hg) * 128 + q * 32 + lane, xo = (t * 2 + (hg ^ 1)) * 128 + q * 32 + lane;
+    long long* trbuf = (p.trace != nullptr && blockIdx.x == 0 && q == 0 && lane == 0) ? p.trace + 512 * (1 + t * 2 + hg) : nullptr;
+    int trn = 0;
     int it = 0;
     for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++it) {
       if (!tile_live) continue;
       const uint32_t tp = it & 1;
       const int b = item / p.H, h = item - b * p.H;
+      VB_TR(10);
       ptx::mbar_wait(&s_full[t], tp);
       ptx::tc_fence_after();
-      // pass 1: row maximum of the raw logits over the T valid keys (full chunks unmasked, tail chunk masked)
-      const int nfull = p.T / 32;                // chunks whose 32 keys are all valid
+      VB_TR(11);
+      // pass 1: row maximum of the raw logits over my share of the T valid keys (tail chunk masked)
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
-      for (int c = 0; c < nfull; ++c) {
+      for (int c = cb; c < ce; ++c) {
         uint32_t r[32];
         ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(c * 32), r);
         ptx::tmem_ld_wait();
+        if (c * 32 + 32 <= p.T) {
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          mx0 = fmaxf(mx0, __uint_as_float(r[j]));
-          mx1 = fmaxf(mx1, __uint_as_float(r[j + 1]));
-          mx2 = fmaxf(mx2, __uint_as_float(r[j + 2]));
-          mx3 = fmaxf(mx3, __uint_as_float(r[j + 3]));
+          for (int j = 0; j < 32; j += 4) {
+            mx0 = fmaxf(mx0, __uint_as_float(r[j]));
+            mx1 = fmaxf(mx1, __uint_as_float(r[j + 1]));
+            mx2 = fmaxf(mx2, __uint_as_float(r[j + 2]));
+            mx3 = fmaxf(mx3, __uint_as_float(r[j + 3]));
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c * 32 + j < p.T) mx0 = fmaxf(mx0, __uint_as_float(r[j]));
         }
       }
-      if (nfull < nchunk) {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(nfull * 32), r);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (nfull * 32 + j < p.T) mx0 = fmaxf(mx0, __uint_as_float(r[j]));
+      float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      if (EWG == 2) {                            // the row maximum is over BOTH halves
+        xch[xi] = mx;
+        asm volatile("bar.sync %0, 256;" ::"r"(1 + t) : "memory");
+        mx = fmaxf(mx, xch[xo]);
       }
-      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
       const float sl2 = p.scale_log2;
       const float mneg = -mx * sl2;              // scale > 0: max commutes with the scaling
+      VB_TR(12);
       // pass 2: p = exp2(s*c - m), row sum in fp32, P written over S as packed bf16
       float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
-      for (int c = 0; c < nfull; ++c) {
+      for (int c = cb; c < ce; ++c) {
         uint32_t r[32];
         ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(c * 32), r);
         ptx::tmem_ld_wait();
         uint32_t pk[16];
+        if (c * 32 + 32 <= p.T) {
 #pragma unroll
-        for (int j = 0; j < 16; j += 2) {
-          const float p0 = ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg));
-          const float p1 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg));
-          const float p2 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 2]), sl2, mneg));
-          const float p3 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 3]), sl2, mneg));
-          l0 += p0; l1 += p1; l2 += p2; l3 += p3;
-          pk[j] = pack_bf16x2(p0, p1);
-          pk[j + 1] = pack_bf16x2(p2, p3);
-        }
-        ptx::tmem_st_32x16(t_row + static_cast<uint32_t>(c * 16), pk);
-      }
-      if (nfull < nchunk) {
-        uint32_t r[32];
-        ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(nfull * 32), r);
-        ptx::tmem_ld_wait();
-        uint32_t pk[16];
+          for (int j = 0; j < 16; j += 2) {
+            const float p0 = ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg));
+            const float p1 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg));
+            const float p2 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 2]), sl2, mneg));
+            const float p3 = ptx::ex2(fmaf(__uint_as_float(r[2 * j + 3]), sl2, mneg));
+            l0 += p0; l1 += p1; l2 += p2; l3 += p3;
+            pk[j] = pack_bf16x2(p0, p1);
+            pk[j + 1] = pack_bf16x2(p2, p3);
+          }
+        } else {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int k0 = nfull * 32 + 2 * j;
-          const float p0 = k0 < p.T ? ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg)) : 0.f;
-          const float p1 = k0 + 1 < p.T ? ptx::ex2(fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg)) : 0.f;
-          l0 += p0; l1 += p1;
-          pk[j] = pack_bf16x2(p0, p1);
+          for (int j = 0; j < 16; ++j) {
+            const int k0 = c * 32 + 2 * j;
+            const float p0 = k0 < p.T ? ptx::ex2(fmaf(__uint_as_float(r[2 * j]), sl2, mneg)) : 0.f;
+            const float p1 = k0 + 1 < p.T ? ptx::ex2(fmaf(__uint_as_float(r[2 * j + 1]), sl2, mneg)) : 0.f;
+            l0 += p0; l1 += p1;
+            pk[j] = pack_bf16x2(p0, p1);
+          }
         }
-        ptx::tmem_st_32x16(t_row + static_cast<uint32_t>(nfull * 16), pk);
+        ptx::tmem_st_32x16(t_row + static_cast<uint32_t>(pdst(c)), pk);
       }
-      const float l = (l0 + l1) + (l2 + l3);
+      float l = (l0 + l1) + (l2 + l3);
       ptx::tmem_st_wait();
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&p_ready[t]);
-      // epilogue: O / l -> bf16 row, log-sum-exp
+      VB_TR(13);
+      if (EWG == 2) {                            // the row sum is over BOTH halves
+        xch[512 + xi] = l;
+        asm volatile("bar.sync %0, 256;" ::"r"(1 + t) : "memory");
+        l += xch[512 + xo];
+      }
+      // epilogue: O / l -> bf16 row, log-sum-exp.  EWG = 1: all 64 columns; EWG = 2: my 32 of them.
       ptx::mbar_wait(&o_full[t], tp);
       ptx::tc_fence_after();
+      VB_TR(14);
       const float inv = 1.f / l;
       const bool live = row < p.T;
       bf16* orow = out + (static_cast<int64_t>(b) * p.T + row) * E + h * HS;
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      for (int c = (EWG == 2 ? hg : 0); c < (EWG == 2 ? hg + 1 : 2); ++c) {
         uint32_t r[32];
-        ptx::tmem_ld_32x32(t_row + 128u + static_cast<uint32_t>(c * 32), r);
+        ptx::tmem_ld_32x32(t_row + kO0 + static_cast<uint32_t>(c * 32), r);
         if (p.TP >= 32) {                       // second accumulator (odd k-steps of P.V), see the MMA issuer
           uint32_t r2[32];
-          ptx::tmem_ld_32x32(t_row + 192u + static_cast<uint32_t>(c * 32), r2);
+          ptx::tmem_ld_32x32(t_row + kO1 + static_cast<uint32_t>(c * 32), r2);
           ptx::tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
@@ -291,11 +341,12 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
           }
         }
       }
-      if (live && lse != nullptr)
+      if (live && hg == 0 && lse != nullptr)
         lse[(static_cast<int64_t>(b) * p.H + h) * p.T + row] = (mx * sl2) * kLn2 + logf(l);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&t_free[t]);
+      VB_TR(15);
     }
   }
 
@@ -340,10 +391,6 @@ struct BwdParams {
   long long* trace;                         // optional event trace of CTA 0 (tools/attn_trace.py), else nullptr
 };
 
-#define VB_TR(tag)                                                                      \
-  do {                                                                                  \
-    if (trbuf != nullptr && trn < 512) trbuf[trn++] = (clock64() << 8) | (tag);         \
-  } while (0)
 
 template <int N>
 __device__ __forceinline__ void tmem_ld_n(uint32_t taddr, uint32_t (&r)[N]) {
@@ -737,7 +784,8 @@ int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H,
   VB_PROPAGATE(make_tmap_bf16(&tm, qkv, M, 3 * static_cast<int64_t>(E), 3 * static_cast<int64_t>(E), HS, QT));
   static bool attr_done = false;
   if (!attr_done) {
-    VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_fwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_fwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES2));
     attr_done = true;
   }
   FwdParams p;
@@ -746,9 +794,15 @@ int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H,
   p.st256 = (reinterpret_cast<uintptr_t>(out) & 31u) == 0 && (E * 2) % 32 == 0;
   static const int order = getenv("VITB200_ATTN_FWD_ORDER") ? atoi(getenv("VITB200_ATTN_FWD_ORDER")) : 1;
   p.order = order;
+  p.trace = getenv("VITB200_ATTN_TRACE") ? reinterpret_cast<long long*>(strtoull(getenv("VITB200_ATTN_TRACE"), nullptr, 0)) : nullptr;
   ProfScope prof(kProfAttnFwd, 4.0 * B * H * T * static_cast<double>(T) * hs, 1, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
-  VB_CHECK_CUDA(launch_pdl(attn_tc_fwd_kernel, dim3(grid), dim3(kThreads), SMEM_BYTES, stream, 1, tm, out, lse, p));
+  // two softmax groups per tile when there are 7 or 8 chunks of 32 key columns (T in 193..256); VITB200_ATTN_FWD_SPLIT=0/1
+  static const int split_env = getenv("VITB200_ATTN_FWD_SPLIT") ? atoi(getenv("VITB200_ATTN_FWD_SPLIT")) : 1;
+  if (split_env && p.TP > 192)
+    VB_CHECK_CUDA(launch_pdl(attn_tc_fwd_kernel<2>, dim3(grid), dim3(kThreads2), SMEM_BYTES2, stream, 1, tm, out, lse, p));
+  else
+    VB_CHECK_CUDA(launch_pdl(attn_tc_fwd_kernel<1>, dim3(grid), dim3(kThreads), SMEM_BYTES, stream, 1, tm, out, lse, p));
   VB_CHECK_LAUNCH();
   return kOk;
 }
