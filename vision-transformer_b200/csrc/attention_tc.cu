@@ -130,6 +130,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
       const uint32_t idesc_o = ptx::make_idesc_bf16_f32(QT, HS, 0, 1);     // O: M=128, N=64, B (=V) MN-major
       const int ntile = p.T > QT ? 2 : 1;
       const int nks = p.TP / 16;
+      constexpr uint32_t kHiSw = ptx::smem_desc_hi_sw128(1024);
       const bool dual = nks >= 2;              // both O accumulators get initialised by the first two k-steps
       // S = Q_t K^T of one (item, tile) unit into the tile's tensor-memory slot
       long long* trbuf = (p.trace != nullptr && blockIdx.x == 0) ? p.trace : nullptr;
@@ -141,12 +142,11 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
         ptx::tc_fence_after();
         VB_TR(2);
         const uint32_t d_s = tmem_base + static_cast<uint32_t>(t * 256);
+        // lean issue (ptx.cuh): descriptor low words advance by plain adds, the high word is a constant
+        const uint32_t a_lo = ptx::smem_desc_lo(sq + t * (QT * HS * 2), 16), b_lo = ptx::smem_desc_lo(sk, 16);
 #pragma unroll
-        for (int k = 0; k < HS / 16; ++k) {
-          const uint64_t da = ptx::make_smem_desc_sw128(sq + t * (QT * HS * 2) + k * 32, 16, 1024);
-          const uint64_t db = ptx::make_smem_desc_sw128(sk + k * 32, 16, 1024);
-          ptx::umma_f16(d_s, da, db, idesc_s, k > 0 ? 1u : 0u);
-        }
+        for (int k = 0; k < HS / 16; ++k)
+          ptx::umma_f16_lh(d_s, a_lo + 2u * k, b_lo + 2u * k, kHiSw, idesc_s, k > 0 ? 1u : 0u);
         ptx::umma_commit(&s_full[t]);
         VB_TR(3);
       };
@@ -160,13 +160,17 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
         ptx::tc_fence_after();
         VB_TR(5);
         const uint32_t a_p = tmem_base + static_cast<uint32_t>(t * 256);
-        for (int k = 0; k < nks; ++k) {
-          // V as MN-major B: 16 key rows per k-step = 16 * 128 B; 8-row groups 1024 B apart
-          const uint64_t db = ptx::make_smem_desc_sw128(sv + k * 2048, 64 * 128, 1024);
-          const uint32_t d_o = a_p + ((dual && (k & 1)) ? kO1 : kO0);
-          const uint32_t a_k = (EWG == 2 && k >= 8) ? a_p + 128u + static_cast<uint32_t>((k - 8) * 8)
-                                                    : a_p + static_cast<uint32_t>(k * 8);
-          ptx::umma_f16_ts(d_o, a_k, db, idesc_o, k > (dual ? 1 : 0) ? 1u : 0u);
+        // V as MN-major B: 16 key rows per k-step = 16 * 128 B (low word + 128); 8-row groups 1024 B apart
+        const uint32_t b_lo = ptx::smem_desc_lo(sv, 64 * 128);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          if (k < nks) {
+            const uint32_t d_o = a_p + ((dual && (k & 1)) ? kO1 : kO0);
+            const uint32_t a_k = (EWG == 2 && k >= 8) ? a_p + 128u + static_cast<uint32_t>((k - 8) * 8)
+                                                      : a_p + static_cast<uint32_t>(k * 8);
+            ptx::umma_f16_ts_lh(d_o, a_k, b_lo + static_cast<uint32_t>(k * 128), kHiSw, idesc_o,
+                                k > (dual ? 1 : 0) ? 1u : 0u);
+          }
         }
         ptx::umma_commit(&o_full[t]);
         VB_TR(6);
