@@ -305,3 +305,58 @@ def test_train_py_bf16_precision_field(lib):
         assert ck is not None and np.isfinite(ck["loss"])
     finally:
         shutil.rmtree(d, ignore_errors=True)
+
+
+# ------------------------------------------------------------------------------------------- training trajectories
+def test_training_trajectory_matches_reference(lib):
+    """30 optimisation steps with the reference's own recipe (train.py:66,81,92-96: AdamW(lr, weight_decay=1e-4),
+    CrossEntropyLoss, zero_grad / backward / step) on the same synthetic batches and initial weights, dropout off:
+    (a) the REAL reference modules + torch.optim.AdamW, (b) the drop-in modules + torch.optim.AdamW, (c) DPTrainer
+    (fused CE + one-launch AdamW).  fp32: the loss curves coincide (rel 2e-3 at every step: the only differences are
+    fp32 summation orders, which Adam's sign-like first steps amplify on near-zero gradient entries)."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    import train_dp
+    from test_model_gpu import _build
+    E, H, L, B, P, img, classes, steps, lr = 64, 4, 2, 16, 8, 32, 4, 30, 1e-3
+    kw = _cfg_kwargs(E, H, L, B, P, img, classes=classes)
+    ref = _reference(kw, 11, 0.25).eval()                       # eval(): the hard-coded dropout off, grads still flow
+    sd = {k: v.detach().clone() for k, v in ref.state_dict().items()}
+    ours = _build(kw, precision=torch.float32).eval()
+    ours.load_state_dict(sd)
+    tr = train_dp.DPTrainer(input_channels=3, num_classes=classes, image_size=img, patch_size=P, embedding_size=E,
+                            num_heads=H, num_blocks=L, batch_size=B, dtype=torch.float32, dropout_p=0.0, lr=lr)
+    tr.load_state_dict(sd)
+    opt_r = torch.optim.AdamW(ref.parameters(), lr=lr, weight_decay=1e-4)
+    opt_o = torch.optim.AdamW(ours.parameters(), lr=lr, weight_decay=1e-4)
+    crit = torch.nn.CrossEntropyLoss()
+    gen = torch.Generator().manual_seed(12)
+    curves = {"ref": [], "dropin": [], "trainer": []}
+    for s in range(steps):
+        # a learnable synthetic task: the class is the brightest quadrant of the image
+        x = torch.rand(B, 3, img, img, generator=gen)
+        y = torch.randint(0, classes, (B,), generator=gen)
+        for b in range(B):
+            qy, qx = divmod(int(y[b]), 2)
+            x[b, :, qy * 16:(qy + 1) * 16, qx * 16:(qx + 1) * 16] += 0.5
+        x, y = x.to(DEV), y.to(DEV)
+        for name, model, opt in (("ref", ref, opt_r), ("dropin", ours, opt_o)):
+            loss = crit(model(x), y)
+            opt.zero_grad(set_to_none=True)
+            loss.backward()
+            opt.step()
+            curves[name].append(loss.item())
+        curves["trainer"].append(tr.step(x, y, train=False).item())
+    r = torch.tensor(curves["ref"])
+    for name in ("dropin", "trainer"):
+        c = torch.tensor(curves[name])
+        worst = float(((c - r).abs() / r.abs()).max())
+        _record({"config": f"training trajectory, {steps} AdamW steps, fp32, E={E} L={L} B={B}: {name} vs the reference",
+                 "worst_rel_loss_diff": worst, "first_loss_ref": float(r[0]), "last_loss_ref": float(r[-1]),
+                 "last_loss": float(c[-1])})
+        assert worst < 2e-3, (name, worst, curves[name][-3:], curves["ref"][-3:])
+    assert r[-5:].mean() < 0.8 * r[:5].mean()                   # and the task is actually being learnt
+    # the trained weights agree too (mean absolute difference; a handful of weights may sit 2 lr apart per step)
+    a, b = tr.state_dict(), ref.state_dict()
+    mean_abs = sum(float((a[k] - b[k]).abs().sum()) for k in b) / sum(b[k].numel() for k in b)
+    assert mean_abs < 5e-5, mean_abs
