@@ -20,7 +20,8 @@ def _C():
 # ------------------------------------------------------------------------------------------------ contractions
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("variant,M,N,K", [("nt", 300, 200, 104), ("nt", 1000, 768, 768), ("nn", 257, 264, 512),
-                                           ("tn", 264, 136, 1000), ("nt", 128, 256, 64), ("nt", 1, 8, 8)])
+                                           ("tn", 264, 136, 1000), ("nt", 128, 256, 64), ("nt", 1, 8, 8),
+                                           ("tn", 520, 264, 6400)])      # deep K: several atomic splits per tile
 def test_gemm_layouts(lib, dt, variant, M, N, K):
     C = _C()
     torch.manual_seed(1)

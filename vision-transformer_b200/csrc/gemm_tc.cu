@@ -533,12 +533,31 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   p.kb_total = ceil_div(K, BK);
   int s = splits;
   if (!ep.accumulate) s = 1;
-  if (s <= 0) {  // auto: aim for ~2 waves of work units, at least 4 k-blocks per split
+  if (s <= 0) {
+    // auto.  The persistent walk is static: walker i takes units i, i + W, ... (W = CTAs or CTA pairs), all units the
+    // same length, so the launch lasts rounds * (k-blocks per split + hand-over).  Round 1 aimed at "about two waves"
+    // (s = ceil(2W / tiles)), which left the weight-gradient sites of ViT-B/16 at 180 / 162 / 153 units on 74 pairs =
+    // THREE rounds at 81 / 73 / 69 % occupancy — exactly their measured deficit against cuBLAS.  Now: the split count
+    // with the lowest modelled duration, fewest splits on ties (less atomic traffic into the fp32 gradient arena).
+    static const bool old_rule = getenv("VITB200_GEMM_SPLITS_OLD") && atoi(getenv("VITB200_GEMM_SPLITS_OLD")) != 0;
     const int tiles = p.m_tiles * p.n_tiles;
-    s = ceil_div(2 * (num_sms() / cg), tiles);
+    const int walkers = num_sms() / cg;
     const int max_s = p.kb_total / 4 > 0 ? p.kb_total / 4 : 1;
-    if (s > max_s) s = max_s;
-    if (s < 1) s = 1;
+    if (old_rule) {
+      s = ceil_div(2 * walkers, tiles);
+      if (s > max_s) s = max_s;
+      if (s < 1) s = 1;
+    } else {
+      constexpr int kHandOver = 6;   // k-block equivalents per unit: accumulator hand-over + its share of the atomics
+      long best = -1;
+      s = 1;
+      for (int c = 1; c <= max_s && c <= 64; ++c) {
+        const int per = ceil_div(p.kb_total, c);
+        const int units = tiles * ceil_div(p.kb_total, per);
+        const long cost = static_cast<long>(ceil_div(units, walkers)) * (per + kHandOver);
+        if (best < 0 || cost * 100 < best * 99) { best = cost; s = c; }   // a later candidate must win by > 1 %
+      }
+    }
   }
   p.kb_per_split = ceil_div(p.kb_total, s);
   p.splits = ceil_div(p.kb_total, p.kb_per_split);
