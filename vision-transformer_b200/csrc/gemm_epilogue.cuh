@@ -56,13 +56,37 @@ struct EpiPre {
   uint4 a0, a1;    // mask_aux: 8 x bf16 in a0, or 8 x fp32 in a0|a1
   uint32_t bits;   // mask_bits word of this row / 32-column group
 };
+__device__ __forceinline__ float4 ldg_f4_no_l1(const float* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+// 256-bit global accesses (sm_100: LDG/STG.E.256): the 8 consecutive fp32 columns of a lane in ONE request instead of two
+// half-sector 16-byte ones.  The address must be 32-byte aligned.
+__device__ __forceinline__ void ldg_f8(const float* p, float4& a, float4& b) {
+  asm volatile("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
+__device__ __forceinline__ void stg_f8(float* p, const float (&v)[8]) {
+  asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]),
+               "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+}
 template <typename OutT, uint32_t EPI>
-__device__ __forceinline__ void epilogue_fetch8(const GemmEpilogue& ep, int64_t off, int m, int n, EpiPre& pre) {
+__device__ __forceinline__ void epilogue_fetch8(const GemmEpilogue& ep, int64_t off, int m, int n, EpiPre& pre,
+                                                int hints = 0) {
   if (VB_EPI(kEpiBitMask, ep.mask_bits != nullptr))
     pre.bits = __ldg(ep.mask_bits + static_cast<int64_t>(n >> 5) * ep.bits_rows + m);
   if (VB_EPI(kEpiResidual, ep.residual != nullptr)) {
-    pre.r0 = __ldg(reinterpret_cast<const float4*>(ep.residual + off));
-    pre.r1 = __ldg(reinterpret_cast<const float4*>(ep.residual + off + 4));
+    if (hints & 8) {
+      ldg_f8(ep.residual + off, pre.r0, pre.r1);
+    } else if (hints & 4) {   // read once, overwritten in place by this very thread: keep it out of L1
+      pre.r0 = ldg_f4_no_l1(ep.residual + off);
+      pre.r1 = ldg_f4_no_l1(ep.residual + off + 4);
+    } else {
+      pre.r0 = __ldg(reinterpret_cast<const float4*>(ep.residual + off));
+      pre.r1 = __ldg(reinterpret_cast<const float4*>(ep.residual + off + 4));
+    }
   }
   if (VB_EPI(kEpiMask, ep.mask_aux != nullptr)) {
     const OutT* aux = reinterpret_cast<const OutT*>(ep.mask_aux) + off;
@@ -76,7 +100,8 @@ __device__ __forceinline__ void epilogue_fetch8(const GemmEpilogue& ep, int64_t 
 // Requirements: n % 8 == 0, N % 8 == 0, ldc % 8 == 0, all base pointers 16-byte aligned.
 template <typename OutT, uint32_t EPI>
 __device__ __forceinline__ void epilogue_finish8(const GemmEpilogue& ep, int m, int n, int N, int64_t off,
-                                                 float (&v)[8], const EpiPre& pre, const float (&bias8)[8]) {
+                                                 float (&v)[8], const EpiPre& pre, const float (&bias8)[8],
+                                                 int hints = 0) {
   if (VB_EPI(kEpiBias, true)) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] += bias8[i];
@@ -132,6 +157,8 @@ __device__ __forceinline__ void epilogue_finish8(const GemmEpilogue& ep, int m, 
     if (VB_EPI(kEpiAccum, ep.accumulate)) {
       red_add_f32x4(c, v[0], v[1], v[2], v[3]);
       red_add_f32x4(c + 4, v[4], v[5], v[6], v[7]);
+    } else if (hints & 8) {
+      stg_f8(c, v);
     } else {
       *reinterpret_cast<float4*>(c) = make_float4(v[0], v[1], v[2], v[3]);
       *reinterpret_cast<float4*>(c + 4) = make_float4(v[4], v[5], v[6], v[7]);

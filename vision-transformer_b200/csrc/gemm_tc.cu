@@ -55,6 +55,7 @@ struct TcParams {
   int M, N, K;
   int m_tiles, n_tiles;
   int splits, kb_per_split, kb_total;
+  int flags;   // bit 0: epilogue prefetches its read-side operands one tile ahead
 };
 
 template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG>
@@ -222,21 +223,41 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       const int m_blk = tile / p.n_tiles;
       const int n_blk = tile - m_blk * p.n_tiles;
       const int m0 = (m_blk * CG + static_cast<int>(rank)) * BM + q * 32;
-      // While the mainloop of this tile is still running: pull the epilogue's read-side operands (residual rows,
-      // dReLU mask rows) of my 32 x (BN/2) sub-tile into L2, one row segment per lane.
-      if (VB_EPI(kEpiResidual | kEpiMask, ep.residual != nullptr || ep.mask_aux != nullptr)) {
-        const int m = m0 + lane;
-        const int nb = n_blk * BN + half * CW;
+      // Pull the epilogue's read-side operands (residual rows, dReLU mask rows) of my 32 x (BN/2) sub-tile into L2, one
+      // row segment per lane: for THIS tile while its mainloop may still be running and, when the epilogue is the
+      // slower engine (short K: the mainloop is done long before), for the walker's NEXT tile (p.flags bit 0).
+      auto prefetch_unit = [&](int wu) {
+        const int tl = wu - (wu / tiles) * tiles;
+        const int mb = tl / p.n_tiles;
+        const int m = (mb * CG + static_cast<int>(rank)) * BM + q * 32 + lane;
+        const int nb = (tl - mb * p.n_tiles) * BN + half * CW;
         if (m < p.M && nb < p.N) {
           const int ncols = min(CW, p.N - nb);
           const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
           const int64_t off = orow * ep.ldc + nb;
-          if (VB_EPI(kEpiResidual, ep.residual != nullptr))
-            ptx::prefetch_l2_bulk(ep.residual + off, static_cast<uint32_t>(ncols) * 4u);
-          if (VB_EPI(kEpiMask, ep.mask_aux != nullptr))
-            ptx::prefetch_l2_bulk(reinterpret_cast<const OutT*>(ep.mask_aux) + off,
-                                  static_cast<uint32_t>(ncols) * static_cast<uint32_t>(sizeof(OutT)));
+          // bit 1: one prefetch.global.L2 per 128-byte line and lane (the bulk form is a uniform-datapath instruction:
+          // the compiler serialises it into a 32-iteration loop over the lanes, ~10 % of the epilogue's instructions)
+          if (VB_EPI(kEpiResidual, ep.residual != nullptr)) {
+            if (p.flags & 2) {
+              for (int b = 0; b < ncols * 4; b += 128) ptx::prefetch_l2_line(reinterpret_cast<const char*>(ep.residual + off) + b);
+            } else {
+              ptx::prefetch_l2_bulk(ep.residual + off, static_cast<uint32_t>(ncols) * 4u);
+            }
+          }
+          if (VB_EPI(kEpiMask, ep.mask_aux != nullptr)) {
+            const OutT* aux = reinterpret_cast<const OutT*>(ep.mask_aux) + off;
+            if (p.flags & 2) {
+              for (int b = 0; b < ncols * static_cast<int>(sizeof(OutT)); b += 128)
+                ptx::prefetch_l2_line(reinterpret_cast<const char*>(aux) + b);
+            } else {
+              ptx::prefetch_l2_bulk(aux, static_cast<uint32_t>(ncols) * static_cast<uint32_t>(sizeof(OutT)));
+            }
+          }
         }
+      };
+      if (VB_EPI(kEpiResidual | kEpiMask, ep.residual != nullptr || ep.mask_aux != nullptr)) {
+        if (!(p.flags & 1) || w == walker) prefetch_unit(w);
+        if ((p.flags & 1) && w + nwalkers < total_work) prefetch_unit(w + nwalkers);
       }
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
@@ -255,7 +276,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         for (int pass = 0; pass < 4; ++pass) {
           const int m = m0 + pass * 8 + rsub;
           const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
-          if (m < p.M) epilogue_fetch8<OutT, EPI>(ep, orow * ep.ldc + nn, m, nn, dst[pass]);
+          if (m < p.M) epilogue_fetch8<OutT, EPI>(ep, orow * ep.ldc + nn, m, nn, dst[pass], p.flags);
         }
       };
       fetch_chunk(0, pre_nx);
@@ -307,7 +328,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           uint32_t sign8 = 0;
           if (m < p.M && ncol_ok) {
             float v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-            epilogue_finish8<OutT, EPI>(ep, m, n, p.N, off[pass], v, pre[pass], bias8);
+            epilogue_finish8<OutT, EPI>(ep, m, n, p.N, off[pass], v, pre[pass], bias8, p.flags);
             if (VB_EPI(kEpiColSum, ep.col_sum != nullptr)) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) cs[i] += v[i];
@@ -559,6 +580,14 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
       }
     }
   }
+  // Epilogue memory-side switches (VITB200_GEMM_EPI_FLAGS overrides; measured on B200 at the ViT-B/16 proj site, fp32 out
+  // + bias + dropout + residual, 92.3 us with 0): 1 = L2 prefetch one tile ahead (+10 us), 2 = per-lane L2 prefetch
+  // (-5.5 us; aux-mask site 252 -> 237 us), 4 = residual loads bypass L1 (+12 us: the two 16-byte halves of a sector
+  // are then fetched twice), 8 = 256-bit residual loads / output stores (-2.5 us more).  Default 2 | 8.
+  static const int epi_flags_env = getenv("VITB200_GEMM_EPI_FLAGS") ? atoi(getenv("VITB200_GEMM_EPI_FLAGS")) : 10;
+  p.flags = epi_flags_env;
+  // 256-bit accesses need 32-byte aligned rows
+  if ((reinterpret_cast<uintptr_t>(ep.C) & 31) || (reinterpret_cast<uintptr_t>(ep.residual) & 31)) p.flags &= ~8;
   p.kb_per_split = ceil_div(p.kb_total, s);
   p.splits = ceil_div(p.kb_total, p.kb_per_split);
 

@@ -116,6 +116,10 @@ __device__ __forceinline__ void prefetch_l2_bulk(const void* gptr, uint32_t byte
                : "memory");
 }
 
+__device__ __forceinline__ void prefetch_l2_line(const void* gptr) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<uint64_t>(gptr)) : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
