@@ -156,6 +156,109 @@ ln_fwd_reg_kernel(const float* __restrict__ x, const float* __restrict__ gamma, 
   }
 }
 
+// Forward, bulk-copy ring version (round 2; E % 4 == 0, E <= 128 * VPL): one persistent CTA per SM, LNF_WARPS warps,
+// each warp owns a ring of `nst` row slots in shared memory that lane 0 fills with 1-D bulk copies nst-1 rows ahead.
+// The bytes in flight (warps x (nst-1) x 4E, ~100 KB per SM at E = 768) no longer depend on registers, which is what
+// limited the register-resident kernel above to ~4.1 TB/s of DRAM reads (two CTAs x 8 warps x one prefetched row).
+constexpr int LNF_WARPS = 16;
+constexpr int LNF_MAX_STAGES = 4;
+
+template <typename OutT, int VPL>
+__global__ void __launch_bounds__(LNF_WARPS * 32, 1)
+ln_fwd_ring_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                   OutT* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int E,
+                   float eps, int nst) {
+  extern __shared__ __align__(128) uint8_t lnf_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(lnf_smem);
+  uint64_t* bar = bars + warp * LNF_MAX_STAGES;
+  const uint32_t row_bytes = static_cast<uint32_t>(E) * 4u;
+  const uint32_t ring = smem_u32(bars + LNF_WARPS * LNF_MAX_STAGES) + static_cast<uint32_t>(warp * nst) * row_bytes;
+  if (lane == 0) {
+    for (int st = 0; st < nst; ++st) mbar_init(bar + st, 1);
+    fence_barrier_init();
+  }
+  __syncwarp();
+  pdl_wait();
+  pdl_trigger();
+  const int nq = E >> 2;
+  constexpr bool GB_REG = VPL <= 8;   // wide rows (512 threads x 12 chunks): gamma / beta come from L1 instead of registers
+  float4 gm[GB_REG ? VPL : 1], bt[GB_REG ? VPL : 1];
+  if constexpr (GB_REG) {
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const int i = lane + 32 * k;
+      gm[k] = i < nq ? __ldg(reinterpret_cast<const float4*>(gamma) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      bt[k] = i < nq ? __ldg(reinterpret_cast<const float4*>(beta) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  const int w0 = blockIdx.x * nw + warp, stride = gridDim.x * nw;
+  const int nrows = w0 < M ? (M - w0 + stride - 1) / stride : 0;
+  auto issue = [&](int it) {  // lane 0
+    const int st = it % nst;
+    mbar_arrive_expect_tx(bar + st, row_bytes);
+    bulk_load_1d(ring + st * row_bytes, x + (static_cast<int64_t>(w0) + static_cast<int64_t>(it) * stride) * E, row_bytes,
+                 bar + st);
+  };
+  if (lane == 0)
+    for (int it = 0; it < nst - 1 && it < nrows; ++it) issue(it);
+  const float inv_e = 1.f / static_cast<float>(E);
+  for (int it = 0; it < nrows; ++it) {
+    if (lane == 0 && it + nst - 1 < nrows) issue(it + nst - 1);   // refills the slot every lane left in iteration it-1
+    const int st = it % nst;
+    const int64_t m = static_cast<int64_t>(w0) + static_cast<int64_t>(it) * stride;
+    mbar_wait(bar + st, (it / nst) & 1);
+    const uint32_t sx = ring + st * row_bytes;
+    float4 cur[VPL];
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const int i = lane + 32 * k;
+      cur[k] = i < nq ? lds128(sx + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      s += (cur[k].x + cur[k].y) + (cur[k].z + cur[k].w);
+    }
+    const float mean = warp_sum(s) / static_cast<float>(E);
+    float sq = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      if (lane + 32 * k < nq) {
+        const float d0 = cur[k].x - mean, d1 = cur[k].y - mean, d2 = cur[k].z - mean, d3 = cur[k].w - mean;
+        sq = fmaf(d0, d0, sq); sq = fmaf(d1, d1, sq); sq = fmaf(d2, d2, sq); sq = fmaf(d3, d3, sq);
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(sq) * inv_e + eps);
+    if (lane == 0) {
+      if (mean_out) mean_out[m] = mean;
+      if (rstd_out) rstd_out[m] = rstd;
+    }
+    OutT* yr = y + m * E;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const int i = lane + 32 * k;
+      if (i < nq) {
+        float4 gk, bk;
+        if constexpr (GB_REG) {
+          gk = gm[k]; bk = bt[k];
+        } else {
+          gk = __ldg(reinterpret_cast<const float4*>(gamma) + i);
+          bk = __ldg(reinterpret_cast<const float4*>(beta) + i);
+        }
+        const float o0 = (cur[k].x - mean) * rstd * gk.x + bk.x, o1 = (cur[k].y - mean) * rstd * gk.y + bk.y;
+        const float o2 = (cur[k].z - mean) * rstd * gk.z + bk.z, o3 = (cur[k].w - mean) * rstd * gk.w + bk.w;
+        if constexpr (sizeof(OutT) == 2) {
+          uint2 o;
+          o.x = pack_bf16x2(o0, o1);
+          o.y = pack_bf16x2(o2, o3);
+          reinterpret_cast<uint2*>(yr)[i] = o;
+        } else {
+          reinterpret_cast<float4*>(yr)[i] = make_float4(o0, o1, o2, o3);
+        }
+      }
+    }
+    __syncwarp();  // every lane has its chunks of this slot in registers before lane 0 refills it
+  }
+}
+
 // dy: gradient w.r.t. the LN output (DyT).  g: fp32 residual-stream gradient, updated in place (g += dx) when
 // add_to_g != 0, overwritten (g = dx) otherwise.  dyn: optional down-cast copy of the new g multiplied by the
 // dropout factors of the layer that produced this LN's input.
@@ -523,9 +626,39 @@ int ln_forward(const float* x, const float* gamma, const float* beta, void* y, b
   static const bool reg_path = !(getenv("VITB200_LN_REG") && atoi(getenv("VITB200_LN_REG")) == 0);
   if (reg_path && (E & 3) == 0 && E <= 128 * 12 && aligned16(x) && aligned16(y) && aligned16(gamma) &&
       aligned16(beta) && M >= 4 * num_sms()) {
-    // register-resident rows, next row prefetched (the block LayerNorms; the [B, 4E] head LayerNorm stays below)
     ProfScope prof(kProfLnFwd, static_cast<double>(M) * E * (4 + (y_bf16 ? 2 : 4)) + 8.0 * M, 1, stream);
     const int vpl = ceil_div(E, 128);
+    // ---- bulk-copy ring kernel (VITB200_LN_FWD_RING=0 falls back to the register-resident kernel below)
+    static const bool ring_path = !(getenv("VITB200_LN_FWD_RING") && atoi(getenv("VITB200_LN_FWD_RING")) == 0);
+    const size_t lnf_fixed = LNF_WARPS * LNF_MAX_STAGES * 8;
+    int nst = static_cast<int>((208 * 1024 - lnf_fixed) / (static_cast<size_t>(LNF_WARPS) * E * 4));
+    if (nst > LNF_MAX_STAGES) nst = LNF_MAX_STAGES;
+    if (ring_path && nst >= 2 && M >= 4 * LNF_WARPS) {
+      const size_t smem = lnf_fixed + static_cast<size_t>(nst) * LNF_WARPS * E * 4;
+      const int grid = std::min(num_sms(), ceil_div(M, LNF_WARPS));
+#define VB_LNF_RING(T, V)                                                                                         \
+  do {                                                                                                            \
+    static bool attr_set = false;                                                                                 \
+    if (!attr_set) {                                                                                              \
+      VB_CHECK_CUDA(cudaFuncSetAttribute(ln_fwd_ring_kernel<T, V>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                         208 * 1024));                                                            \
+      attr_set = true;                                                                                            \
+    }                                                                                                             \
+    VB_CHECK_CUDA(launch_pdl(ln_fwd_ring_kernel<T, V>, dim3(grid), dim3(LNF_WARPS * 32), smem, stream, 1, x, gamma, \
+                             beta, static_cast<T*>(y), mean, rstd, M, E, eps, nst));                              \
+  } while (0)
+#define VB_LNF_RING_V(T)                                                                                          \
+  do {                                                                                                            \
+    if (vpl <= 3) VB_LNF_RING(T, 3); else if (vpl <= 6) VB_LNF_RING(T, 6); else if (vpl <= 8) VB_LNF_RING(T, 8);   \
+    else VB_LNF_RING(T, 12);                                                                                      \
+  } while (0)
+      if (y_bf16) VB_LNF_RING_V(bf16); else VB_LNF_RING_V(float);
+#undef VB_LNF_RING_V
+#undef VB_LNF_RING
+      VB_CHECK_LAUNCH();
+      return kOk;
+    }
+    // register-resident rows, next row prefetched (the block LayerNorms; the [B, 4E] head LayerNorm stays below)
     const int per_sm = vpl <= 3 ? 4 : vpl <= 6 ? 2 : 1;  // CTAs resident per SM by register count
     const int grid = ln_grid(M, LN_WARPS, per_sm);
 #define VB_LN_REG(V)                                                                                              \
