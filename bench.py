@@ -52,9 +52,9 @@ def parse():
     ap.add_argument("--dropout", type=float, default=0.2,
                     help="EXPERIMENTS ONLY: the reference hard-codes 0.2 (transformer.py:35,53); the line says so if changed")
     ap.add_argument("--bucket-mb", type=float, default=0,
-                    help="gradient bucket size in MB of fp32 gradient; 0 = auto: ONE bucket (exchange after backward, nothing "
-                         "co-runs with the persistent GEMMs) when the arena is <= 400 MB, else 48 MB buckets overlapped "
-                         "with backward")
+                    help="gradient bucket size in MB of fp32 gradient; 0 = auto (train_dp.auto_bucket_mb): TWO buckets, 80 %% of "
+                         "the arena then the rest, when the arena is <= 400 MB, else 48 MB buckets overlapped with "
+                         "backward; a huge value gives ONE bucket exchanged after backward")
     ap.add_argument("--zero1", default="auto", choices=["auto", "0", "1"],
                     help="ZeRO-1 exchange (reduce-scatter / sharded AdamW / all-gather); auto = on when N > 1")
     ap.add_argument("--grad-comm", default="auto", choices=["auto", "bf16", "fp32"], help="gradient exchange dtype")
@@ -292,14 +292,7 @@ def run_b200(args):
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     wl = workload(args)
     if args.bucket_mb <= 0:
-        # measured on one 8 x B200 box (profiles/r02_bench_n8box_*.json, ViT-B/16, 353 MB of fp32 gradients): one bucket
-        # 34.79 ms, seven 48 MB buckets overlapped with backward 35.22 ms, one GPU 33.91 ms — a collective that co-runs
-        # with the persistent GEMM kernels costs more (SMs taken from their static tile walk) than exposing 0.5 GB
-        probe = train_dp.param_layout(C=3, P=wl["patch_size"], E=wl["embedding_size"], H=wl["num_heads"],
-                                      L=wl["num_blocks"], T=(wl["image_size"] // wl["patch_size"]) ** 2 + 1,
-                                      B=args.batch, classes=args.classes)
-        arena_mb = train_dp.arena_offsets(probe)[1] * 4 / 2 ** 20
-        args.bucket_mb = 1e6 if arena_mb <= 400 else 48
+        args.bucket_mb = None   # train_dp.auto_bucket_mb: two buckets for small arenas, 48 MB buckets for large ones
     zero1 = None if args.zero1 == "auto" else args.zero1 == "1"
     grad_comm = None if args.grad_comm == "auto" else args.grad_comm
     tr = train_dp.DPTrainer(batch_size=args.batch, dtype=dtype, device=dev, process_group=pg, world_size=world,

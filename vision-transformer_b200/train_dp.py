@@ -72,6 +72,17 @@ def arena_offsets(layout):
     return offs, (tot + SHARD_ALIGN - 1) // SHARD_ALIGN * SHARD_ALIGN
 
 
+def auto_bucket_mb(total_elems):
+    """Bucket size (MB of fp32 gradients) of the exchange when the caller does not choose one.  A collective that
+    co-runs with the persistent GEMM kernels takes SMs from their static tile walk, so small arenas (<= 400 MB: ViT-S/B)
+    use TWO buckets — 80 % of the arena (head + all but the first ~two blocks), whose exchange overlaps the rest of the
+    backward pass, and the remainder, the only part left exposed.  Measured on 4 x B200, ViT-B/16 (337 MB):
+    one bucket 33.53-33.64 ms, [279 | 58] MB 33.27, [306 | 31] 33.28, [252 | 85] 33.41, seven 48 MB buckets 33.46, one GPU
+    32.55 (profiles/r02_bucket_policy_n4.txt).  Larger arenas keep 48 MB buckets overlapped with backward."""
+    arena_mb = total_elems * 4 / 2 ** 20
+    return 0.8 * arena_mb if arena_mb <= 400 else 48.0
+
+
 def make_buckets(layout, offs, total, bucket_elems):
     """Contiguous arena slices in the order their gradients complete (head first, embedding last).
     -> [(start, end, stage_that_completes_it)]"""
@@ -221,7 +232,7 @@ class DPTrainer:
     def __init__(self, *, input_channels=3, num_classes=2, image_size=224, patch_size=16, embedding_size=768,
                  num_heads=12, num_blocks=12, batch_size=256, dtype=torch.bfloat16, device=None, lr=1e-4,
                  weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8, dropout_p=eng.DROPOUT_P, process_group=None,
-                 world_size=1, bucket_mb=48, seed=0, last_block_row0=False, zero1=None, grad_comm=None):
+                 world_size=1, bucket_mb=None, seed=0, last_block_row0=False, zero1=None, grad_comm=None):
         dev = torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
         eng.require_cuda(torch.empty(0, device=dev), "trainer device")
         if _C.lib().vitb200_device_ok() != 1:
@@ -249,6 +260,8 @@ class DPTrainer:
         z = lambda dt, n=None: torch.zeros(self.total if n is None else n, dtype=dt, device=dev)  # noqa: E731
         self.p, self.g = z(torch.float32), z(torch.float32)
         self.shadow = z(torch.bfloat16) if dtype == torch.bfloat16 else None
+        if bucket_mb is None or bucket_mb <= 0:
+            bucket_mb = auto_bucket_mb(self.total)
         self.buckets = make_buckets(self.layout, self.offs, self.total, int(bucket_mb * (1 << 20) / 4))
         # exchange scheme (module docstring): ZeRO-1 by default when there is more than one rank; gradients travel
         # in bf16 in bf16 mode and in fp32 in fp32 mode (the DP == single-GPU 1e-5 gate)
