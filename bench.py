@@ -53,8 +53,8 @@ def parse():
                     help="EXPERIMENTS ONLY: the reference hard-codes 0.2 (transformer.py:35,53); the line says so if changed")
     ap.add_argument("--bucket-mb", type=float, default=0,
                     help="gradient bucket size in MB of fp32 gradient; 0 = auto (train_dp.auto_bucket_mb): TWO buckets, 80 %% of "
-                         "the arena then the rest, when the arena is <= 400 MB, else 48 MB buckets overlapped with "
-                         "backward; a huge value gives ONE bucket exchanged after backward")
+                         "the arena (its exchange overlaps the rest of backward) then the remainder; a huge value gives "
+                         "ONE bucket exchanged after backward")
     ap.add_argument("--zero1", default="auto", choices=["auto", "0", "1"],
                     help="ZeRO-1 exchange (reduce-scatter / sharded AdamW / all-gather); auto = on when N > 1")
     ap.add_argument("--grad-comm", default="auto", choices=["auto", "bf16", "fp32"], help="gradient exchange dtype")
@@ -292,7 +292,7 @@ def run_b200(args):
     dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
     wl = workload(args)
     if args.bucket_mb <= 0:
-        args.bucket_mb = None   # train_dp.auto_bucket_mb: two buckets for small arenas, 48 MB buckets for large ones
+        args.bucket_mb = None   # train_dp.auto_bucket_mb: two buckets (80 % of the arena, then the rest)
     zero1 = None if args.zero1 == "auto" else args.zero1 == "1"
     grad_comm = None if args.grad_comm == "auto" else args.grad_comm
     tr = train_dp.DPTrainer(batch_size=args.batch, dtype=dtype, device=dev, process_group=pg, world_size=world,

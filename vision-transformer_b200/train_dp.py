@@ -73,14 +73,13 @@ def arena_offsets(layout):
 
 
 def auto_bucket_mb(total_elems):
-    """Bucket size (MB of fp32 gradients) of the exchange when the caller does not choose one.  A collective that
-    co-runs with the persistent GEMM kernels takes SMs from their static tile walk, so small arenas (<= 400 MB: ViT-S/B)
-    use TWO buckets — 80 % of the arena (head + all but the first ~two blocks), whose exchange overlaps the rest of the
-    backward pass, and the remainder, the only part left exposed.  Measured on 4 x B200, ViT-B/16 (337 MB):
-    one bucket 33.53-33.64 ms, [279 | 58] MB 33.27, [306 | 31] 33.28, [252 | 85] 33.41, seven 48 MB buckets 33.46, one GPU
-    32.55 (profiles/r02_bucket_policy_n4.txt).  Larger arenas keep 48 MB buckets overlapped with backward."""
-    arena_mb = total_elems * 4 / 2 ** 20
-    return 0.8 * arena_mb if arena_mb <= 400 else 48.0
+    """Bucket size (MB of fp32 gradients) of the exchange when the caller does not choose one: TWO buckets — 80 % of the
+    arena (the head and all but the first few blocks), whose exchange overlaps the rest of the backward pass, and the
+    remainder, the only part left exposed.  A collective that co-runs with the persistent GEMM kernels takes SMs from
+    their static tile walk, so FEW launches beat many small ones.  Measured on 4 x B200 (profiles/r02_bucket_policy_n4.txt):
+    ViT-B/16 (337 MB) one bucket 33.53-33.64 ms, [279 | 58] MB 33.27, seven 48 MB buckets 33.46, one GPU 32.55;
+    ViT-L/16 (1.17 GB) [1025 | 149] MB 105.7 ms, three buckets 106.0, twenty-five 48 MB buckets 107.6-107.9, one GPU 104.6."""
+    return 0.8 * total_elems * 4 / 2 ** 20
 
 
 def make_buckets(layout, offs, total, bucket_elems):
