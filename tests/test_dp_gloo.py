@@ -181,3 +181,20 @@ def test_every_stage_starts_on_a_shard_boundary():
     for be in (1, 5000, 10 ** 9):
         for a, b, _ in train_dp.make_buckets(layout, offs, total, be):
             assert (b - a) % (8 * train_dp.ALIGN) == 0
+
+
+def test_default_exchange_policy_is_two_buckets_that_shard_over_eight_ranks():
+    """train_dp.auto_bucket_mb (profiles/r02_bucket_policy_n4.txt): 80 % of the gradient arena, then the rest — for
+    every BASELINE config, each bucket a union of whole stages that splits into 8 aligned shards (ZeRO-1)."""
+    for E, H, L, P, img in ((384, 6, 12, 16, 224), (768, 12, 12, 16, 224), (1024, 16, 24, 16, 224), (1280, 16, 32, 14, 336)):
+        T = (img // P) ** 2 + 1
+        layout = train_dp.param_layout(C=3, P=P, E=E, H=H, L=L, T=T, B=4, classes=2)
+        offs, total = train_dp.arena_offsets(layout)
+        mb = train_dp.auto_bucket_mb(total)
+        buckets = train_dp.make_buckets(layout, offs, total, int(mb * (1 << 20) / 4))
+        assert len(buckets) == 2, (E, [(b - a) for a, b, _ in buckets])
+        (a0, b0, _), (a1, b1, st1) = buckets
+        assert b0 == total and a0 == b1 and a1 == 0 and st1 == layout[0][0]      # contiguous, embedding stage closes
+        assert 0.78 * total <= b0 - a0 <= 0.95 * total
+        for a, b, _ in buckets:
+            assert (b - a) % (8 * train_dp.ALIGN) == 0
