@@ -90,6 +90,14 @@ typedef struct {
   uint32_t* bits_out;
   const uint32_t* mask_bits;
   int bits_rows;         /* >= M */
+  /* Fused per-head row dot (BF16 inputs, BF16 output, N == 64 * dot_H, M % dot_T == 0, no mask_aux / row map):
+   * dot_out[(b * dot_H + h) * dot_T + t] = sum over the 64 columns of head h of (value stored at C[m,n]) * dot_aux[m,n],
+   * m = b * dot_T + t.  With C = dO (the gradient of the concatenated head outputs, reference transformer.py:45-46) and
+   * dot_aux = O this is delta = rowsum(dO o O), the softmax-backward statistic of transformer.py:26-27's autograd. */
+  const void* dot_aux;   /* [M][ldc], C's dtype and layout, or NULL */
+  float* dot_out;        /* [M / dot_T][dot_H][dot_T] fp32, or NULL */
+  int dot_T;
+  int dot_H;
 } vitb200_gemm_args;
 
 int vitb200_gemm(const vitb200_gemm_args* args, void* stream);

@@ -119,6 +119,39 @@ def test_gemm_dropout_epilogue_matches_exported_mask(lib):
     assert (keep != keep2).float().mean().item() > 0.2  # independent streams
 
 
+@pytest.mark.parametrize("Bi,T,H,K", [(3, 197, 12, 768), (2, 65, 4, 256), (5, 130, 2, 64)])
+def test_gemm_fused_head_dot_is_the_attention_backward_delta(lib, Bi, T, H, K):
+    """kEpiDot: delta[b,h,t] = sum_j dO[b*T+t, 64h+j] * O[b*T+t, 64h+j] from the epilogue of the GEMM that produces dO
+    (NN layout, as the block backward calls it), against torch on the STORED bf16 values and against the stand-alone
+    delta kernel through vitb200_attn_bwd's scratch."""
+    C = _C()
+    torch.manual_seed(11)
+    M, N = Bi * T, 64 * H
+    A = (torch.randn(M, K, device=DEV) * 0.5).bfloat16()
+    W = (torch.randn(K, N, device=DEV) / K ** 0.5).bfloat16()          # MN-major B operand: [K][N]
+    O = torch.randn(M, N, device=DEV).bfloat16()
+    dO = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    delta = torch.full((Bi, H, T), float("nan"), device=DEV)
+    C.gemm(A, W, dO, b_major=C.MAJOR_MN, M=M, N=N, K=K, dot_aux=O, dot_out=delta, dot_T=T, dot_H=H)
+    plain = torch.empty_like(dO)
+    C.gemm(A, W, plain, b_major=C.MAJOR_MN, M=M, N=N, K=K)
+    assert torch.equal(dO, plain)                                       # the output itself is untouched by the fusion
+    ref = (dO.float() * O.float()).reshape(Bi, T, H, 64).sum(-1).permute(0, 2, 1)
+    assert torch.isfinite(delta).all()
+    assert (delta - ref).abs().max().item() <= 2e-5 * (ref.abs().max().item() + 1.0)
+    # bit-identical to the stand-alone delta kernel (same association of the 64 products): vitb200_attn_bwd fills its
+    # `delta` scratch from (O, dO) before anything else
+    qkv = (torch.randn(M, 3 * N, device=DEV) * 0.1).bfloat16()
+    lse = torch.zeros(Bi, H, T, device=DEV)
+    scratch = torch.full((Bi, H, T), float("nan"), device=DEV)
+    dqkv = torch.empty_like(qkv)
+    C.check(lib.vitb200_attn_bwd(qkv.data_ptr(), O.data_ptr(), dO.data_ptr(), lse.data_ptr(), scratch.data_ptr(),
+                                 dqkv.data_ptr(), C.BF16, Bi, T, H, 64, 8.0, C.stream_ptr()))
+    assert torch.equal(delta, scratch)
+    with pytest.raises(RuntimeError, match="fused head dot"):
+        C.gemm(A, W, dO, b_major=C.MAJOR_MN, M=M, N=N, K=K, dot_aux=O, dot_out=delta, dot_T=T, dot_H=H + 1)
+
+
 def test_gemm_rejects_bad_arguments(lib):
     C = _C()
     A = torch.randn(16, 12, device=DEV).bfloat16()  # lda = 12: not a 16-byte row pitch

@@ -36,6 +36,7 @@ out_e, out_f, out_3e = torch.empty(M, E, device=dev, dtype=bf), torch.empty(M, F
 b_e, b_f = rnd(E, dt=torch.float32), rnd(F, dt=torch.float32)
 dw_qkv, dw_proj, dw_fc1, dw_fc2 = (torch.zeros(s, device=dev) for s in ((3 * E, E), (E, E), (F, E), (E, F)))
 K0, K1 = _C.MAJOR_K, _C.MAJOR_MN
+x_e2, delta_buf = rnd(M, E), torch.empty(B, E // 64, T, device=dev)
 hbits = torch.zeros((F // 32) * M, device=dev, dtype=torch.int32)  # ReLU sign bits, word (n/32)*M + m
 sites = [
     # name, flops, ours, torch
@@ -55,6 +56,7 @@ sites = [
     ("bwd dln2  NN bf16", 2 * M * F * E, lambda: _C.gemm(x_f, w_fc1, out_e, b_major=K1, M=M, N=E, K=F), lambda: x_f @ w_fc1),
     ("bwd dWprj TN acc", 2 * M * E * E, lambda: _C.gemm(x_e, x_e, dw_proj, a_major=K1, b_major=K1, M=E, N=E, K=M, accumulate=True), lambda: x_e.t() @ x_e),
     ("bwd dO    NN bf16", 2 * M * E * E, lambda: _C.gemm(x_e, w_proj, out_e, b_major=K1, M=M, N=E, K=E), lambda: x_e @ w_proj),
+    ("bwd dO    NN bf16 +delta", 2 * M * E * E, lambda: _C.gemm(x_e, w_proj, out_e, b_major=K1, M=M, N=E, K=E, dot_aux=x_e2, dot_out=delta_buf, dot_T=T, dot_H=E // 64), lambda: x_e @ w_proj),
     ("bwd dWqkv TN acc", 2 * M * 3 * E * E, lambda: _C.gemm(x_3e, x_e, dw_qkv, a_major=K1, b_major=K1, M=3 * E, N=E, K=M, accumulate=True), lambda: x_3e.t() @ x_e),
     ("bwd dln1  NN bf16", 2 * M * 3 * E * E, lambda: _C.gemm(x_3e, w_qkv, out_e, b_major=K1, M=M, N=E, K=3 * E), lambda: x_3e @ w_qkv),
 ]
@@ -69,7 +71,7 @@ for name, fl, ours, ref in sites:
     if "drop" not in name or True:
         pass
     print(f"{name:<34} ours {to*1e3:7.1f} us {fl/to/1e9:7.0f} TF/s | cuBLAS {tt*1e3:7.1f} us {fl/tt/1e9:7.0f} TF/s | ratio {to/tt:4.2f}")
-    if ("bias+res" in name and "drop" not in name) or "plain" in name or "mask" in name or name.endswith("relu"):
+    if ("bias+res" in name and "drop" not in name) or "plain" in name or "mask" in name or name.endswith("relu") or "+delta" in name:
         continue  # the dropout variant is the one the training step uses
     tot_o += to; tot_t += tt
 print(f"per-block GEMM total: ours {tot_o:.3f} ms, cuBLAS (no epilogues) {tot_t:.3f} ms; x12 blocks = {12*tot_o:.1f} / {12*tot_t:.1f} ms")

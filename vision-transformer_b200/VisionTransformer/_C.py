@@ -44,6 +44,10 @@ class GemmArgs(ctypes.Structure):
         ("bits_out", c_void_p),
         ("mask_bits", c_void_p),
         ("bits_rows", c_int),
+        ("dot_aux", c_void_p),
+        ("dot_out", c_void_p),
+        ("dot_T", c_int),
+        ("dot_H", c_int),
     ]
 
 
@@ -236,7 +240,8 @@ def ptr(t):
 
 def gemm(A, B, C, *, a_major=MAJOR_K, b_major=MAJOR_K, M, N, K, bias=None, relu=False, mask_aux=None,
          dropout=(0.0, 0, 0), row_add=None, row_period=0, row_group_stride=0, residual=None, splits=0,
-         accumulate=False, col_sum=None, bits_out=None, mask_bits=None, bits_rows=0, lda=None, ldb=None, ldc=None):
+         accumulate=False, col_sum=None, bits_out=None, mask_bits=None, bits_rows=0, lda=None, ldb=None, ldc=None,
+         dot_aux=None, dot_out=None, dot_T=0, dot_H=0):
     """C[m,n] = epilogue(sum_k A(m,k) B(n,k)); see vitb200_gemm_args in include/vitb200.h."""
     a = GemmArgs()
     a.M, a.N, a.K = M, N, K
@@ -255,5 +260,6 @@ def gemm(A, B, C, *, a_major=MAJOR_K, b_major=MAJOR_K, M, N, K, bias=None, relu=
     a.splits, a.accumulate = splits, int(accumulate)
     a.col_sum = ptr(col_sum)
     a.bits_out, a.mask_bits, a.bits_rows = ptr(bits_out), ptr(mask_bits), int(bits_rows)
+    a.dot_aux, a.dot_out, a.dot_T, a.dot_H = ptr(dot_aux), ptr(dot_out), int(dot_T), int(dot_H)
     check(lib().vitb200_gemm(ctypes.byref(a), stream_ptr()))
     return C

@@ -144,6 +144,11 @@ int vitb200_gemm(const vitb200_gemm_args* a, void* stream) {
   ep.bits_out = a->bits_out;
   ep.mask_bits = a->mask_bits;
   ep.bits_rows = a->bits_rows;
+  ep.dot_aux = a->dot_aux;
+  ep.dot_out = a->dot_out;
+  ep.dot_T = a->dot_T;
+  ep.dot_H = a->dot_H;
+  VB_REQUIRE(a->dot_out == nullptr || a->in_dtype == VITB200_BF16, "vitb200_gemm: the fused head dot needs BF16 inputs");
   ep.drop = make_dropout(a->dropout.p, a->dropout.seed, a->dropout.stream);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (a->in_dtype == VITB200_BF16) {

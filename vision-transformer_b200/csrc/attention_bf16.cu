@@ -493,8 +493,9 @@ int attn_bf16_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int 
 }
 
 int attn_bf16_backward(const bf16* qkv, const bf16* out, const bf16* d_o, const float* lse, float* delta, bf16* dqkv,
-                       int B, int T, int H, int hs, float scale, cudaStream_t stream) {
-  VB_PROPAGATE(attn_delta(out, d_o, true, delta, B, T, H, hs, stream));
+                       int B, int T, int H, int hs, float scale, cudaStream_t stream, bool delta_ready) {
+  // delta_ready: the caller's dO GEMM already wrote delta = rowsum(dO o O) from its epilogue (kEpiDot)
+  if (!delta_ready) VB_PROPAGATE(attn_delta(out, d_o, true, delta, B, T, H, hs, stream));
   if (use_tc_attention(T, hs)) return attn_tc_backward(qkv, d_o, lse, delta, dqkv, B, T, H, hs, scale, stream);
   switch (hs) {
     case 16: return bwd_launch<16>(qkv, d_o, lse, delta, dqkv, B, T, H, scale, stream);

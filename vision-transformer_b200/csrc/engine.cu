@@ -501,10 +501,17 @@ static int block_backward(const vitb200_dims* d, int layer, const vitb200_block_
   // dO[M,E] = s3 Wproj
   l = Lin(); l.M = M; l.N = E; l.K = E; l.b_major = 1; l.A = sc.s3; l.lda = E; l.B = p->w_proj; l.ldb = E;
   l.ep = make_ep(sc.s2, attn_ld); l.out_f32 = !bf;
+  // VITB200_FUSED_DELTA=1: delta = rowsum(dO o O) per (image, head, token) straight from this GEMM's epilogue (64-wide
+  // heads, every row computed; bit-identical to the stand-alone kernel).  Off by default: measured NEUTRAL — the K = 768
+  // GEMM is epilogue-bound and grows 47.7 -> 68.1 us, the delta kernel it replaces takes ~29 us; step 32.65 vs 32.63 ms
+  // (profiles/r02_fused_delta_ab.txt).
+  static const bool fuse_delta_on = getenv("VITB200_FUSED_DELTA") && atoi(getenv("VITB200_FUSED_DELTA")) != 0;
+  const bool fuse_delta = fuse_delta_on && bf && !row0 && hs == 64 && M == M_all;
+  if (fuse_delta) { l.ep.dot_aux = a.attn; l.ep.dot_out = sc.delta; l.ep.dot_T = d->T; l.ep.dot_H = d->H; }
   VB_PROPAGATE(run_lin(bf, l, s));
   M = M_all;   // from here on every token takes part
   // dqkv[M,3E] (into s1)
-  if (bf) VB_PROPAGATE(attn_bf16_backward(static_cast<const bf16*>(a.qkv), static_cast<const bf16*>(a.attn), static_cast<const bf16*>(sc.s2), a.lse, sc.delta, static_cast<bf16*>(sc.s1), d->B, d->T, d->H, hs, scale, s));
+  if (bf) VB_PROPAGATE(attn_bf16_backward(static_cast<const bf16*>(a.qkv), static_cast<const bf16*>(a.attn), static_cast<const bf16*>(sc.s2), a.lse, sc.delta, static_cast<bf16*>(sc.s1), d->B, d->T, d->H, hs, scale, s, fuse_delta));
   else VB_PROPAGATE(attn_f32_backward(static_cast<const float*>(a.qkv), static_cast<const float*>(a.attn), static_cast<const float*>(sc.s2), a.lse, sc.delta, static_cast<float*>(sc.s1), d->B, d->T, d->H, hs, scale, s));
   // dWqkv[3E,E] += dqkv^T ln1
   l = Lin(); l.M = 3 * E; l.N = E; l.K = M; l.a_major = 1; l.b_major = 1; l.A = sc.s1; l.lda = 3 * E; l.B = a.ln1; l.ldb = E;

@@ -22,6 +22,11 @@ struct GemmEpilogue {
   const uint32_t* mask_bits; // or null: keep v where the bit is set  (tensor-core kernel only, N % 32 == 0)
   int bits_rows;
   Dropout drop;
+  // Fused attention-backward statistic (tensor-core kernel, 2-byte output, N % 64 == 0): dot_out[(b*dot_H + h)*dot_T + t] =
+  // sum over the 64 columns of head h of stored(m, n) * dot_aux(m, n), m = b*dot_T + t  (delta = rowsum(dO o O), the dO GEMM)
+  const void* dot_aux = nullptr;   // [M][ldc] (OutT), same layout as C
+  float* dot_out = nullptr;
+  int dot_T = 0, dot_H = 0;
 };
 
 // Compile-time epilogue specialisation: a kernel instantiated with EPI != kEpiGeneric evaluates each option as a
@@ -29,13 +34,13 @@ struct GemmEpilogue {
 // combination reachable through the C ABI still works.
 enum : uint32_t {
   kEpiBias = 1u, kEpiRelu = 2u, kEpiMask = 4u, kEpiDrop = 8u, kEpiRowMap = 16u, kEpiResidual = 32u, kEpiAccum = 64u,
-  kEpiColSum = 128u, kEpiBitsOut = 256u, kEpiBitMask = 512u, kEpiGeneric = 0x80000000u
+  kEpiColSum = 128u, kEpiBitsOut = 256u, kEpiBitMask = 512u, kEpiDot = 1024u, kEpiGeneric = 0x80000000u
 };
 inline uint32_t epi_flags(const GemmEpilogue& ep) {
   return (ep.bias ? kEpiBias : 0u) | (ep.relu ? kEpiRelu : 0u) | (ep.mask_aux ? kEpiMask : 0u) |
          (ep.drop.p > 0.f ? kEpiDrop : 0u) | ((ep.row_add || ep.row_period > 0) ? kEpiRowMap : 0u) |
          (ep.residual ? kEpiResidual : 0u) | (ep.accumulate ? kEpiAccum : 0u) | (ep.col_sum ? kEpiColSum : 0u) |
-         (ep.bits_out ? kEpiBitsOut : 0u) | (ep.mask_bits ? kEpiBitMask : 0u);
+         (ep.bits_out ? kEpiBitsOut : 0u) | (ep.mask_bits ? kEpiBitMask : 0u) | (ep.dot_out ? kEpiDot : 0u);
 }
 #define VB_EPI(flag, cond) ((EPI == ::vb::kEpiGeneric) ? (cond) : ((EPI & (flag)) != 0u))
 
@@ -92,6 +97,10 @@ __device__ __forceinline__ void epilogue_fetch8(const GemmEpilogue& ep, int64_t 
     const OutT* aux = reinterpret_cast<const OutT*>(ep.mask_aux) + off;
     pre.a0 = __ldg(reinterpret_cast<const uint4*>(aux));
     if constexpr (sizeof(OutT) == 4) pre.a1 = __ldg(reinterpret_cast<const uint4*>(aux) + 1);
+  }
+  if constexpr (sizeof(OutT) == 2) {   // the dot operand shares the aux registers (never combined with the aux mask)
+    if (VB_EPI(kEpiDot, ep.dot_out != nullptr))
+      pre.a0 = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const OutT*>(ep.dot_aux) + off));
   }
 }
 

@@ -244,8 +244,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
               ptx::prefetch_l2_bulk(ep.residual + off, static_cast<uint32_t>(ncols) * 4u);
             }
           }
-          if (VB_EPI(kEpiMask, ep.mask_aux != nullptr)) {
-            const OutT* aux = reinterpret_cast<const OutT*>(ep.mask_aux) + off;
+          if (VB_EPI(kEpiMask | kEpiDot, ep.mask_aux != nullptr || ep.dot_out != nullptr)) {
+            const OutT* aux = reinterpret_cast<const OutT*>(VB_EPI(kEpiDot, ep.dot_out != nullptr) ? ep.dot_aux : ep.mask_aux) + off;
             if (p.flags & 2) {
               for (int b = 0; b < ncols * static_cast<int>(sizeof(OutT)); b += 128)
                 ptx::prefetch_l2_line(reinterpret_cast<const char*>(aux) + b);
@@ -255,7 +255,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           }
         }
       };
-      if (VB_EPI(kEpiResidual | kEpiMask, ep.residual != nullptr || ep.mask_aux != nullptr)) {
+      if (VB_EPI(kEpiResidual | kEpiMask | kEpiDot, ep.residual != nullptr || ep.mask_aux != nullptr || ep.dot_out != nullptr)) {
         if (!(p.flags & 1) || w == walker) prefetch_unit(w);
         if ((p.flags & 1) && w + nwalkers < total_work) prefetch_unit(w + nwalkers);
       }
@@ -269,6 +269,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       // Read-side operands (residual / dReLU mask) are fetched ONE CHUNK AHEAD into registers: their L2 latency is
       // covered by the previous chunk's transpose + stores instead of stalling every chunk.
       EpiPre pre_nx[4];
+      float dacc[4] = {0.f, 0.f, 0.f, 0.f};   // kEpiDot: per-row partial sums over the two 32-column chunks of a 64-wide head
       auto fetch_chunk = [&](int cc, EpiPre (&dst)[4]) {
         const int nn = nb + cc * 32 + cg * 8;
         if (nn >= p.N) return;
@@ -326,9 +327,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           const float4 lo = ptx::lds128(stg_s + static_cast<uint32_t>(R * 128 + (((2 * cg) ^ (R & 7)) << 4)));
           const float4 hi = ptx::lds128(stg_s + static_cast<uint32_t>(R * 128 + (((2 * cg + 1) ^ (R & 7)) << 4)));
           uint32_t sign8 = 0;
+          float dpart = 0.f;
           if (m < p.M && ncol_ok) {
             float v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
             epilogue_finish8<OutT, EPI>(ep, m, n, p.N, off[pass], v, pre[pass], bias8, p.flags);
+            if constexpr (sizeof(OutT) == 2) {
+              if (VB_EPI(kEpiDot, ep.dot_out != nullptr)) {   // stored (bf16-rounded) values x the aux operand
+                const uint32_t ov[4] = {pre[pass].a0.x, pre[pass].a0.y, pre[pass].a0.z, pre[pass].a0.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const uint32_t pk = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+                  dpart = fmaf(__uint_as_float(pk << 16), __uint_as_float(ov[j] << 16), dpart);
+                  dpart = fmaf(__uint_as_float(pk & 0xffff0000u), __uint_as_float(ov[j] & 0xffff0000u), dpart);
+                }
+              }
+            }
             if (VB_EPI(kEpiColSum, ep.col_sum != nullptr)) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) cs[i] += v[i];
@@ -336,6 +349,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             if (VB_EPI(kEpiBitsOut, ep.bits_out != nullptr)) {
 #pragma unroll
               for (int i = 0; i < 8; ++i) sign8 |= (v[i] > 0.f ? 1u : 0u) << i;
+            }
+          }
+          if constexpr (sizeof(OutT) == 2) {
+            if (VB_EPI(kEpiDot, ep.dot_out != nullptr)) {   // warp-uniform
+              // Same association as attn_delta_vec_kernel (8 sequential FMAs per 16-byte piece, then a butterfly over
+              // the head's 8 pieces with strides 4, 2, 1), so the fused statistic is BIT-IDENTICAL to the stand-alone
+              // kernel's: lane cg holds piece cg of the even chunk and piece 4 + cg of the odd one.
+              if (c & 1) {                                   // second chunk of the head: n0 % 64 == 32
+                float t = dacc[pass] + dpart;                //  stride 4
+                t += __shfl_xor_sync(0xffffffffu, t, 2);
+                t += __shfl_xor_sync(0xffffffffu, t, 1);
+                if (cg == 0 && m < p.M && ncol_ok) {
+                  const int bi = m / ep.dot_T, ti = m - bi * ep.dot_T;
+                  ep.dot_out[(static_cast<int64_t>(bi) * ep.dot_H + (n0 >> 6)) * ep.dot_T + ti] = t;
+                }
+              } else {
+                dacc[pass] = dpart;
+              }
             }
           }
           if (VB_EPI(kEpiBitsOut, ep.bits_out != nullptr)) {   // warp-uniform: the 4 lanes of a row merge their bytes
@@ -531,6 +562,10 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   VB_REQUIRE(ep.residual == nullptr || out_f32, "gemm_tc: residual add needs an fp32 output");
   VB_REQUIRE((ep.bits_out == nullptr && ep.mask_bits == nullptr) || (N % 32 == 0 && ep.bits_rows >= M),
              "gemm_tc: bit masks need N %% 32 == 0 and bits_rows >= M (N=%d, bits_rows=%d)", N, ep.bits_rows);
+  VB_REQUIRE(ep.dot_out == nullptr || (!out_f32 && ep.dot_aux != nullptr && N % 64 == 0 && ep.dot_T > 0 &&
+                                       ep.dot_H * 64 == N && M % ep.dot_T == 0 && ep.mask_aux == nullptr &&
+                                       ep.row_period == 0 && aligned16(ep.dot_aux)),
+             "gemm_tc: the fused head dot needs a 2-byte output, N = 64 * dot_H, M a multiple of dot_T and no aux mask / row map");
   constexpr int BN = 256;
 
   // CTA pairs (256-row tiles) whenever there is more than one 128-row tile of output; VITB200_GEMM_CG=1|2 forces.
@@ -610,6 +645,7 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
   } else if (a_major == 0 && b_major == 1) {
     if (out_f32) return launch_tc<0, 1, BN, float, kEpiGeneric>(cg, ta, tb, p, ep, stream);
     VB_TC(0, 1, bf16, 0u);
+    VB_TC(0, 1, bf16, kEpiDot);
     VB_TC(0, 1, bf16, kEpiMask | kEpiColSum);
     VB_TC(0, 1, bf16, kEpiBitMask | kEpiColSum);
     return launch_tc<0, 1, BN, bf16, kEpiGeneric>(cg, ta, tb, p, ep, stream);

@@ -48,7 +48,7 @@ int attn_f32_backward(const float* qkv, const float* out, const float* d_o, cons
 int attn_bf16_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
                       cudaStream_t stream);
 int attn_bf16_backward(const bf16* qkv, const bf16* out, const bf16* d_o, const float* lse, float* delta, bf16* dqkv,
-                       int B, int T, int H, int hs, float scale, cudaStream_t stream);
+                       int B, int T, int H, int hs, float scale, cudaStream_t stream, bool delta_ready = false);
 
 // tcgen05 attention (head_size 64, T <= 256); returns kErrUnsupported outside that envelope
 int attn_tc_forward(const bf16* qkv, bf16* out, float* lse, int B, int T, int H, int hs, float scale,
