@@ -256,7 +256,7 @@ def run_reference(args):
 def _recorded_traffic(args):
     """DRAM bytes per gemm_tc_kernel launch from the committed ncu --set full capture (it cannot be measured inside
     a timed run); only valid for the workload it was captured on."""
-    path = os.path.join(ROOT, "profiles", "r01_gemm_traffic.json")
+    path = os.path.join(ROOT, "profiles", "r02_gemm_traffic.json")
     if args.model != "vit_b16" or args.batch != 256 or args.dtype != "bf16" or not os.path.exists(path):
         return None
     with open(path) as f:
