@@ -380,6 +380,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
 // Both groups drain half of each accumulator (32 columns) once a unit's last chunk is committed.
 constexpr int kBwdThreads = 64 + 8 * 32 + 32;   // producer, S/dP issuer, 8 element-wise warps, output-MMA issuer
 constexpr int kOutWarp = 10;
+// DW (round 2): four more warps (11-14, one per tensor-memory lane quarter) drain the accumulators, so the element-wise
+// warps never stop for the read-out and its uncoalesced row stores (35 of 319 us per ViT-B/16 layer with the stores
+// removed, profiles/r02_attn_bwd_bound_experiments.txt) and the accumulators are released as early as possible.
+constexpr int kBwdThreadsDW = kBwdThreads + 4 * 32;
 constexpr int kStatBytes = 2048;            // lse*log2e [256] | delta*scale [256] per stage
 
 struct BwdParams {
@@ -460,8 +464,8 @@ __device__ __forceinline__ void bwd_piece(uint32_t tS, uint32_t tP, int c0, int 
   if (MODE == 1) tmem_st_n<N / 2>(tP + static_cast<uint32_t>(d0), pk1);
 }
 
-template <int MODE>
-__global__ void __launch_bounds__(kBwdThreads, 1)
+template <int MODE, bool DW>
+__global__ void __launch_bounds__(DW ? kBwdThreadsDW : kBwdThreads, 1)
 attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                    const float* __restrict__ lse, const float* __restrict__ delta, bf16* __restrict__ dqkv,
                    const BwdParams p) {
@@ -501,7 +505,7 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
       ptx::mbar_init(&slot_free[s], 1);
     }
     ptx::mbar_init(acc_full, 1);
-    ptx::mbar_init(acc_free, 8);
+    ptx::mbar_init(acc_free, DW ? 4 : 8);
     ptx::fence_barrier_init();
   }
   if (warp == 1) {
@@ -659,6 +663,58 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
         }
       }
     }
+  } else if (DW && warp > kOutWarp) {
+    // ------------------------------------------------------------------ drain warps (DW): accumulators -> bf16 rows of dqkv
+    const int q = warp & 3;
+    const uint32_t lane_base = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const int my_items = blockIdx.x < p.items ? (p.items - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int total_units = my_items * ntile;
+    for (int u = 0; u < total_units; ++u) {
+      const int it_u = u / ntile, t = u - it_u * ntile;
+      const int item = blockIdx.x + it_u * gridDim.x;
+      const int b = item / p.H, h = item - b * p.H;
+      const int row = t * QT + q * 32 + lane;
+      const bool live = row < p.T && !(p.dbg & 2);
+      bf16* grow = dqkv + (static_cast<int64_t>(b) * p.T + (live ? row : 0)) * (3 * static_cast<int64_t>(E)) + h * HS;
+      ptx::mbar_wait(acc_full, static_cast<uint32_t>(u) & 1u);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {     // 32 columns of each accumulator at a time (register budget)
+        uint32_t r0[32], r1[32];
+        ptx::tmem_ld_32x32(lane_base + kAcc0 + static_cast<uint32_t>(half * 32), r0);
+        if (MODE == 1 || dual) ptx::tmem_ld_32x32(lane_base + kAcc1 + static_cast<uint32_t>(half * 32), r1);
+        ptx::tmem_ld_wait();
+        if (half == 1) {                         // everything is in registers: the next unit may overwrite the accumulators
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(acc_free);
+        }
+        if (MODE == 0 && dual) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) r0[j] = __float_as_uint(__uint_as_float(r0[j]) + __uint_as_float(r1[j]));
+        }
+        auto put = [&](bf16* dst, const uint32_t (&r)[32]) {     // 32 columns = 64 contiguous bytes of my row
+          uint32_t w[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) w[j] = pack_bf16x2(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+          if (p.st256) {
+            const uint32_t lo[8] = {w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7]};
+            const uint32_t hi[8] = {w[8], w[9], w[10], w[11], w[12], w[13], w[14], w[15]};
+            ptx::stg256(dst, lo);
+            ptx::stg256(dst + 16, hi);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<uint4*>(dst + j * 8) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+          }
+        };
+        if (live) {
+          // MODE 0: dQ -> section 0.  MODE 1: accumulator 0 = dV -> section 2, accumulator 1 = dK -> section 1.
+          put(grow + (MODE == 0 ? 0 : 2) * static_cast<int64_t>(E) + half * 32, r0);
+          if (MODE == 1) put(grow + static_cast<int64_t>(E) + half * 32, r1);
+        }
+      }
+    }
   } else {
     // ------------------------------------------------------------------ element-wise warps: one thread per row
     const int q = warp & 3;                      // tensor-memory lane quarter
@@ -754,11 +810,15 @@ attn_tc_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_cons
           // Drain a unit's accumulators one chunk LATE (after the first chunk of the next unit): right after the unit's
           // own last chunk its output MMAs have only just been issued and both groups would sit on acc_full.
           // (full width: at once — the next unit's S/dP cannot be issued before this unit's accumulators are drained)
-          while (next_drain < total_units && (next_drain + 1) * nchk - 1 < g + (full ? 1 : 0)) drain(next_drain++);
+          if constexpr (!DW) {
+            while (next_drain < total_units && (next_drain + 1) * nchk - 1 < g + (full ? 1 : 0)) drain(next_drain++);
+          }
         }
       }
     }
-    while (next_drain < total_units) drain(next_drain++);
+    if constexpr (!DW) {
+      while (next_drain < total_units) drain(next_drain++);
+    }
     VB_TR(16);
   }
 
@@ -842,8 +902,13 @@ int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const f
   CUtensorMap tq, td;
   VB_PROPAGATE(make_tmap_bf16(&tq, qkv, M, 3 * static_cast<int64_t>(E), 3 * static_cast<int64_t>(E), HS, p.TP));
   VB_PROPAGATE(make_tmap_bf16(&td, d_o, M, E, E, HS, p.TP));
-  VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  VB_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_bwd_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  // VITB200_ATTN_BWD_DRAIN: bit 0 = dQ kernel, bit 1 = dK/dV kernel run with dedicated drain warps.  Measured at the
+  // ViT-B/16 layer shape (profiles/r02_attn_bwd_drain_warps_ab.txt): 342.1 us with 0, 327.1 with 1, 332.4 with 2, 317.4-317.8 with 3.
+  static const int drain_mask = getenv("VITB200_ATTN_BWD_DRAIN") ? atoi(getenv("VITB200_ATTN_BWD_DRAIN")) : 3;
   ProfScope prof(kProfAttnBwd, 8.0 * B * H * T * static_cast<double>(T) * hs, 2, stream);
   const int grid = p.items < num_sms() ? p.items : num_sms();
   // Two tensor-memory plans.  CHUNKED (round 1): chunks of W <= 96 columns flow through two [S | dP] slots, accumulators
@@ -867,10 +932,16 @@ int attn_tc_backward(const bf16* qkv, const bf16* d_o, const float* lse, const f
     }
   };
   plan(1);
-  VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<1>, dim3(grid), dim3(kBwdThreads), smem, stream, 1, tq, td, lse, delta, dqkv, p));
+  if ((drain_mask & 2) && !p.full)
+    VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<1, true>, dim3(grid), dim3(kBwdThreadsDW), smem, stream, 1, tq, td, lse, delta, dqkv, p));
+  else
+    VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<1, false>, dim3(grid), dim3(kBwdThreads), smem, stream, 1, tq, td, lse, delta, dqkv, p));
   VB_CHECK_LAUNCH();
   plan(0);
-  VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<0>, dim3(grid), dim3(kBwdThreads), smem, stream, 1, tq, td, lse, delta, dqkv, p));
+  if ((drain_mask & 1) && !p.full)
+    VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<0, true>, dim3(grid), dim3(kBwdThreadsDW), smem, stream, 1, tq, td, lse, delta, dqkv, p));
+  else
+    VB_CHECK_CUDA(launch_pdl(attn_tc_bwd_kernel<0, false>, dim3(grid), dim3(kBwdThreads), smem, stream, 1, tq, td, lse, delta, dqkv, p));
   VB_CHECK_LAUNCH();
   return kOk;
 }
