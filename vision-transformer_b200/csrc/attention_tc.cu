@@ -328,6 +328,11 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
           for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
         }
         ptx::tmem_ld_wait();
+        if (c == (EWG == 2 ? hg : 1)) {          // my last read of the slot: release it BEFORE the scaling and the stores,
+          ptx::tc_fence_before();                //  the next item's S = Q K^T of this tile can be issued meanwhile
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(&t_free[t]);
+        }
         if (live) {
           uint32_t w[16];
 #pragma unroll
@@ -347,9 +352,6 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, bf16* __restrict_
       }
       if (live && hg == 0 && lse != nullptr)
         lse[(static_cast<int64_t>(b) * p.H + h) * p.T + row] = (mx * sl2) * kLn2 + logf(l);
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(&t_free[t]);
       VB_TR(15);
     }
   }
