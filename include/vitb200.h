@@ -102,6 +102,12 @@ typedef struct {
 
 int vitb200_gemm(const vitb200_gemm_args* args, void* stream);
 
+/* Host arithmetic only (no GPU needed): the split-K count vitb200_gemm picks for an atomically accumulated BF16 contraction
+ * (accumulate = 1, splits = 0) of M x N x K on a device with `sms` SMs — the weight-gradient GEMMs dW = dY^T X behind
+ * nn.Linear's backward (reference transformer.py:22-28,46,56-58).  Units of equal depth are walked statically by sms / 2 CTA
+ * pairs; the rule minimises rounds x (k-blocks per split + hand-over).  -1 on bad arguments. */
+int vitb200_gemm_auto_splits(int M, int N, int K, int sms);
+
 
 /* ------------------------------------------------------------------------------------------------------
  * Single-op entry points (unit-tested one by one against the oracle / torch fp32).

@@ -52,3 +52,29 @@ def test_error_channel_without_gpu():
     # no device in the CPU container -> refuses, never crashes
     assert L.vitb200_device_ok() in (0, 1)
     assert isinstance(L.vitb200_last_error(), bytes)
+
+
+def test_split_k_rule_of_the_weight_gradient_gemms():
+    """Host arithmetic of vitb200_gemm_auto_splits (no GPU): on the static persistent walk over 74 CTA pairs the split count
+    must leave no partly filled extra round — the 'about two waves' rule of round 1 ran ViT-B/16's dW sites as three rounds
+    at 69-81 % occupancy (profiles/r02_gemm_sites_split_rule_{old,new}.log)."""
+    L = ctypes.CDLL(_C.LIB_PATH)
+    L.vitb200_gemm_auto_splits.argtypes = [ctypes.c_int] * 4
+    L.vitb200_gemm_auto_splits.restype = ctypes.c_int
+    cd = lambda a, b: -(-a // b)  # noqa: E731
+    tok = 256 * 197
+    # ViT-B/16 at batch 256: dW1 / dW2 (36 tiles) -> 2 splits = 72 units, dWqkv (27) -> 8 = 216, dWproj (9) -> 8 = 72
+    assert L.vitb200_gemm_auto_splits(3072, 768, tok, 148) == 2
+    assert L.vitb200_gemm_auto_splits(768, 3072, tok, 148) == 2
+    assert L.vitb200_gemm_auto_splits(2304, 768, tok, 148) == 8
+    assert L.vitb200_gemm_auto_splits(768, 768, tok, 148) == 8
+    assert L.vitb200_gemm_auto_splits(0, 8, 8, 148) == -1
+    # every weight-gradient site of every BASELINE config: occupancy of the walk >= 0.85 and >= 4 k-blocks per split
+    for E, tokens in ((384, 64 * 197), (768, tok), (1024, tok), (1280, 128 * 577), (1280, 64 * 730)):
+        for M, N in ((4 * E, E), (E, 4 * E), (3 * E, E), (E, E)):
+            s = L.vitb200_gemm_auto_splits(M, N, tokens, 148)
+            kb = cd(tokens, 64)
+            per = cd(kb, s)
+            units = cd(M, 256) * cd(N, 256) * cd(kb, per)
+            assert 1 <= s <= 64 and per >= 4
+            assert units / (cd(units, 74) * 74) >= 0.85, (E, M, N, s, units)

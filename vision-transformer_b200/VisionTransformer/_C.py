@@ -111,6 +111,8 @@ def _declare(L):
     L.vitb200_gemm.argtypes = [ctypes.POINTER(GemmArgs), c_void_p]
     L.vitb200_gemm.restype = c_int
     L.vitb200_launch_count.restype = c_int64
+    L.vitb200_gemm_auto_splits.argtypes = [c_int, c_int, c_int, c_int]
+    L.vitb200_gemm_auto_splits.restype = c_int
     L.vitb200_abi_sizeof.argtypes = [c_int]
     L.vitb200_abi_sizeof.restype = c_int64
     L.vitb200_prof_class_name.argtypes = [c_int]
@@ -177,7 +179,7 @@ def _declare(L):
 
 EXPORTS = (
     "vitb200_last_error", "vitb200_version", "vitb200_device_ok", "vitb200_launch_count", "vitb200_prof_class_name",
-    "vitb200_prof_begin", "vitb200_prof_end", "vitb200_abi_sizeof", "vitb200_gemm", "vitb200_ln_fwd", "vitb200_ln_bwd",
+    "vitb200_prof_begin", "vitb200_prof_end", "vitb200_abi_sizeof", "vitb200_gemm", "vitb200_gemm_auto_splits", "vitb200_ln_fwd", "vitb200_ln_bwd",
     "vitb200_attn_fwd", "vitb200_attn_bwd", "vitb200_attn_bwd_noalloc", "vitb200_attn_probs", "vitb200_im2col", "vitb200_colsum",
     "vitb200_cross_entropy", "vitb200_cast_f32_bf16", "vitb200_dropout_mask", "vitb200_mask_cast", "vitb200_adamw_flat",
     "vitb200_resize_bilinear_u8", "vitb200_grad_pack", "vitb200_adamw_range", "vitb200_adamw_range_dev",

@@ -161,6 +161,15 @@ int vitb200_gemm(const vitb200_gemm_args* a, void* stream) {
                   static_cast<const float*>(a->B), a->ldb, a->splits, ep, s);
 }
 
+int vitb200_gemm_auto_splits(int M, int N, int K, int sms) {
+  using namespace vb;
+  if (M <= 0 || N <= 0 || K <= 0 || sms <= 0) return -1;
+  const int cg = M > 128 ? 2 : 1;                       // as gemm_tc_bf16: CTA pairs own 256-row tiles
+  const int tiles = ((M + 128 * cg - 1) / (128 * cg)) * ((N + 255) / 256);
+  const int walkers = sms / cg > 0 ? sms / cg : 1;
+  return gemm_tc_auto_splits(tiles, (K + 63) / 64, walkers);
+}
+
 int64_t vitb200_abi_sizeof(int which) {
   switch (which) {
     case 0: return sizeof(vitb200_dims);

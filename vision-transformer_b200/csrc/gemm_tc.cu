@@ -550,6 +550,23 @@ int launch_tc(int cg, const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
 
 }  // namespace
 
+// Split count of an atomically accumulated contraction on the static persistent walk: `tiles` output tiles, `kb_total`
+// 64-deep k-blocks, `walkers` CTAs (or CTA pairs).  Minimises rounds x (k-blocks per split + hand-over); a larger count
+// must win by more than 1 % (fewer splits = less atomic traffic).  Pure host arithmetic (vitb200_gemm_auto_splits).
+int gemm_tc_auto_splits(int tiles, int kb_total, int walkers) {
+  constexpr int kHandOver = 6;   // k-block equivalents per unit: accumulator hand-over + its share of the atomics
+  const int max_s = kb_total / 4 > 0 ? kb_total / 4 : 1;
+  long best = -1;
+  int s = 1;
+  for (int c = 1; c <= max_s && c <= 64; ++c) {
+    const int per = ceil_div(kb_total, c);
+    const int units = tiles * ceil_div(kb_total, per);
+    const long cost = static_cast<long>(ceil_div(units, walkers)) * (per + kHandOver);
+    if (best < 0 || cost * 100 < best * 99) { best = cost; s = c; }
+  }
+  return s;
+}
+
 // Entry used by vitb200_gemm() for in_dtype == BF16.  out_f32 selects the C dtype.
 int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, int64_t lda, const void* B,
                  int64_t ldb, bool out_f32, int splits, const GemmEpilogue& ep, cudaStream_t stream) {
@@ -604,15 +621,7 @@ int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, i
       if (s > max_s) s = max_s;
       if (s < 1) s = 1;
     } else {
-      constexpr int kHandOver = 6;   // k-block equivalents per unit: accumulator hand-over + its share of the atomics
-      long best = -1;
-      s = 1;
-      for (int c = 1; c <= max_s && c <= 64; ++c) {
-        const int per = ceil_div(p.kb_total, c);
-        const int units = tiles * ceil_div(p.kb_total, per);
-        const long cost = static_cast<long>(ceil_div(units, walkers)) * (per + kHandOver);
-        if (best < 0 || cost * 100 < best * 99) { best = cost; s = c; }   // a later candidate must win by > 1 %
-      }
+      s = gemm_tc_auto_splits(tiles, p.kb_total, walkers);
     }
   }
   // Epilogue memory-side switches (VITB200_GEMM_EPI_FLAGS overrides; measured on B200 at the ViT-B/16 proj site, fp32 out

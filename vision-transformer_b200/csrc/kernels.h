@@ -14,6 +14,7 @@ struct AdamWHyper {
 };
 
 // contractions
+int gemm_tc_auto_splits(int tiles, int kb_total, int walkers);
 int gemm_tc_bf16(int M, int N, int K, int a_major, int b_major, const void* A, int64_t lda, const void* B,
                  int64_t ldb, bool out_f32, int splits, const GemmEpilogue& ep, cudaStream_t stream);
 int gemm_f32(int M, int N, int K, int a_major, int b_major, const float* A, int64_t lda, const float* B,
