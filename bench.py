@@ -336,6 +336,9 @@ def run_b200(args):
     ms_step = total_ms / args.steps
     gb = args.batch * world
     value = gb / (ms_step * 1e-3)
+    # device memory held by the trainer after the timed steps (parameters, moments, activation arenas, device-resident
+    # input batches), before the other legs allocate theirs; compare reference_gpu_eager.*.peak_mem_gb
+    peak_mem_gb = torch.cuda.max_memory_allocated(dev) / 2 ** 30
 
     # ---- host-resident inputs through the public step API: `e2e`
     e2e = None
@@ -505,7 +508,7 @@ def run_b200(args):
         "roofline": roofline, "cpu_baseline": cpu,
         "mfu": {"algorithmic_tflops_per_gpu": step_tflops, "of_measured_sustained": step_tflops / pk["tflops_sustained"],
                 "of_measured_burst": step_tflops / pk["tflops_burst"], "of_datasheet_2250": step_tflops / 2250.0},
-        "kernels": kern, "loss_after": loss_after, "last_block_row0": row0,
+        "kernels": kern, "loss_after": loss_after, "peak_mem_gb": peak_mem_gb, "last_block_row0": row0,
         "module_path": module_path, "reference_gpu_eager": ref_eager, "cuda_graph": graph_line,
     }
     emit(line)
