@@ -419,7 +419,8 @@ constexpr int LNB_MAX_STAGES = 4;
 
 // KEEP: xhat / dy of the row stay in registers between the two passes (CH <= 8); otherwise they are re-read from
 // the shared-memory slot in the second pass so that wide rows (E up to 1536, CH = 10 / 12) do not spill.
-template <typename DyT, int CH, bool KEEP>
+// EXACT: E == 128 * CH (every lane owns CH whole chunks), so the per-chunk bounds tests and their divergence regions vanish.
+template <typename DyT, int CH, bool KEEP, bool EXACT>
 __global__ void __launch_bounds__(LNB_WARPS * 32, 1)
 ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, const float* __restrict__ mean_in,
                    const float* __restrict__ rstd_in, const float* __restrict__ gamma, float* __restrict__ g,
@@ -514,7 +515,7 @@ ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, cons
     for (int k = 0; k < CH; ++k) {
       const int i = lane + 32 * k;
       float hh[4] = {0.f, 0.f, 0.f, 0.f}, dd[4] = {0.f, 0.f, 0.f, 0.f};
-      if (i < E4) {
+      if (EXACT || i < E4) {
         row_chunk(i, hh, dd);
         const float4 gm = lds128(sgam + 16 * i);
         const float gg[4] = {gm.x, gm.y, gm.z, gm.w};
@@ -543,7 +544,7 @@ ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, cons
       const int i = lane + 32 * k;
       uint32_t kb = 0xfu;
       if (masked) kb = __shfl_sync(0xffffffffu, keep[k >> 1], (k & 1) * 16 + (lane >> 1)) >> ((lane & 1) * 4);
-      if (i < E4) {
+      if (EXACT || i < E4) {
         const float4 gm = lds128(sgam + 16 * i);
         const float gg[4] = {gm.x, gm.y, gm.z, gm.w};
         float hh[4], dd[4];
@@ -588,7 +589,7 @@ ln_bwd_ring_kernel(const DyT* __restrict__ dy, const float* __restrict__ x, cons
 #pragma unroll
   for (int k = 0; k < CH; ++k) {
     const int i = lane + 32 * k;
-    if (i < E4) {
+    if (EXACT || i < E4) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         atomicAdd(&s_acc[i * 4 + j], rg[k][j]);
@@ -711,17 +712,25 @@ int ln_backward(const void* dy, bool dy_bf16, const float* x, const float* mean,
       const size_t smem = fixed + static_cast<size_t>(nst) * nwarps * stage;
       const int ch = ceil_div(E, 128);
       const int grid = std::min(num_sms(), ceil_div(M, nwarps));
+      static const bool exact_on = !(getenv("VITB200_LNB_EXACT") && atoi(getenv("VITB200_LNB_EXACT")) == 0);
 #define VB_LN_RING(T, C)                                                                                          \
   do {                                                                                                            \
     static bool attr_set = false; /* one flag per instantiation: the opt-in is the 216 KB bound, not this call's size */ \
     if (!attr_set) {                                                                                              \
-      VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C, (C <= 8)>,                                      \
+      VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C, (C <= 8), false>,                               \
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));               \
+      VB_CHECK_CUDA(cudaFuncSetAttribute(ln_bwd_ring_kernel<T, C, (C <= 8), true>,                                \
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024));               \
       attr_set = true;                                                                                            \
     }                                                                                                             \
-    VB_CHECK_CUDA(launch_pdl(ln_bwd_ring_kernel<T, C, (C <= 8)>, dim3(grid), dim3(nwarps * 32), smem, stream, 1,    \
-                             static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta,         \
-                             static_cast<T*>(dyn), dyn_colsum, drop, M, E, nst));                                 \
+    if (exact_on && E == 128 * C)                                                                                 \
+      VB_CHECK_CUDA(launch_pdl(ln_bwd_ring_kernel<T, C, (C <= 8), true>, dim3(grid), dim3(nwarps * 32), smem, stream, 1, \
+                               static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta,       \
+                               static_cast<T*>(dyn), dyn_colsum, drop, M, E, nst));                               \
+    else                                                                                                          \
+      VB_CHECK_CUDA(launch_pdl(ln_bwd_ring_kernel<T, C, (C <= 8), false>, dim3(grid), dim3(nwarps * 32), smem, stream, 1, \
+                               static_cast<const T*>(dy), x, mean, rstd, gamma, g, add_to_g, dgamma, dbeta,       \
+                               static_cast<T*>(dyn), dyn_colsum, drop, M, E, nst));                               \
   } while (0)
 #define VB_LN_RING_CH(T)                                                                                          \
   do {                                                                                                            \
