@@ -58,7 +58,9 @@ struct TcParams {
   int flags;   // bit 0: epilogue prefetches its read-side operands one tile ahead
 };
 
-template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG>
+// EXACT: M is a multiple of the tile rows (128 * CG) and N of BN — the epilogue carries no bounds tests, so its four row
+// passes per chunk are one straight-line region the compiler can interleave (loads first, stores last).
+template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG, bool EXACT>
 __global__ void __launch_bounds__((gemm_threads<OutT, CG>()), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                const TcParams p, const GemmEpilogue ep) {
@@ -231,8 +233,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
         const int mb = tl / p.n_tiles;
         const int m = (mb * CG + static_cast<int>(rank)) * BM + q * 32 + lane;
         const int nb = (tl - mb * p.n_tiles) * BN + half * CW;
-        if (m < p.M && nb < p.N) {
-          const int ncols = min(CW, p.N - nb);
+        if (EXACT || (m < p.M && nb < p.N)) {
+          const int ncols = EXACT ? CW : min(CW, p.N - nb);
           const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
           const int64_t off = orow * ep.ldc + nb;
           // bit 1: one prefetch.global.L2 per 128-byte line and lane (the bulk form is a uniform-datapath instruction:
@@ -265,28 +267,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
       const int nb = n_blk * BN + half * CW;     // first column of my share
       constexpr int NCH = CW / 32;
       uint32_t r[32];
-      if (nb < p.N) ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * CW), r);
+      if (EXACT || nb < p.N) ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * CW), r);
       // Read-side operands (residual / dReLU mask) are fetched ONE CHUNK AHEAD into registers: their L2 latency is
       // covered by the previous chunk's transpose + stores instead of stalling every chunk.
       EpiPre pre_nx[4];
       float dacc[4] = {0.f, 0.f, 0.f, 0.f};   // kEpiDot: per-row partial sums over the two 32-column chunks of a 64-wide head
       auto fetch_chunk = [&](int cc, EpiPre (&dst)[4]) {
         const int nn = nb + cc * 32 + cg * 8;
-        if (nn >= p.N) return;
+        if (!EXACT && nn >= p.N) return;
 #pragma unroll
         for (int pass = 0; pass < 4; ++pass) {
           const int m = m0 + pass * 8 + rsub;
           const int64_t orow = VB_EPI(kEpiRowMap, ep.row_period > 0) ? epi_out_row(ep, m) : static_cast<int64_t>(m);
-          if (m < p.M) epilogue_fetch8<OutT, EPI>(ep, orow * ep.ldc + nn, m, nn, dst[pass], p.flags);
+          if (EXACT || m < p.M) epilogue_fetch8<OutT, EPI>(ep, orow * ep.ldc + nn, m, nn, dst[pass], p.flags);
         }
       };
       fetch_chunk(0, pre_nx);
 #pragma unroll 1
       for (int c = 0; c < NCH; ++c) {
         const int n0 = nb + c * 32;
-        if (n0 >= p.N) break;                          // warp-uniform
+        if (!EXACT && n0 >= p.N) break;                // warp-uniform
         const int n = n0 + cg * 8;
-        const bool ncol_ok = n < p.N;
+        const bool ncol_ok = EXACT || n < p.N;
         EpiPre pre[4];
 #pragma unroll
         for (int pass = 0; pass < 4; ++pass) pre[pass] = pre_nx[pass];
@@ -315,7 +317,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                       r[4 * j + 2], r[4 * j + 3]);
         __syncwarp();
         // (3) next chunk's TMEM load flies while this chunk is finished
-        if (c + 1 < NCH && n0 + 32 < p.N)
+        if (c + 1 < NCH && (EXACT || n0 + 32 < p.N))
           ptx::tmem_ld_32x32(t_row + static_cast<uint32_t>(half * CW + (c + 1) * 32), r);
         float cs[8];
 #pragma unroll
@@ -328,7 +330,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
           const float4 hi = ptx::lds128(stg_s + static_cast<uint32_t>(R * 128 + (((2 * cg + 1) ^ (R & 7)) << 4)));
           uint32_t sign8 = 0;
           float dpart = 0.f;
-          if (m < p.M && ncol_ok) {
+          if (EXACT || (m < p.M && ncol_ok)) {
             float v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
             epilogue_finish8<OutT, EPI>(ep, m, n, p.N, off[pass], v, pre[pass], bias8, p.flags);
             if constexpr (sizeof(OutT) == 2) {
@@ -360,7 +362,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
                 float t = dacc[pass] + dpart;                //  stride 4
                 t += __shfl_xor_sync(0xffffffffu, t, 2);
                 t += __shfl_xor_sync(0xffffffffu, t, 1);
-                if (cg == 0 && m < p.M && ncol_ok) {
+                if (cg == 0 && (EXACT || (m < p.M && ncol_ok))) {
                   const int bi = m / ep.dot_T, ti = m - bi * ep.dot_T;
                   ep.dot_out[(static_cast<int64_t>(bi) * ep.dot_H + (n0 >> 6)) * ep.dot_T + ti] = t;
                 }
@@ -373,7 +375,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant_
             uint32_t w = sign8 << (8 * cg);
             w |= __shfl_xor_sync(0xffffffffu, w, 1);
             w |= __shfl_xor_sync(0xffffffffu, w, 2);
-            if (cg == 0 && m < p.M) ep.bits_out[static_cast<int64_t>(n0 >> 5) * ep.bits_rows + m] = w;
+            if (cg == 0 && (EXACT || m < p.M)) ep.bits_out[static_cast<int64_t>(n0 >> 5) * ep.bits_rows + m] = w;
           }
         }
         if (VB_EPI(kEpiColSum, ep.col_sum != nullptr)) {   // warp-uniform
@@ -489,12 +491,12 @@ int make_tmap_bf16_heads(void* map_out, const void* base, int64_t rows, int sect
 
 namespace {
 
-template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG>
+template <int AMAJ, int BMAJ, int BN, typename OutT, uint32_t EPI, int CG, bool EXACT = false>
 int launch_tc_cg(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, const GemmEpilogue& ep,
                  cudaStream_t stream) {
   using Cfg = TileCfg<BN, CG, epi_warps<OutT, CG>()>;
   constexpr int kThreads = gemm_threads<OutT, CG>();
-  auto kern = gemm_tc_kernel<AMAJ, BMAJ, BN, OutT, EPI, CG>;
+  auto kern = gemm_tc_kernel<AMAJ, BMAJ, BN, OutT, EPI, CG, EXACT>;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
@@ -544,7 +546,15 @@ int launch_tc(int cg, const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
   }
 #endif
   if (cg == 4) cg = 2;
-  if (cg == 2) return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 2>(ta, tb, p, ep, stream);
+  if (cg == 2) {
+    // the hot call sites of the training step tile exactly (ViT-B/16 at batch 256: M = 50432 = 197 x 256, N = 768 .. 3072)
+    if constexpr (EPI != kEpiGeneric) {
+      static const bool exact_on = !(getenv("VITB200_GEMM_EXACT") && atoi(getenv("VITB200_GEMM_EXACT")) == 0);
+      if (exact_on && p.M % (2 * BM) == 0 && p.N % BN == 0)
+        return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 2, true>(ta, tb, p, ep, stream);
+    }
+    return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 2>(ta, tb, p, ep, stream);
+  }
   return launch_tc_cg<AMAJ, BMAJ, BN, OutT, EPI, 1>(ta, tb, p, ep, stream);
 }
 

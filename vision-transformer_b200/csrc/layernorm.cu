@@ -163,7 +163,7 @@ ln_fwd_reg_kernel(const float* __restrict__ x, const float* __restrict__ gamma, 
 constexpr int LNF_WARPS = 16;
 constexpr int LNF_MAX_STAGES = 4;
 
-template <typename OutT, int VPL>
+template <typename OutT, int VPL, bool EXACT>   // EXACT: E == 128 * VPL, no per-chunk bounds tests (see ln_bwd_ring_kernel)
 __global__ void __launch_bounds__(LNF_WARPS * 32, 1)
 ln_fwd_ring_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                    OutT* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out, int M, int E,
@@ -188,8 +188,8 @@ ln_fwd_ring_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
       const int i = lane + 32 * k;
-      gm[k] = i < nq ? __ldg(reinterpret_cast<const float4*>(gamma) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-      bt[k] = i < nq ? __ldg(reinterpret_cast<const float4*>(beta) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      gm[k] = (EXACT || i < nq) ? __ldg(reinterpret_cast<const float4*>(gamma) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      bt[k] = (EXACT || i < nq) ? __ldg(reinterpret_cast<const float4*>(beta) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
   }
   const int w0 = blockIdx.x * nw + warp, stride = gridDim.x * nw;
@@ -214,14 +214,14 @@ ln_fwd_ring_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
       const int i = lane + 32 * k;
-      cur[k] = i < nq ? lds128(sx + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      cur[k] = (EXACT || i < nq) ? lds128(sx + 16 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
       s += (cur[k].x + cur[k].y) + (cur[k].z + cur[k].w);
     }
     const float mean = warp_sum(s) / static_cast<float>(E);
     float sq = 0.f;
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
-      if (lane + 32 * k < nq) {
+      if (EXACT || lane + 32 * k < nq) {
         const float d0 = cur[k].x - mean, d1 = cur[k].y - mean, d2 = cur[k].z - mean, d3 = cur[k].w - mean;
         sq = fmaf(d0, d0, sq); sq = fmaf(d1, d1, sq); sq = fmaf(d2, d2, sq); sq = fmaf(d3, d3, sq);
       }
@@ -235,7 +235,7 @@ ln_fwd_ring_kernel(const float* __restrict__ x, const float* __restrict__ gamma,
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
       const int i = lane + 32 * k;
-      if (i < nq) {
+      if (EXACT || i < nq) {
         float4 gk, bk;
         if constexpr (GB_REG) {
           gk = gm[k]; bk = bt[k];
@@ -641,12 +641,18 @@ int ln_forward(const float* x, const float* gamma, const float* beta, void* y, b
   do {                                                                                                            \
     static bool attr_set = false;                                                                                 \
     if (!attr_set) {                                                                                              \
-      VB_CHECK_CUDA(cudaFuncSetAttribute(ln_fwd_ring_kernel<T, V>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+      VB_CHECK_CUDA(cudaFuncSetAttribute(ln_fwd_ring_kernel<T, V, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                         208 * 1024));                                                            \
+      VB_CHECK_CUDA(cudaFuncSetAttribute(ln_fwd_ring_kernel<T, V, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                          208 * 1024));                                                            \
       attr_set = true;                                                                                            \
     }                                                                                                             \
-    VB_CHECK_CUDA(launch_pdl(ln_fwd_ring_kernel<T, V>, dim3(grid), dim3(LNF_WARPS * 32), smem, stream, 1, x, gamma, \
-                             beta, static_cast<T*>(y), mean, rstd, M, E, eps, nst));                              \
+    if (E == 128 * V)                                                                                             \
+      VB_CHECK_CUDA(launch_pdl(ln_fwd_ring_kernel<T, V, true>, dim3(grid), dim3(LNF_WARPS * 32), smem, stream, 1, x, \
+                               gamma, beta, static_cast<T*>(y), mean, rstd, M, E, eps, nst));                     \
+    else                                                                                                          \
+      VB_CHECK_CUDA(launch_pdl(ln_fwd_ring_kernel<T, V, false>, dim3(grid), dim3(LNF_WARPS * 32), smem, stream, 1, x, \
+                               gamma, beta, static_cast<T*>(y), mean, rstd, M, E, eps, nst));                     \
   } while (0)
 #define VB_LNF_RING_V(T)                                                                                          \
   do {                                                                                                            \
